@@ -1,0 +1,154 @@
+/*
+ * sglk_fp8.h — C ABI of libsglk_sm100a.so: the B200 (sm_100a) implementation of the FP8
+ * block-quantized linear hot path of sgl-kernel.
+ *
+ * This is the drop-in boundary.  Plain pointers and sizes only — no torch types — so any host
+ * (the Python `sgl_kernel` package in this repo via ctypes, or a C++ TORCH_LIBRARY shim, see
+ * INTEGRATION.md) can bind it.  The shape of the interface follows the reference's own
+ * "thin C-ABI" pattern for JIT kernels:
+ *   /root/reference/include/sgl_kernel/jit_kernel/gemm/per_token_group_quant_8bit.hpp:272-302
+ * (extern "C" launcher taking a queue pointer, raw data pointers and scalars), with a CUDA
+ * stream in place of the SYCL queue.
+ *
+ * Conventions
+ *   - All data pointers are DEVICE pointers (or pointers valid on the device).  Nothing is copied.
+ *   - Work is enqueued on `stream` (a cudaStream_t passed as void*); no host synchronisation, no
+ *     allocation, CUDA-graph capturable.  (Reference: "no .wait() -- PyTorch owns stream
+ *     synchronization", ...8bit.hpp:265; src/sycl/Utils.h:75-77.)
+ *   - Every function returns 0 on success, a negative SGLK_E_* code for a rejected argument
+ *     (validated BEFORE any launch, like the reference's TORCH_CHECKs,
+ *     src/sycl/per_token_group_quant_8bit.cpp:231-237,265-274,356) or a positive cudaError_t for a
+ *     launch failure.  Nothing throws across the ABI.
+ *   - There is no CPU fallback: on a machine without an sm_100 device the launch fails loudly.
+ */
+#ifndef SGLK_FP8_H_
+#define SGLK_FP8_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define SGLK_ABI_VERSION 1
+
+#if defined(__GNUC__)
+#define SGLK_API __attribute__((visibility("default")))
+#else
+#define SGLK_API
+#endif
+
+/* element types (in_dtype / out_dtype arguments) */
+enum {
+  SGLK_BF16 = 0,
+  SGLK_F16 = 1,
+  SGLK_F32 = 2,
+  SGLK_E4M3 = 3, /* float8_e4m3fn */
+  SGLK_INT8 = 4
+};
+
+/* layouts of output_s for the quant op (what the reference derives from output_s's dtype and
+ * strides, src/sycl/per_token_group_quant_8bit.cpp:259-262,279-335) */
+enum {
+  SGLK_SCALE_F32_ROW_MAJOR = 0,  /* fp32 [M, G] contiguous                               */
+  SGLK_SCALE_F32_COL_MAJOR = 1,  /* fp32, element (m,g) at g*scale_stride + m            */
+  SGLK_SCALE_UE8M0_ROW_MAJOR = 2, /* uint8 exponent+127, [M, G] contiguous               */
+  SGLK_SCALE_UE8M0_COL_PACKED = 3 /* 4 exponent bytes per int32, int32 (m, g/4) at (g/4)*scale_stride + m */
+};
+
+/* validation errors */
+enum {
+  SGLK_OK = 0,
+  SGLK_E_NULL = -1,        /* null pointer                                   */
+  SGLK_E_DTYPE = -2,       /* unsupported dtype                              */
+  SGLK_E_GROUP = -3,       /* unsupported group size                         */
+  SGLK_E_SHAPE = -4,       /* inconsistent / unsupported shape               */
+  SGLK_E_STRIDE = -5,      /* stride or alignment not supported              */
+  SGLK_E_LAYOUT = -6,      /* unknown scale layout                           */
+  SGLK_E_ARG = -7,         /* other invalid argument                         */
+  SGLK_E_DRIVER = -8,      /* cuTensorMapEncodeTiled unavailable / failed    */
+  SGLK_E_VARIANT = -9      /* unknown kernel variant                         */
+};
+
+SGLK_API int sglk_abi_version(void);
+SGLK_API const char* sglk_error_string(int code);
+
+/*
+ * Replaces: at::native::xpu::sgl_per_token_group_quant_8bit
+ *   /root/reference/src/sycl/per_token_group_quant_8bit.cpp:222-386  (host launcher)
+ *   /root/reference/src/sycl/per_token_group_quant_8bit.cpp:48-220   (kernel)
+ * and its JIT twin per_token_group_quant_8bit_forward_<in>_<out>_<gs>
+ *   /root/reference/include/sgl_kernel/jit_kernel/gemm/per_token_group_quant_8bit.hpp:272-302.
+ *
+ * input     : [num_groups * group_size] contiguous elements of in_dtype (bf16 / f16 / f32)
+ * output_q  : same number of 1-byte codes (e4m3fn or int8), contiguous
+ * output_s  : scales, layout given by scale_layout; scale_stride in elements of the scale
+ *             tensor's dtype (floats, or int32 words for SGLK_SCALE_UE8M0_COL_PACKED)
+ * groups_per_row = hidden_dim / group_size (needed for the column-major layouts)
+ * group_size in {16, 32, 64, 128, 256, 512}
+ * Math: absmax = max(eps, max|x|); s = absmax / max_8bit (correctly rounded);
+ *       UE8M0: s = 2^ceil(log2(max(s,1e-10))); q = clamp(x / s, min_8bit, max_8bit) -> RNE e4m3 /
+ *       truncating int8.  Division is IEEE-correct (bit-exact with the torch oracle
+ *       tests/test_per_token_group_quant_8bit.py:23-40, unlike the reference's x * (1/s)).
+ */
+SGLK_API int sglk_per_token_group_quant_8bit(const void* input, void* output_q, void* output_s,
+                                    int64_t num_groups, int64_t groups_per_row, int64_t group_size,
+                                    int in_dtype, int out_dtype, float eps, float min_8bit,
+                                    float max_8bit, int scale_ue8m0, int scale_layout,
+                                    int64_t scale_stride, void* stream);
+
+/*
+ * Replaces: at::native::xpu::sgl_per_token_group_quant_8bit_v2 for its fused-activation mode
+ *   /root/reference/src/sycl/per_token_group_quant_8bit_v2.cpp:714-843 (host), :255-262 (silu*mul).
+ * input is [M, 2*hidden] (gate | up); the quantised tensor is silu(gate)*up rounded to in_dtype,
+ * [M, hidden].  Other arguments as above (groups are counted on the OUTPUT).
+ */
+SGLK_API int sglk_silu_mul_per_token_group_quant_8bit(const void* input, void* output_q, void* output_s,
+                                             int64_t num_tokens, int64_t hidden, int64_t group_size,
+                                             int in_dtype, int out_dtype, float eps, float min_8bit,
+                                             float max_8bit, int scale_ue8m0, int scale_layout,
+                                             int64_t scale_stride, void* stream);
+
+/*
+ * Replaces: torch::Tensor fp8_blockwise_scaled_mm(mat_a, mat_b, scales_a, scales_b, out_dtype)
+ *   declared /root/reference/include/sgl_kernel_ops.h:581-586, wrapped python/sgl_kernel/gemm.py:24-31,
+ *   semantics pinned by tests/test_fp8_blockwise_gemm.py:23-63 (the reference ships no kernel).
+ *
+ * C[m,n] = sum_kb sa[m,kb] * sb[kb, n/128] * sum_{k in kb} A[m,k] * B[k,n]      (fp32 accumulate)
+ * A  : e4m3fn [M,K], row-major, row stride lda (elements)
+ * B  : e4m3fn [K,N] COLUMN-major == [N,K] row-major, stride ldb between consecutive n
+ * sa : fp32 (m,kb) at m*sa_stride_m + kb*sa_stride_k   (M-major from the test, or quant's row-major)
+ * sb : fp32 (kb,nb) at kb*sb_stride_k + nb*sb_stride_n, nb = n/128, ceil(N/128) columns
+ * C  : bf16 or f16 [M,N], row stride ldc
+ * Requirements: K % 16 == 0, lda % 16 == 0, ldb % 16 == 0, A/B 16-byte aligned.  Any M >= 0, N >= 0.
+ */
+SGLK_API int sglk_fp8_blockwise_scaled_mm(const void* A, const void* B, const float* sa, const float* sb,
+                                 void* C, int64_t M, int64_t N, int64_t K, int64_t lda, int64_t ldb,
+                                 int64_t ldc, int64_t sa_stride_m, int64_t sa_stride_k,
+                                 int64_t sb_stride_k, int64_t sb_stride_n, int out_dtype,
+                                 void* stream);
+
+/* Same, with an explicit kernel variant (tile shape / CTA pairing) for tests and tuning.
+ * variant = -1 selects the heuristic used by sglk_fp8_blockwise_scaled_mm.
+ * num_sms <= 0 uses every SM of the current device. */
+SGLK_API int sglk_fp8_blockwise_scaled_mm_ex(const void* A, const void* B, const float* sa, const float* sb,
+                                    void* C, int64_t M, int64_t N, int64_t K, int64_t lda,
+                                    int64_t ldb, int64_t ldc, int64_t sa_stride_m,
+                                    int64_t sa_stride_k, int64_t sb_stride_k, int64_t sb_stride_n,
+                                    int out_dtype, int variant, int num_sms, void* stream);
+
+/* number of GEMM variants compiled in, and a printable name for each ("" if out of range) */
+SGLK_API int sglk_gemm_num_variants(void);
+SGLK_API const char* sglk_gemm_variant_name(int variant);
+/* the variant the heuristic would pick for a problem */
+SGLK_API int sglk_gemm_pick_variant(int64_t M, int64_t N, int64_t K);
+
+/* Device self-check of the quant kernel's division scheme against __fdiv_rn over every bf16
+ * numerator for `num_scales` scales; writes the mismatch count to *mismatches (device ptr). */
+SGLK_API int sglk_debug_check_division(const float* scales, int64_t num_scales, unsigned long long* mismatches,
+                              void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SGLK_FP8_H_ */

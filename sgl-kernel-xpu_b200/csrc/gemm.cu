@@ -1,0 +1,537 @@
+// fp8 (e4m3) blockwise-scaled GEMM for sm_100a:  C = sum_kb (sa[:,kb] x sb[kb,:]) .* (A_kb @ B_kb)
+//
+// Implements the op the reference only declares (include/sgl_kernel_ops.h:581-586,
+// python/sgl_kernel/gemm.py:24-31); semantics from tests/test_fp8_blockwise_gemm.py:23-63.
+//
+// Design (B200-first; nothing here derives from the reference, which ships no kernel for this op):
+//   * persistent, warp-specialised CTA: warp 0 = TMA producer, warp 1 = tcgen05.mma issuer,
+//     warp 2 = TMEM allocator, warps 4..11 = promotion/epilogue warps.
+//   * operands are both K-major e4m3, staged by TMA (128-byte swizzle) into a kStages-deep
+//     shared-memory ring; one stage = one 128-deep K block = one scale block.
+//   * fp32 (not UE8M0) scales rule out the hardware block-scaled MMA kinds, so every K block is
+//     accumulated on its own into a TMEM accumulator stage (tcgen05.mma.kind::f8f6f4, 4 x K=32,
+//     first one overwrites) and *promoted* in registers: the epilogue warps tcgen05.ld the
+//     128 x BLOCK_N partial, and do acc += partial * (sa[m,kb]*sb[kb,nb]) with packed FFMA2.
+//     kAccStages TMEM stages let the MMA of block kb+1.. run under the promotion of block kb.
+//   * kCG == 2 pairs two CTAs (cta_group::2): one 256 x BLOCK_N tile per pair, each CTA loads its
+//     own 128 rows of A and half of the B tile; the leader CTA issues the MMAs for both.
+//   * C leaves through per-warp swizzled smem boxes and TMA stores (coalesced, clipped at M/N
+//     edges by the tensor map); a plain predicated store path covers unaligned ldc.
+#include <cuda.h>
+#include <cuda_bf16.h>
+#include <cuda_fp16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <string.h>
+
+#include <mutex>
+
+#include "../../include/sglk_fp8.h"
+#include "common.cuh"
+#include "ptx.cuh"
+
+namespace sglk {
+
+constexpr int BLOCK_M = 128;   // rows per CTA (TMEM lanes)
+constexpr int BLOCK_K = 128;   // one scale block; 128 B of e4m3 = one 128B-swizzle atom row
+constexpr int UMMA_K = 32;     // K per tcgen05.mma for 8-bit operands
+constexpr int kNumEpiWarps = 8;
+constexpr int kNumThreads = 128 + kNumEpiWarps * 32;   // 4 control warps + 8 epilogue warps
+constexpr int kStoreBoxCols = 64;                      // bf16 columns per TMA store box (128 B)
+
+struct GemmParams {
+  const float* sa;
+  const float* sb;
+  void* C;
+  int64_t M, N, K;
+  int64_t ldc;
+  int64_t sa_sm, sa_sk, sb_sk, sb_sn;
+  int32_t num_m_blocks, num_n_blocks, num_k_blocks, num_sb_cols;
+  int32_t group_m;   // tile rasterisation: tiles of `group_m` consecutive m-blocks share B panels in L2
+};
+
+template <int BLOCK_N, int kCG>
+struct Cfg {
+  static constexpr int LOAD_N = BLOCK_N / kCG;                 // B rows this CTA loads per stage
+  static constexpr int A_BYTES = BLOCK_M * BLOCK_K;            // 16 KB
+  static constexpr int B_BYTES = LOAD_N * BLOCK_K;
+  static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
+  static constexpr int NC = BLOCK_N / 2;                       // columns per epilogue warp
+  static constexpr int kAccStages = (512 / BLOCK_N) < 4 ? (512 / BLOCK_N) : 4;
+  static constexpr int TMEM_COLS = kAccStages * BLOCK_N;       // 256 or 512: power of two
+  static constexpr int STORE_BYTES = kNumEpiWarps * 32 * kStoreBoxCols * 2;   // 32 KB
+  static constexpr int BAR_BYTES = 1024;
+  static constexpr int smem_bytes(int stages) { return 1024 + stages * STAGE_BYTES + STORE_BYTES + BAR_BYTES; }
+  static_assert(BLOCK_N % 64 == 0 && BLOCK_N <= 256, "BLOCK_N");
+  static constexpr bool kCanTmaStore = (NC % kStoreBoxCols) == 0;
+  static_assert((TMEM_COLS & (TMEM_COLS - 1)) == 0 && TMEM_COLS >= 32 && TMEM_COLS <= 512, "TMEM columns");
+};
+
+// K-major, 128-byte-swizzled operand tile: 8-row x 128-B atoms, 1024 B apart (SBO); LBO unused.
+__device__ __forceinline__ uint64_t make_smem_desc(uint32_t smem_addr) {
+  uint64_t d = 0;
+  d |= uint64_t((smem_addr & 0x3FFFFu) >> 4);        // start address      bits [0,14)
+  d |= uint64_t(0) << 16;                            // leading byte offset bits [16,30) (ignored)
+  d |= uint64_t(1024 >> 4) << 32;                    // stride byte offset  bits [32,46)
+  d |= uint64_t(1) << 46;                            // descriptor version (sm_100)
+  d |= uint64_t(2) << 61;                            // SWIZZLE_128B
+  return d;
+}
+// kind::f8f6f4, A = B = e4m3, D = f32, both K-major, dense
+__host__ __device__ constexpr uint32_t make_idesc(int umma_m, int umma_n) {
+  return (1u << 4)                        // D format f32
+       | (0u << 7) | (0u << 10)           // A, B format e4m3
+       | (0u << 15) | (0u << 16)          // A, B K-major
+       | (uint32_t(umma_n >> 3) << 17)
+       | (uint32_t(umma_m >> 4) << 24);
+}
+
+template <typename OutT> __device__ __forceinline__ uint32_t pack2(float a, float b);
+template <> __device__ __forceinline__ uint32_t pack2<__nv_bfloat16>(float a, float b) {
+  const __nv_bfloat162 v = __floats2bfloat162_rn(a, b);
+  return *reinterpret_cast<const uint32_t*>(&v);
+}
+template <> __device__ __forceinline__ uint32_t pack2<__half>(float a, float b) {
+  const __half2 v = __floats2half2_rn(a, b);
+  return *reinterpret_cast<const uint32_t*>(&v);
+}
+
+// tile index -> (m_block, n_block): groups of `group_m` m-blocks are walked n-major so that the
+// CTAs resident at one time share a few B panels and `group_m` A panels in L2.
+__device__ __forceinline__ void tile_coords(int tile, const GemmParams& p, int& mb, int& nb) {
+  const int per_group = p.group_m * p.num_n_blocks;
+  const int g = tile / per_group;
+  const int first_m = g * p.group_m;
+  const int rows = min(p.group_m, p.num_m_blocks - first_m);
+  const int in_g = tile - g * per_group;
+  mb = first_m + in_g % rows;
+  nb = in_g / rows;
+}
+
+template <int BLOCK_N, int kStages, int kCG, typename OutT, bool kTmaStore>
+__global__ void __launch_bounds__(kNumThreads, 1)
+fp8_blockwise_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
+                          const __grid_constant__ CUtensorMap tmap_c, const GemmParams p) {
+  using C = Cfg<BLOCK_N, kCG>;
+  constexpr int NC = C::NC;
+  constexpr int kAccStages = C::kAccStages;
+  static_assert(!kTmaStore || C::kCanTmaStore, "TMA-store epilogue needs >= 64 columns per warp");
+
+  extern __shared__ uint8_t smem_raw[];
+  // 128B-swizzled TMA/UMMA tiles need 1024-byte alignment
+  const uint32_t smem_base = (ptx::smem_u32(smem_raw) + 1023u) & ~1023u;
+  const uint32_t smem_store = smem_base + kStages * C::STAGE_BYTES;
+  const uint32_t bar_base = smem_store + C::STORE_BYTES;
+  auto full_bar = [&](int s) { return bar_base + 8u * s; };
+  auto empty_bar = [&](int s) { return bar_base + 8u * (kStages + s); };
+  auto tfull_bar = [&](int s) { return bar_base + 8u * (2 * kStages + s); };
+  auto tempty_bar = [&](int s) { return bar_base + 8u * (2 * kStages + kAccStages + s); };
+  const uint32_t tmem_slot = bar_base + 8u * (2 * kStages + 2 * kAccStages);
+  uint8_t* smem_gen = smem_raw + (smem_base - ptx::smem_u32(smem_raw));   // generic pointer to smem_base
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const uint32_t cta_rank = (kCG == 2) ? ptx::cluster_ctarank() : 0u;
+  const bool is_leader = cta_rank == 0;
+
+  if (warp == 0 && lane == 0) {
+    ptx::prefetch_tensormap(&tmap_a);
+    ptx::prefetch_tensormap(&tmap_b);
+    if (kTmaStore) ptx::prefetch_tensormap(&tmap_c);
+  }
+  if (warp == 1 && lane == 0) {
+    for (int s = 0; s < kStages; ++s) {
+      ptx::mbar_init(full_bar(s), 1);                    // one arrive.expect_tx by the (leader's) producer
+      ptx::mbar_init(empty_bar(s), 1);                   // one tcgen05.commit
+    }
+    for (int s = 0; s < kAccStages; ++s) {
+      ptx::mbar_init(tfull_bar(s), 1);                   // one tcgen05.commit
+      ptx::mbar_init(tempty_bar(s), kCG * kNumEpiWarps); // one arrive per epilogue warp of every CTA
+    }
+    ptx::fence_mbar_init();
+  }
+  if (warp == 2) {
+    ptx::tmem_alloc<kCG>(tmem_slot, C::TMEM_COLS);
+    ptx::tmem_relinquish<kCG>();
+  }
+  ptx::tc_fence_before();
+  if (kCG == 2) ptx::cluster_sync(); else __syncthreads();
+  ptx::tc_fence_after();
+  const uint32_t tmem_base = *reinterpret_cast<volatile uint32_t*>(smem_gen + (tmem_slot - smem_base));
+
+  const int num_tiles = p.num_m_blocks * p.num_n_blocks;     // m-blocks of 128*kCG rows
+  const int num_workers = gridDim.x / kCG;
+  const int worker = blockIdx.x / kCG;
+  const int num_kb = p.num_k_blocks;
+
+  // Register budget: 384 threads x 168 at launch; the 4 control warps give theirs back so the
+  // promotion warps can hold 128 fp32 accumulators + two 32-column TMEM staging buffers.
+  // (each role's code must be dominated by its own setmaxnreg, or ptxas budgets it for the minimum)
+  if (warp == 0) {
+    // =========================== TMA producer ===========================
+    ptx::reg_dealloc<56>();
+    if (lane == 0) {
+      const uint64_t pol_a = ptx::policy_evict_normal();
+      const uint64_t pol_b = ptx::policy_evict_normal();
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int tile = worker; tile < num_tiles; tile += num_workers) {
+        int mb, nb;
+        tile_coords(tile, p, mb, nb);
+        const int m0 = mb * (BLOCK_M * kCG) + int(cta_rank) * BLOCK_M;
+        const int n0 = nb * BLOCK_N + int(cta_rank) * C::LOAD_N;
+        for (int kb = 0; kb < num_kb; ++kb) {
+          ptx::mbar_wait(empty_bar(stage), phase ^ 1);
+          const uint32_t sa_addr = smem_base + stage * C::STAGE_BYTES;
+          const uint32_t sb_addr = sa_addr + C::A_BYTES;
+          if constexpr (kCG == 1) {
+            ptx::mbar_arrive_expect_tx(full_bar(stage), C::STAGE_BYTES);
+            ptx::tma_load_2d(&tmap_a, full_bar(stage), sa_addr, kb * BLOCK_K, m0, pol_a);
+            ptx::tma_load_2d(&tmap_b, full_bar(stage), sb_addr, kb * BLOCK_K, n0, pol_b);
+          } else {
+            // both CTAs' bytes are counted on the leader's barrier
+            const uint32_t leader_full = full_bar(stage) & 0xFEFFFFFFu;
+            if (is_leader) ptx::mbar_arrive_expect_tx(full_bar(stage), 2 * C::STAGE_BYTES);
+            ptx::tma_load_2d_pair(&tmap_a, leader_full, sa_addr, kb * BLOCK_K, m0, pol_a);
+            ptx::tma_load_2d_pair(&tmap_b, leader_full, sb_addr, kb * BLOCK_K, n0, pol_b);
+          }
+          if (++stage == kStages) { stage = 0; phase ^= 1; }
+        }
+      }
+    }
+    __syncwarp();
+  } else if (warp == 1) {
+    // =========================== MMA issuer (leader CTA only) ===========================
+    ptx::reg_dealloc<56>();
+    if (is_leader && lane == 0) {
+      constexpr uint32_t idesc = make_idesc(BLOCK_M * kCG, BLOCK_N);
+      int stage = 0, acc = 0;
+      uint32_t phase = 0, acc_phase = 0;
+      for (int tile = worker; tile < num_tiles; tile += num_workers) {
+        for (int kb = 0; kb < num_kb; ++kb) {
+          // accumulator stage drained by every epilogue warp (of both CTAs)?
+          ptx::mbar_wait(tempty_bar(acc), acc_phase ^ 1);
+          ptx::mbar_wait(full_bar(stage), phase);
+          ptx::tc_fence_after();
+          const uint32_t sa_addr = smem_base + stage * C::STAGE_BYTES;
+          const uint64_t da = make_smem_desc(sa_addr);
+          const uint64_t db = make_smem_desc(sa_addr + C::A_BYTES);
+          const uint32_t d_tmem = tmem_base + uint32_t(acc * BLOCK_N);
+#pragma unroll
+          for (int k = 0; k < BLOCK_K / UMMA_K; ++k) {
+            // +32 B along K inside the swizzle atom = +2 in the descriptor's 16-byte address units
+            ptx::mma_f8f6f4<kCG>(d_tmem, da + uint64_t(k * (UMMA_K >> 4)), db + uint64_t(k * (UMMA_K >> 4)), idesc,
+                                 k > 0 ? 1u : 0u);
+          }
+          ptx::tc_commit<kCG>(empty_bar(stage));   // smem stage reusable once these MMAs have read it
+          ptx::tc_commit<kCG>(tfull_bar(acc));     // partial for this K block complete
+          if (++stage == kStages) { stage = 0; phase ^= 1; }
+          if (++acc == kAccStages) { acc = 0; acc_phase ^= 1; }
+        }
+      }
+    }
+    __syncwarp();
+  } else if (warp < 4) {
+    ptx::reg_dealloc<56>();                  // warps 2 (TMEM owner) and 3 (spare) only wait for the end
+  } else {
+    // =========================== promotion + epilogue warps ===========================
+    ptx::reg_alloc<224>();
+    const int ew = warp - 4;
+    const int quarter = warp & 3;            // TMEM lanes this warp may touch: 32*quarter .. +31
+    const int half = ew >> 2;                // which half of the tile's columns
+    const uint32_t lane_base = uint32_t(quarter * 32) << 16;
+    const uint32_t tempty_leader = (kCG == 2) ? ptx::mapa(tempty_bar(0), 0) : tempty_bar(0);
+    const uint32_t my_store = smem_store + ew * (32 * kStoreBoxCols * 2);
+    int acc = 0;
+    uint32_t acc_phase = 0;
+    for (int tile = worker; tile < num_tiles; tile += num_workers) {
+      int mb, nb;
+      tile_coords(tile, p, mb, nb);
+      const int m0 = mb * (BLOCK_M * kCG) + int(cta_rank) * BLOCK_M;
+      const int row = m0 + quarter * 32 + lane;
+      const int col0 = nb * BLOCK_N + half * NC;          // first column this warp owns
+      const bool row_ok = row < p.M;
+      // scale pointers: sa walks kb for this row, sb walks kb for this warp's 128-column block
+      const float* sa_ptr = p.sa + int64_t(row_ok ? row : 0) * p.sa_sm;
+      const int sbc = min(col0 / 128, p.num_sb_cols - 1);
+      const float* sb_ptr = p.sb + int64_t(sbc) * p.sb_sn;
+      // NC <= 128 and col0 % NC == 0, so the warp's columns never straddle a 128-wide scale block
+      float accum[NC];
+#pragma unroll
+      for (int i = 0; i < NC; ++i) accum[i] = 0.0f;
+      float s_next = (row_ok ? __ldg(sa_ptr) : 0.0f) * __ldg(sb_ptr);
+      for (int kb = 0; kb < num_kb; ++kb) {
+        const float s = s_next;
+        if (kb + 1 < num_kb)
+          s_next = (row_ok ? __ldg(sa_ptr + int64_t(kb + 1) * p.sa_sk) : 0.0f) * __ldg(sb_ptr + int64_t(kb + 1) * p.sb_sk);
+        ptx::mbar_wait(tfull_bar(acc), acc_phase);
+        ptx::tc_fence_after();
+        const uint32_t taddr = tmem_base + lane_base + uint32_t(acc * BLOCK_N + half * NC);
+        uint32_t v[2][32];
+        ptx::tmem_ld_32x32(taddr, v[0]);
+        ptx::tmem_ld_wait(v[0]);
+#pragma unroll
+        for (int c = 0; c < NC / 32; ++c) {
+          // double-buffered: fetch chunk c+1 while chunk c is folded into the accumulators
+          if (c + 1 < NC / 32) ptx::tmem_ld_32x32(taddr + uint32_t((c + 1) * 32), v[(c + 1) & 1]);
+#pragma unroll
+          for (int i = 0; i < 32; i += 2)
+            ptx::fma2(accum[c * 32 + i], accum[c * 32 + i + 1], v[c & 1][i], v[c & 1][i + 1], s);
+          if (c + 1 < NC / 32) ptx::tmem_ld_wait(v[(c + 1) & 1]);
+        }
+        // all of this warp's reads of the stage are complete: hand it back to the MMA issuer
+        ptx::tc_fence_before();
+        __syncwarp();
+        if (lane == 0) {
+          if constexpr (kCG == 2) ptx::mbar_arrive_cluster(tempty_leader + 8u * acc);
+          else ptx::mbar_arrive(tempty_bar(acc));
+        }
+        if (++acc == kAccStages) { acc = 0; acc_phase ^= 1; }
+      }
+      // ---------------- write the finished 32 x NC sub-tile ----------------
+      if constexpr (kTmaStore) {
+#pragma unroll
+        for (int cb = 0; cb < NC / kStoreBoxCols; ++cb) {
+          if (col0 + cb * kStoreBoxCols < p.N) {              // warp-uniform
+            // the previous TMA store must have finished reading this warp's staging box
+            if (lane == 0) ptx::tma_store_wait_read<0>();
+            __syncwarp();
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {                     // 8 x 16 B = 64 bf16 of this lane's row
+              const float* a = accum + cb * kStoreBoxCols + j * 8;
+              const uint32_t w0 = pack2<OutT>(a[0], a[1]), w1 = pack2<OutT>(a[2], a[3]);
+              const uint32_t w2 = pack2<OutT>(a[4], a[5]), w3 = pack2<OutT>(a[6], a[7]);
+              const uint32_t dst = my_store + uint32_t(lane * 128 + ((j ^ (lane & 7)) << 4));
+              asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(dst), "r"(w0), "r"(w1), "r"(w2), "r"(w3) : "memory");
+            }
+            ptx::fence_proxy_async_smem();
+            __syncwarp();
+            if (lane == 0) {
+              ptx::tma_store_2d(&tmap_c, my_store, col0 + cb * kStoreBoxCols, m0 + quarter * 32);
+              ptx::tma_store_commit();
+            }
+          }
+        }
+      } else {
+        OutT* crow = reinterpret_cast<OutT*>(p.C) + int64_t(row) * p.ldc;
+        if (row_ok) {
+          const bool vec_ok = (p.ldc % 8 == 0) && ((reinterpret_cast<uintptr_t>(p.C) & 15) == 0);
+#pragma unroll
+          for (int j = 0; j < NC / 8; ++j) {
+            const int col = col0 + j * 8;
+            if (vec_ok && col + 8 <= p.N) {
+              const float* a = accum + j * 8;
+              uint4 w;
+              w.x = pack2<OutT>(a[0], a[1]); w.y = pack2<OutT>(a[2], a[3]);
+              w.z = pack2<OutT>(a[4], a[5]); w.w = pack2<OutT>(a[6], a[7]);
+              *reinterpret_cast<uint4*>(crow + col) = w;
+            } else {
+#pragma unroll
+              for (int i = 0; i < 8; ++i)
+                if (col + i < p.N) {
+                  const uint32_t w = pack2<OutT>(accum[j * 8 + i], 0.0f);
+                  crow[col + i] = *reinterpret_cast<const OutT*>(&w);
+                }
+            }
+          }
+        }
+      }
+    }
+    if (kTmaStore && lane == 0) ptx::tma_store_wait<0>();     // global writes complete before exit
+    __syncwarp();
+  }
+
+  // =========================== teardown ===========================
+  ptx::tc_fence_before();
+  if (kCG == 2) ptx::cluster_sync(); else __syncthreads();
+  if (warp == 2) ptx::tmem_dealloc<kCG>(tmem_base, C::TMEM_COLS);
+}
+
+// --------------------------------------------------------------------------------------------
+// host side
+// --------------------------------------------------------------------------------------------
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn get_encode_fn() {
+  static EncodeTiledFn fn = nullptr;
+  static std::once_flag once;
+  std::call_once(once, [] {
+    void* sym = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &sym, cudaEnableDefault, &qres) == cudaSuccess &&
+        qres == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<EncodeTiledFn>(sym);
+  });
+  return fn;
+}
+
+// 2-D row-major tensor [rows, cols] with `ld` elements between rows; box = [box_rows, box_cols]
+static bool make_tmap_2d(CUtensorMap* m, CUtensorMapDataType dt, int elem_bytes, const void* ptr, uint64_t rows,
+                         uint64_t cols, uint64_t ld, uint32_t box_rows, uint32_t box_cols) {
+  EncodeTiledFn enc = get_encode_fn();
+  if (!enc) return false;
+  const cuuint64_t dims[2] = {cols, rows};
+  const cuuint64_t strides[1] = {ld * uint64_t(elem_bytes)};
+  const cuuint32_t box[2] = {box_cols, box_rows};
+  const cuuint32_t estr[2] = {1, 1};
+  return enc(m, dt, 2, const_cast<void*>(ptr), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+             CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+             CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
+struct Variant {
+  const char* name;
+  int block_n, stages, cg;
+  bool tma_store;
+};
+// index == variant id of the C ABI
+static const Variant kVariants[] = {
+    {"n128_s6_cta1_tma", 128, 6, 1, true},
+    {"n128_s6_cta1_direct", 128, 6, 1, false},
+    {"n256_s4_cta1_tma", 256, 4, 1, true},
+    {"n256_s6_cta2_tma", 256, 6, 2, true},
+    {"n256_s6_cta2_direct", 256, 6, 2, false},
+    {"n128_s8_cta2_tma", 128, 8, 2, true},
+    {"n64_s8_cta1_direct", 64, 8, 1, false},
+};
+constexpr int kNumVariants = int(sizeof(kVariants) / sizeof(kVariants[0]));
+
+template <int BLOCK_N, int kStages, int kCG, typename OutT, bool kTmaStore>
+static int launch_variant(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& tc, const GemmParams& p,
+                          int num_sms, cudaStream_t st) {
+  using C = Cfg<BLOCK_N, kCG>;
+  auto kern = fp8_blockwise_gemm_kernel<BLOCK_N, kStages, kCG, OutT, kTmaStore>;
+  constexpr int smem = C::smem_bytes(kStages);
+  static_assert(smem <= 232448, "shared memory budget");
+  static bool configured = false;   // per instantiation
+  if (!configured) {
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    if (e != cudaSuccess) return int(e);
+    configured = true;
+  }
+  const int tiles = p.num_m_blocks * p.num_n_blocks;
+  int workers = num_sms / kCG;
+  if (workers > tiles) workers = tiles;
+  if (workers < 1) workers = 1;
+  cudaLaunchConfig_t cfg;
+  memset(&cfg, 0, sizeof(cfg));
+  cfg.gridDim = dim3(unsigned(workers * kCG));
+  cfg.blockDim = dim3(kNumThreads);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = kCG;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  return int(cudaLaunchKernelEx(&cfg, kern, ta, tb, tc, p));
+}
+
+template <typename OutT>
+static int launch_by_id(int v, const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& tc,
+                        const GemmParams& p, int num_sms, cudaStream_t st) {
+  switch (v) {
+    case 0: return launch_variant<128, 6, 1, OutT, true>(ta, tb, tc, p, num_sms, st);
+    case 1: return launch_variant<128, 6, 1, OutT, false>(ta, tb, tc, p, num_sms, st);
+    case 2: return launch_variant<256, 4, 1, OutT, true>(ta, tb, tc, p, num_sms, st);
+    case 3: return launch_variant<256, 6, 2, OutT, true>(ta, tb, tc, p, num_sms, st);
+    case 4: return launch_variant<256, 6, 2, OutT, false>(ta, tb, tc, p, num_sms, st);
+    case 5: return launch_variant<128, 8, 2, OutT, true>(ta, tb, tc, p, num_sms, st);
+    case 6: return launch_variant<64, 8, 1, OutT, false>(ta, tb, tc, p, num_sms, st);
+    default: return SGLK_E_VARIANT;
+  }
+}
+
+static bool tma_store_ok(const void* C, int64_t ldc, int out_bytes) {
+  return (reinterpret_cast<uintptr_t>(C) & 15) == 0 && (ldc * out_bytes) % 16 == 0;
+}
+
+static int pick_variant(int64_t M, int64_t N, int64_t K) {
+  (void)K;
+  if (M > 128 && N >= 256 && M * N >= int64_t(148) * 128 * 256) return 3;   // paired 256x256 tiles
+  if (M > 128) return 0;
+  // decode: weight streaming; more, narrower tiles keep every SM pulling on HBM
+  if (N >= 148 * 128) return 0;
+  return 6;
+}
+
+static int gemm_entry(const void* A, const void* B, const float* sa, const float* sb, void* Cout, int64_t M,
+                      int64_t N, int64_t K, int64_t lda, int64_t ldb, int64_t ldc, int64_t sa_sm, int64_t sa_sk,
+                      int64_t sb_sk, int64_t sb_sn, int out_dtype, int variant, int num_sms, void* stream) {
+  if (M < 0 || N < 0 || K < 0) return SGLK_E_SHAPE;
+  if (out_dtype != SGLK_BF16 && out_dtype != SGLK_F16) return SGLK_E_DTYPE;
+  if (M == 0 || N == 0) return SGLK_OK;
+  if (!Cout) return SGLK_E_NULL;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (K == 0) {   // empty sum: C = 0
+    if (ldc == N) return int(cudaMemsetAsync(Cout, 0, size_t(M) * N * 2, st));
+    return int(cudaMemset2DAsync(Cout, size_t(ldc) * 2, 0, size_t(N) * 2, size_t(M), st));
+  }
+  if (!A || !B || !sa || !sb) return SGLK_E_NULL;
+  if (K % 16 != 0 || lda % 16 != 0 || ldb % 16 != 0 || lda < K || ldb < K || ldc < N) return SGLK_E_STRIDE;
+  if ((reinterpret_cast<uintptr_t>(A) & 15) || (reinterpret_cast<uintptr_t>(B) & 15)) return SGLK_E_STRIDE;
+  if (M >= (int64_t(1) << 31) || N >= (int64_t(1) << 31) || K >= (int64_t(1) << 31)) return SGLK_E_SHAPE;
+  if (variant < 0) variant = pick_variant(M, N, K);
+  if (variant >= kNumVariants) return SGLK_E_VARIANT;
+  Variant v = kVariants[variant];
+  if (v.tma_store && !tma_store_ok(Cout, ldc, 2)) {
+    // same tile shape, predicated-store epilogue
+    variant = (v.cg == 2) ? 4 : 1;
+    v = kVariants[variant];
+  }
+  if (num_sms <= 0) num_sms = device_sm_count();
+
+  GemmParams p;
+  p.sa = sa; p.sb = sb; p.C = Cout;
+  p.M = M; p.N = N; p.K = K; p.ldc = ldc;
+  p.sa_sm = sa_sm; p.sa_sk = sa_sk; p.sb_sk = sb_sk; p.sb_sn = sb_sn;
+  p.num_m_blocks = int32_t((M + BLOCK_M * v.cg - 1) / (BLOCK_M * v.cg));
+  p.num_n_blocks = int32_t((N + v.block_n - 1) / v.block_n);
+  p.num_k_blocks = int32_t((K + BLOCK_K - 1) / BLOCK_K);
+  p.num_sb_cols = int32_t((N + 127) / 128);
+  p.group_m = 8;
+
+  CUtensorMap ta, tb, tc;
+  if (!make_tmap_2d(&ta, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, A, uint64_t(M), uint64_t(K), uint64_t(lda), BLOCK_M, BLOCK_K))
+    return SGLK_E_DRIVER;
+  if (!make_tmap_2d(&tb, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, B, uint64_t(N), uint64_t(K), uint64_t(ldb),
+                    uint32_t(v.block_n / v.cg), BLOCK_K))
+    return SGLK_E_DRIVER;
+  if (v.tma_store) {
+    const CUtensorMapDataType cdt = out_dtype == SGLK_BF16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT16;
+    if (!make_tmap_2d(&tc, cdt, 2, Cout, uint64_t(M), uint64_t(N), uint64_t(ldc), 32, kStoreBoxCols)) return SGLK_E_DRIVER;
+  } else {
+    tc = ta;   // unused by the kernel
+  }
+  if (out_dtype == SGLK_BF16) return launch_by_id<__nv_bfloat16>(variant, ta, tb, tc, p, num_sms, st);
+  return launch_by_id<__half>(variant, ta, tb, tc, p, num_sms, st);
+}
+
+}  // namespace sglk
+
+extern "C" int sglk_fp8_blockwise_scaled_mm_ex(const void* A, const void* B, const float* sa, const float* sb, void* C,
+                                               int64_t M, int64_t N, int64_t K, int64_t lda, int64_t ldb, int64_t ldc,
+                                               int64_t sa_stride_m, int64_t sa_stride_k, int64_t sb_stride_k,
+                                               int64_t sb_stride_n, int out_dtype, int variant, int num_sms,
+                                               void* stream) {
+  return sglk::gemm_entry(A, B, sa, sb, C, M, N, K, lda, ldb, ldc, sa_stride_m, sa_stride_k, sb_stride_k,
+                          sb_stride_n, out_dtype, variant, num_sms, stream);
+}
+
+extern "C" int sglk_fp8_blockwise_scaled_mm(const void* A, const void* B, const float* sa, const float* sb, void* C,
+                                            int64_t M, int64_t N, int64_t K, int64_t lda, int64_t ldb, int64_t ldc,
+                                            int64_t sa_stride_m, int64_t sa_stride_k, int64_t sb_stride_k,
+                                            int64_t sb_stride_n, int out_dtype, void* stream) {
+  return sglk::gemm_entry(A, B, sa, sb, C, M, N, K, lda, ldb, ldc, sa_stride_m, sa_stride_k, sb_stride_k,
+                          sb_stride_n, out_dtype, -1, 0, stream);
+}
+
+extern "C" int sglk_gemm_num_variants(void) { return sglk::kNumVariants; }
+extern "C" const char* sglk_gemm_variant_name(int v) {
+  return (v >= 0 && v < sglk::kNumVariants) ? sglk::kVariants[v].name : "";
+}
+extern "C" int sglk_gemm_pick_variant(int64_t M, int64_t N, int64_t K) { return sglk::pick_variant(M, N, K); }

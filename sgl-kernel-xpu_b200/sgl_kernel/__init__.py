@@ -1,0 +1,28 @@
+"""sgl_kernel — B200 (sm_100a) build of the FP8 block-quantized linear hot path.
+
+Drop-in for the four names the reference exports for this path
+(python/sgl_kernel/__init__.py:67,75-78); everything else in the reference is out of scope here.
+Importing the package registers torch.ops.sgl_kernel.{sgl_per_token_group_quant_8bit,
+sgl_per_token_group_quant_8bit_v2, fp8_blockwise_scaled_mm} for dispatch key CUDA.
+"""
+from .gemm import (
+    fp8_blockwise_scaled_mm,
+    sgl_per_token_group_quant_8bit,
+    sgl_per_token_group_quant_fp8,
+    sgl_per_token_group_quant_int8,
+)
+from .linear import Fp8BlockLinear, create_per_token_group_quant_fp8_output_scale, per_token_group_quant_fp8
+from .sharded import ColumnShardedFp8Linear
+
+__version__ = "0.11.0+b200"
+
+__all__ = [
+    "fp8_blockwise_scaled_mm",
+    "sgl_per_token_group_quant_8bit",
+    "sgl_per_token_group_quant_fp8",
+    "sgl_per_token_group_quant_int8",
+    "per_token_group_quant_fp8",
+    "create_per_token_group_quant_fp8_output_scale",
+    "Fp8BlockLinear",
+    "ColumnShardedFp8Linear",
+]

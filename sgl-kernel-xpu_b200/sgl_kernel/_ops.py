@@ -1,0 +1,197 @@
+"""torch.ops.sgl_kernel.* registrations for the FP8 block-quantized linear path (dispatch key CUDA).
+
+Schemas are the reference's, verbatim:
+  sgl_per_token_group_quant_8bit / _v2 : /root/reference/src/torch_extension_sycl.cc:395-402
+  fp8_blockwise_scaled_mm              : derived from include/sgl_kernel_ops.h:581-586 +
+                                         python/sgl_kernel/gemm.py:24-31 (the reference registers none)
+The reference binds dispatch key XPU; this build binds CUDA.  Each impl validates like the reference's
+host launcher (TORCH_CHECK -> RuntimeError before any launch), then calls the C ABI with raw pointers
+and the *current* CUDA stream.  No host sync, no allocation in quant, caching-allocator only in GEMM.
+"""
+from __future__ import annotations
+
+from typing import Optional
+
+import torch
+
+from . import _lib
+
+_IN_DTYPES = {torch.bfloat16: _lib.BF16, torch.float16: _lib.F16, torch.float32: _lib.F32}
+_OUT_DTYPES = {torch.float8_e4m3fn: _lib.E4M3, torch.int8: _lib.INT8}
+_SUPPORTED_GROUPS_V1 = (32, 64, 128, 256, 512)   # per_token_group_quant_8bit.cpp:337-358
+_SUPPORTED_GROUPS_V2 = (16, 32, 64, 128)         # per_token_group_quant_8bit_v2.cpp:829-839
+
+_QUANT_SCHEMA = (
+    "sgl_per_token_group_quant_8bit(Tensor input, Tensor output_q, Tensor output_s, int group_size,"
+    " float eps, float fp8_min, float fp8_max, bool scale_ue8m0) -> ()"
+)
+_QUANT_V2_SCHEMA = (
+    "sgl_per_token_group_quant_8bit_v2(Tensor input, Tensor output_q, Tensor output_s, int group_size,"
+    " float eps, float fp8_min, float fp8_max, bool scale_ue8m0, bool fuse_silu_and_mul, Tensor? masked_m) -> ()"
+)
+_GEMM_SCHEMA = (
+    "fp8_blockwise_scaled_mm(Tensor mat_a, Tensor mat_b, Tensor scales_a, Tensor scales_b,"
+    " ScalarType out_dtype) -> Tensor"
+)
+
+_library = torch.library.Library("sgl_kernel", "FRAGMENT")
+_library.define(_QUANT_SCHEMA)
+_library.define(_QUANT_V2_SCHEMA)
+_library.define(_GEMM_SCHEMA)
+
+
+def _stream_ptr(t: torch.Tensor) -> int:
+    return torch.cuda.current_stream(t.device).cuda_stream
+
+
+def _check(cond: bool, msg: str) -> None:
+    if not cond:
+        raise RuntimeError(msg)
+
+
+def _scale_layout(output_s: torch.Tensor, scale_ue8m0: bool):
+    """What the reference derives from output_s (per_token_group_quant_8bit.cpp:237,259-262,279-335)."""
+    _check(output_s.dim() == 2, "Expected output_s.dim() == 2")
+    col_major = output_s.stride(0) < output_s.stride(1)
+    stride = output_s.stride(1)
+    if scale_ue8m0:
+        if col_major:
+            _check(output_s.dtype == torch.int32, "UE8M0 column-major scales must be packed int32")
+            return _lib.SCALE_UE8M0_COL_PACKED, stride
+        _check(output_s.dtype in (torch.uint8, getattr(torch, "float8_e8m0fnu", torch.uint8)),
+               "UE8M0 row-major scales must be uint8")
+        _check(output_s.is_contiguous(), "UE8M0 row-major scales must be contiguous")
+        return _lib.SCALE_UE8M0_ROW_MAJOR, stride
+    _check(output_s.dtype == torch.float32, "output_s must be float32 unless scale_ue8m0")
+    if col_major:
+        return _lib.SCALE_F32_COL_MAJOR, stride
+    _check(output_s.is_contiguous(), "row-major output_s must be contiguous")
+    return _lib.SCALE_F32_ROW_MAJOR, stride
+
+
+def _quant_common(input, output_q, output_s, group_size, eps, fp8_min, fp8_max, scale_ue8m0, fuse, groups_ok, name):
+    _check(input.is_cuda and output_q.is_cuda and output_s.is_cuda, f"{name}: tensors must be CUDA tensors")
+    _check(input.is_contiguous(), "input must be contiguous")          # CHECK_CONTIGUOUS, Utils.h:13
+    _check(output_q.is_contiguous(), "output_q must be contiguous")
+    _check(input.dtype in _IN_DTYPES,
+           f"{name}: input dtype must be Float16, BFloat16, or Float32, got {input.dtype}")
+    _check(output_q.dtype in _OUT_DTYPES,
+           f"{name}: output_q dtype must be Int8 or Float8_e4m3fn, got {output_q.dtype}")
+    _check(group_size in groups_ok, f"Unsupported group_size: {group_size}. Supported sizes are: {groups_ok}")
+    hidden_in = input.size(-1) if input.dim() > 0 else 1
+    hidden = hidden_in // 2 if fuse else hidden_in
+    _check(not fuse or hidden_in % 2 == 0, "fuse_silu_and_mul needs an even hidden size")
+    _check(hidden % group_size == 0 and input.numel() % group_size == 0,
+           "input.numel() must be divisible by group_size")
+    _check(output_q.numel() == (input.numel() // 2 if fuse else input.numel()),
+           "output_q must have one code per quantised element")
+    layout, stride = _scale_layout(output_s, scale_ue8m0)
+    num_tokens = input.numel() // hidden_in if hidden_in else 0
+    groups_per_row = hidden // group_size
+    if layout in (_lib.SCALE_F32_ROW_MAJOR, _lib.SCALE_UE8M0_ROW_MAJOR):
+        _check(output_s.numel() >= num_tokens * groups_per_row, "output_s too small")
+    else:
+        _check(output_s.size(0) >= num_tokens, "output_s has fewer rows than tokens")
+    if input.numel() == 0:
+        return
+    lib = _lib.load()
+    with torch.cuda.device(input.device):
+        if fuse:
+            rc = lib.sglk_silu_mul_per_token_group_quant_8bit(
+                input.data_ptr(), output_q.data_ptr(), output_s.data_ptr(), num_tokens, hidden, group_size,
+                _IN_DTYPES[input.dtype], _OUT_DTYPES[output_q.dtype], eps, fp8_min, fp8_max,
+                int(scale_ue8m0), layout, stride, _stream_ptr(input))
+        else:
+            rc = lib.sglk_per_token_group_quant_8bit(
+                input.data_ptr(), output_q.data_ptr(), output_s.data_ptr(), num_tokens * groups_per_row,
+                groups_per_row, group_size, _IN_DTYPES[input.dtype], _OUT_DTYPES[output_q.dtype], eps,
+                fp8_min, fp8_max, int(scale_ue8m0), layout, stride, _stream_ptr(input))
+    _lib.check(rc, name)
+
+
+def _quant_v1(input, output_q, output_s, group_size, eps, fp8_min, fp8_max, scale_ue8m0):
+    """at::native::xpu::sgl_per_token_group_quant_8bit, src/sycl/per_token_group_quant_8bit.cpp:222-386."""
+    _quant_common(input, output_q, output_s, group_size, eps, fp8_min, fp8_max, scale_ue8m0, False,
+                  _SUPPORTED_GROUPS_V1 + (16,), "sgl_per_token_group_quant_8bit")
+
+
+def _quant_v2(input, output_q, output_s, group_size, eps, fp8_min, fp8_max, scale_ue8m0,
+              fuse_silu_and_mul, masked_m: Optional[torch.Tensor]):
+    """sgl_per_token_group_quant_8bit_v2, src/sycl/per_token_group_quant_8bit_v2.cpp:714-843.
+    The masked MoE layout (:464-563) is a 'next' row of SURVEY.md §8(f) and is rejected loudly."""
+    _check(masked_m is None, "sgl_per_token_group_quant_8bit_v2: masked_m layout is not implemented in the B200 build")
+    _quant_common(input, output_q, output_s, group_size, eps, fp8_min, fp8_max, scale_ue8m0,
+                  bool(fuse_silu_and_mul), _SUPPORTED_GROUPS_V2 + (256, 512), "sgl_per_token_group_quant_8bit_v2")
+
+
+_GEMM_OUT = {torch.bfloat16: _lib.BF16, torch.float16: _lib.F16}
+
+
+def _gemm_checks(mat_a, mat_b, scales_a, scales_b, out_dtype):
+    _check(mat_a.dim() == 2 and mat_b.dim() == 2, "mat_a and mat_b must be 2-D")
+    _check(mat_a.size(1) == mat_b.size(0), "mat_a and mat_b shapes cannot be multiplied")
+    _check(mat_a.dtype == torch.float8_e4m3fn and mat_b.dtype == torch.float8_e4m3fn,
+           "mat_a and mat_b must be Float8_e4m3fn")
+    _check(scales_a.dtype == torch.float32 and scales_b.dtype == torch.float32, "scales must be Float32")
+    _check(out_dtype in _GEMM_OUT, "out_dtype must be Half or BFloat16")
+    M, K = mat_a.shape
+    N = mat_b.size(1)
+    _check(K == 0 or mat_a.stride(1) == 1 or M == 0, "mat_a must be a row major tensor")
+    _check(K == 0 or mat_b.stride(0) == 1 or N == 0, "mat_b must be a column major tensor")
+    _check(K % 16 == 0, "mat_a.size(1) must be a multiple of 16 (TMA row pitch)")
+    kb, nb = -(K // -128), -(N // -128)
+    _check(scales_a.dim() == 2 and tuple(scales_a.shape) == (M, kb), f"scales_a must be [M, ceil(K/128)] = [{M}, {kb}]")
+    _check(scales_b.dim() == 2 and tuple(scales_b.shape) == (kb, nb),
+           f"scales_b must be [ceil(K/128), ceil(N/128)] = [{kb}, {nb}]")
+    return M, N, K
+
+
+def _gemm(mat_a, mat_b, scales_a, scales_b, out_dtype, variant: int = -1, num_sms: int = 0):
+    """fp8_blockwise_scaled_mm, include/sgl_kernel_ops.h:581-586 (allocates and returns C)."""
+    _check(mat_a.is_cuda and mat_b.is_cuda and scales_a.is_cuda and scales_b.is_cuda,
+           "fp8_blockwise_scaled_mm: tensors must be CUDA tensors")
+    M, N, K = _gemm_checks(mat_a, mat_b, scales_a, scales_b, out_dtype)
+    out = torch.empty((M, N), dtype=out_dtype, device=mat_a.device)
+    if M == 0 or N == 0:
+        return out
+    lda = mat_a.stride(0) if M > 1 else max(K, 16)
+    ldb = mat_b.stride(1) if N > 1 else max(K, 16)
+    _check(lda % 16 == 0 and ldb % 16 == 0 and mat_a.data_ptr() % 16 == 0 and mat_b.data_ptr() % 16 == 0,
+           "mat_a / mat_b rows must be 16-byte aligned")
+    lib = _lib.load()
+    with torch.cuda.device(mat_a.device):
+        rc = lib.sglk_fp8_blockwise_scaled_mm_ex(
+            mat_a.data_ptr(), mat_b.data_ptr(), scales_a.data_ptr(), scales_b.data_ptr(), out.data_ptr(),
+            M, N, K, lda, ldb, out.stride(0), scales_a.stride(0), scales_a.stride(1), scales_b.stride(0),
+            scales_b.stride(1), _GEMM_OUT[out_dtype], variant, num_sms, _stream_ptr(mat_a))
+    _lib.check(rc, "fp8_blockwise_scaled_mm")
+    return out
+
+
+def _gemm_op(mat_a, mat_b, scales_a, scales_b, out_dtype):
+    return _gemm(mat_a, mat_b, scales_a, scales_b, out_dtype)
+
+
+_library.impl("sgl_per_token_group_quant_8bit", _quant_v1, "CUDA")
+_library.impl("sgl_per_token_group_quant_8bit_v2", _quant_v2, "CUDA")
+_library.impl("fp8_blockwise_scaled_mm", _gemm_op, "CUDA")
+
+
+# Fake (meta) kernels so the ops trace under torch.compile / FakeTensor, as the reference README asks of
+# every op (README.md:84-85).
+def _quant_fake(input, output_q, output_s, group_size, eps, fp8_min, fp8_max, scale_ue8m0):
+    return None
+
+
+def _quant_v2_fake(input, output_q, output_s, group_size, eps, fp8_min, fp8_max, scale_ue8m0,
+                   fuse_silu_and_mul, masked_m):
+    return None
+
+
+def _gemm_fake(mat_a, mat_b, scales_a, scales_b, out_dtype):
+    return torch.empty((mat_a.size(0), mat_b.size(1)), dtype=out_dtype, device=mat_a.device)
+
+
+_library.impl("sgl_per_token_group_quant_8bit", _quant_fake, "Meta")
+_library.impl("sgl_per_token_group_quant_8bit_v2", _quant_v2_fake, "Meta")
+_library.impl("fp8_blockwise_scaled_mm", _gemm_fake, "Meta")

@@ -1,0 +1,116 @@
+"""Host-side callers of the two ops: the allocation helpers every caller of the reference writes around
+`sgl_per_token_group_quant_8bit` (tests/test_per_token_group_quant_8bit.py:86-164 — the same helper
+lives in SGLang's fp8_kernel.py), and the FP8 block-quantized linear layer that chains quant -> GEMM.
+Device memory, streams and allocation are PyTorch's; all arithmetic is in libsglk_sm100a.so.
+"""
+from __future__ import annotations
+
+from typing import Optional, Tuple
+
+import torch
+
+from .gemm import fp8_blockwise_scaled_mm, sgl_per_token_group_quant_8bit
+
+FP8_MAX = 448.0  # torch.finfo(torch.float8_e4m3fn).max
+
+
+def _ceil_align(x: int, a: int) -> int:
+    return (x + a - 1) // a * a
+
+
+def create_per_token_group_quant_fp8_output_scale(
+    x_shape,
+    device,
+    group_size: int,
+    column_major_scales: bool,
+    scale_tma_aligned: bool,
+    scale_ue8m0: bool,
+) -> torch.Tensor:
+    """The four scale layouts of the reference's `create_fp8_output_scale`
+    (tests/test_per_token_group_quant_8bit.py:86-126): row-major fp32; column-major fp32;
+    column-major fp32 with rows padded to 4 ("TMA aligned"); UE8M0 packed int32, column-major."""
+    if scale_ue8m0:
+        assert column_major_scales and scale_tma_aligned
+        *x_batch, x_q_mn, x_q_k = x_shape
+        x_s_mn, x_s_k = x_q_mn, x_q_k // 128
+        aligned_mn = _ceil_align(x_s_mn, 4)
+        aligned_k = _ceil_align(x_s_k, 4)
+        return torch.empty((*x_batch, aligned_k // 4, aligned_mn), device=device, dtype=torch.int).transpose(-1, -2)[
+            ..., :x_s_mn, :
+        ]
+    if column_major_scales:
+        if scale_tma_aligned:
+            aligned_size = _ceil_align(x_shape[-2], 4)
+            return torch.empty(
+                tuple(x_shape[:-2]) + (x_shape[-1] // group_size, aligned_size), device=device, dtype=torch.float32
+            ).transpose(-1, -2)[: x_shape[-2], :]
+        return torch.empty(
+            (x_shape[-1] // group_size,) + tuple(x_shape[:-1]), device=device, dtype=torch.float32
+        ).permute(-1, -2)
+    return torch.empty(tuple(x_shape[:-1]) + (x_shape[-1] // group_size,), device=device, dtype=torch.float32)
+
+
+def per_token_group_quant_fp8(
+    x: torch.Tensor,
+    group_size: int = 128,
+    eps: float = 1e-10,
+    column_major_scales: bool = False,
+    scale_tma_aligned: bool = False,
+    scale_ue8m0: bool = False,
+    fuse_silu_and_mul: bool = False,
+    masked_m: Optional[torch.Tensor] = None,
+    enable_v2: Optional[bool] = None,
+    dtype: torch.dtype = torch.float8_e4m3fn,
+) -> Tuple[torch.Tensor, torch.Tensor]:
+    """Allocate outputs and quantise — `sglapi_per_token_group_quant_fp8`,
+    tests/test_per_token_group_quant_8bit.py:129-164."""
+    assert x.shape[-1] % group_size == 0, "the last dimension of `x` cannot be divisible by `group_size`"
+    assert x.is_contiguous(), "`x` is not contiguous"
+    out_shape = (*x.shape[:-1], x.shape[-1] // (2 if fuse_silu_and_mul else 1))
+    x_q = torch.empty(out_shape, device=x.device, dtype=dtype)
+    x_s = create_per_token_group_quant_fp8_output_scale(
+        out_shape, x.device, group_size, column_major_scales, scale_tma_aligned, scale_ue8m0
+    )
+    if dtype == torch.int8:
+        qmin, qmax = -128.0, 127.0
+    else:
+        qmax = torch.finfo(dtype).max
+        qmin = -qmax
+    if x.shape[0] > 0:
+        if fuse_silu_and_mul and enable_v2 is None:
+            enable_v2 = True
+        sgl_per_token_group_quant_8bit(
+            x, x_q, x_s, group_size, eps, qmin, qmax, scale_ue8m0, fuse_silu_and_mul, masked_m, enable_v2
+        )
+    return x_q, x_s
+
+
+class Fp8BlockLinear:
+    """y = x @ W^T with W stored as e4m3 codes [N, K] and one fp32 scale per 128x128 block
+    [ceil(N/128), ceil(K/128)] — the layer SGLang builds on the two ops.  `forward` quantises the bf16
+    activations per 1x128 group (column-major scales, the layout the GEMM reads coalesced) and calls
+    the blockwise GEMM.  Weights stay resident in HBM; nothing is re-laid-out per call."""
+
+    def __init__(self, weight_q: torch.Tensor, weight_scale: torch.Tensor, out_dtype: torch.dtype = torch.bfloat16):
+        assert weight_q.dtype == torch.float8_e4m3fn and weight_q.dim() == 2 and weight_q.is_contiguous()
+        n, k = weight_q.shape
+        assert tuple(weight_scale.shape) == (-(n // -128), -(k // -128)), "weight_scale must be [N/128, K/128]"
+        self.weight_q = weight_q
+        self.weight_scale = weight_scale.contiguous()
+        self.out_dtype = out_dtype
+        self.out_features, self.in_features = n, k
+
+    def quantize_input(self, x: torch.Tensor) -> Tuple[torch.Tensor, torch.Tensor]:
+        return per_token_group_quant_fp8(x, 128, column_major_scales=True, enable_v2=False)
+
+    def forward_quantized(self, x_q: torch.Tensor, x_s: torch.Tensor) -> torch.Tensor:
+        # mat_b = [K, N] column-major view of the [N, K] codes; scales_b = [K/128, N/128] view
+        return fp8_blockwise_scaled_mm(x_q, self.weight_q.t(), x_s, self.weight_scale.t(), self.out_dtype)
+
+    def forward(self, x: torch.Tensor) -> torch.Tensor:
+        lead = x.shape[:-1]
+        x2 = x.reshape(-1, x.shape[-1])
+        x_q, x_s = self.quantize_input(x2)
+        return self.forward_quantized(x_q, x_s).reshape(*lead, self.out_features)
+
+    __call__ = forward

@@ -1,0 +1,75 @@
+"""Column-(N-)sharded FP8 block linear over the GPUs of one NVSwitch box.
+
+One process per GPU.  Rank r owns weight rows [r*N/g, (r+1)*N/g) — a multiple of 128, so no 128x128
+scale block straddles ranks — and the matching rows of the weight-scale matrix.  Activations are
+replicated and quantised on every rank (cheap, HBM-bound); each rank's GEMM produces its [M, N/g]
+column panel with no reduction.  Only when the consumer needs the full [M, N] is one all-gather issued
+(NCCL over NVLink; gloo in the CPU tests).  The reference has no communication layer at all
+(SURVEY.md §2), so there is no reference file to cite for this part; the partitioning follows
+BASELINE.json's north_star.
+"""
+from __future__ import annotations
+
+from typing import Optional, Tuple
+
+import torch
+import torch.distributed as dist
+
+
+def shard_bounds(n: int, world: int, rank: int, block: int = 128) -> Tuple[int, int]:
+    """Rows [lo, hi) of the [N, K] weight owned by `rank`: whole 128-row blocks, spread as evenly as
+    possible (earlier ranks take the remainder); the last block may be ragged (N % 128 != 0)."""
+    blocks = -(n // -block)
+    base, rem = divmod(blocks, world)
+    lo_b = rank * base + min(rank, rem)
+    hi_b = lo_b + base + (1 if rank < rem else 0)
+    return min(lo_b * block, n), min(hi_b * block, n)
+
+
+def shard_weight(weight_q: torch.Tensor, weight_scale: torch.Tensor, world: int, rank: int):
+    """Slice a full [N,K] code matrix and its [N/128,K/128] scales down to this rank's panel."""
+    lo, hi = shard_bounds(weight_q.shape[0], world, rank)
+    return weight_q[lo:hi].contiguous(), weight_scale[lo // 128 : -(hi // -128)].contiguous()
+
+
+class ColumnShardedFp8Linear:
+    def __init__(self, local_linear, n_total: int, group: Optional[dist.ProcessGroup] = None):
+        self.local = local_linear
+        self.group = group
+        self.world = dist.get_world_size(group) if dist.is_initialized() else 1
+        self.rank = dist.get_rank(group) if dist.is_initialized() else 0
+        self.n_total = n_total
+        self.bounds = [shard_bounds(n_total, self.world, r) for r in range(self.world)]
+        assert self.bounds[self.rank][1] - self.bounds[self.rank][0] == local_linear.out_features
+
+    def forward_local(self, x: torch.Tensor) -> torch.Tensor:
+        return self.local(x)
+
+    def gather(self, y_local: torch.Tensor, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+        """All-gather the column panels into [M, N]: one all_gather_into_tensor (rank-major
+        [g, M, N/g]) and one strided copy into the column-major-of-panels [M, N] result."""
+        if self.world == 1:
+            return y_local
+        m = y_local.shape[0]
+        widths = [hi - lo for lo, hi in self.bounds]
+        if out is None:
+            out = torch.empty((m, self.n_total), dtype=y_local.dtype, device=y_local.device)
+        wmax = max(widths)
+        staged = torch.empty((self.world * m, wmax), dtype=y_local.dtype, device=y_local.device)
+        if len(set(widths)) == 1:
+            dist.all_gather_into_tensor(staged, y_local.contiguous(), group=self.group)
+            out.view(m, self.world, wmax).copy_(staged.view(self.world, m, wmax).permute(1, 0, 2))
+        else:
+            # ragged last panel (N % (128*g) != 0): pad to the widest panel, gather, slice
+            mine = torch.zeros((m, wmax), dtype=y_local.dtype, device=y_local.device)
+            mine[:, : y_local.shape[1]] = y_local
+            dist.all_gather_into_tensor(staged, mine, group=self.group)
+            for r, (lo, hi) in enumerate(self.bounds):
+                out[:, lo:hi] = staged[r * m : (r + 1) * m, : hi - lo]
+        return out
+
+    def forward(self, x: torch.Tensor, gather_output: bool = True) -> torch.Tensor:
+        y = self.forward_local(x)
+        return self.gather(y) if gather_output else y
+
+    __call__ = forward

@@ -1,0 +1,183 @@
+"""GPU parity tests for fp8_blockwise_scaled_mm (torch.ops -> C ABI -> tcgen05 kernel).
+Bar (BASELINE.json): relative error <= 1e-2 and cosine >= 0.9999 against the fp32 dequantised matmul
+of the CPU oracle, for bf16 and fp16 outputs; plus the reference test's own
+assert_close(rtol=0.02, atol=1) (tests/test_fp8_blockwise_gemm.py:83-85)."""
+import pytest
+import torch
+
+from conftest import from_bits
+from oracle import torch_oracle as O
+
+import sgl_kernel
+from sgl_kernel import _lib, _ops
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda"
+REL_TOL, COS_TOL = 1e-2, 0.9999
+
+
+def n_variants():
+    return _lib.load().sglk_gemm_num_variants()
+
+
+def gpu_mm(a, b, sa, sb, odt, variant=-1):
+    out = _ops._gemm(a.to(DEV), b.t().contiguous().to(DEV).t(), sa.t().contiguous().to(DEV).t() if sa.shape[0] > 0 else sa.to(DEV),
+                     sb.t().contiguous().to(DEV).t(), odt, variant)
+    torch.cuda.synchronize()
+    return out.cpu()
+
+
+def check(out, ref, ref_assert_close=True):
+    assert out.shape == ref.shape and out.dtype == ref.dtype
+    assert torch.isfinite(out.float()).all()
+    r, c = O.rel_err(out, ref), O.cosine(out, ref)
+    assert r <= REL_TOL and c >= COS_TOL, f"rel_err={r:.3e} cosine={c:.6f}"
+    if ref_assert_close:
+        torch.testing.assert_close(out, ref, rtol=0.02, atol=1)
+
+
+GOLDEN = ["mm_1x128x512_bf16", "mm_3x256x512_f16", "mm_5x512x1024_bf16", "mm_127x128x512_bf16",
+          "mm_128x256x1024_f16", "mm_130x384x256_bf16"]
+
+
+@pytest.mark.parametrize("name", GOLDEN)
+def test_golden(gemm_golden, name):
+    a = from_bits(gemm_golden[name + ".a"], torch.float8_e4m3fn)
+    bt = from_bits(gemm_golden[name + ".bt"], torch.float8_e4m3fn)
+    sa = torch.from_numpy(gemm_golden[name + ".sa"])
+    sb = torch.from_numpy(gemm_golden[name + ".sb"])
+    odt = torch.bfloat16 if name.endswith("bf16") else torch.float16
+    out = gpu_mm(a, bt.t(), sa, sb, odt)
+    check(out, from_bits(gemm_golden[name + ".o"], odt))
+
+
+SHAPES = [(1, 128, 512), (5, 512, 1024), (127, 256, 512), (128, 128, 7168), (129, 384, 1024), (300, 640, 2048),
+          (512, 2112, 1024), (1024, 1024, 512), (64, 4096, 128)]
+
+
+@pytest.mark.parametrize("variant", range(7))
+@pytest.mark.parametrize("M,N,K", SHAPES)
+def test_every_variant(variant, M, N, K):
+    if variant >= n_variants():
+        pytest.skip("variant not compiled")
+    a, b, sa, sb = O.make_gemm_inputs(M, N, K, seed=M + N + K)
+    odt = torch.bfloat16 if (M + variant) % 2 == 0 else torch.float16
+    ref = O.baseline_scaled_mm(a, b, sa, sb, odt)
+    check(gpu_mm(a, b, sa, sb, odt, variant), ref)
+
+
+# a diagonal slice of the reference grid (tests/test_fp8_blockwise_gemm.py:88-91): every M, N and K
+# value of the grid appears; the full 576-case product is bounded by CPU-oracle time, not by the kernel
+REF_GRID = [(1, 128, 512), (3, 512, 1024), (5, 1024, 4096), (127, 4096, 8192), (128, 8192, 14080), (512, 14080, 16384),
+            (1024, 128, 16384), (4096, 512, 512), (1, 14080, 1024), (3, 8192, 512), (5, 4096, 16384), (127, 1024, 14080),
+            (128, 512, 8192), (512, 128, 4096), (1024, 14080, 512), (4096, 8192, 1024), (4096, 128, 8192), (1024, 4096, 4096)]
+
+
+@pytest.mark.parametrize("M,N,K", REF_GRID)
+@pytest.mark.parametrize("odt", [torch.bfloat16, torch.float16])
+def test_reference_grid_slice(M, N, K, odt):
+    a, b, sa, sb = O.make_gemm_inputs(M, N, K, seed=0)
+    rows = None if M * N * K <= (1 << 33) else torch.arange(0, M, M // 128)
+    out = gpu_mm(a, b, sa, sb, odt)
+    if rows is not None:
+        ref = O.baseline_scaled_mm(a[rows], b, sa[rows], sb, odt)
+        out = out[rows]
+    else:
+        ref = O.baseline_scaled_mm(a, b, sa, sb, odt)
+    check(out, ref)
+
+
+def test_quant_then_gemm_chain_config1():
+    """BASELINE.json config 1: M=128 N=4096 K=7168 group 128, the realistic chain, GPU vs CPU oracle.
+    Quant is bit-exact, so both GEMMs see identical codes and scales."""
+    x, wq_t, ws_t = O.make_linear_inputs(128, 4096, 7168, seed=42)
+    ref = O.fp8_linear_ref(x, wq_t, ws_t)
+    layer = sgl_kernel.Fp8BlockLinear(wq_t.t().contiguous().to(DEV), ws_t.t().contiguous().to(DEV))
+    out = layer(x.to(DEV))
+    torch.cuda.synchronize()
+    check(out.cpu(), ref, ref_assert_close=False)
+    torch.testing.assert_close(out.cpu().float(), ref.float(), rtol=0.02, atol=0.05)
+
+
+def test_chain_golden(gemm_golden):
+    x = from_bits(gemm_golden["chain_8x256x512.x"], torch.bfloat16)
+    wq = from_bits(gemm_golden["chain_8x256x512.wq"], torch.float8_e4m3fn)
+    ws = torch.from_numpy(gemm_golden["chain_8x256x512.ws"])
+    layer = sgl_kernel.Fp8BlockLinear(wq.to(DEV), ws.to(DEV))
+    out = layer(x.to(DEV)).cpu()
+    check(out, from_bits(gemm_golden["chain_8x256x512.o"], torch.bfloat16), ref_assert_close=False)
+
+
+def test_row_major_activation_scales():
+    """scales_a straight from the quant op's default (row-major) layout is accepted too."""
+    a, b, sa, sb = O.make_gemm_inputs(200, 512, 1024, seed=3)
+    ref = O.baseline_scaled_mm(a, b, sa, sb, torch.bfloat16)
+    out = _ops._gemm(a.to(DEV), b.t().contiguous().to(DEV).t(), sa.contiguous().to(DEV),
+                     sb.contiguous().to(DEV), torch.bfloat16)
+    check(out.cpu(), ref)
+
+
+BIG = [("llama3_70b_gate_up", 8192, 28672, 8192), ("dsv3_mlp", 16384, 18432, 7168), ("dsv3_decode_wide", 256, 24576, 7168),
+       ("dsv3_decode_ragged", 256, 2112, 7168), ("dsv3_decode_m1", 1, 24576, 7168)]
+
+
+@pytest.mark.parametrize("name,M,N,K", BIG)
+def test_baseline_full_sizes(name, M, N, K):
+    """BASELINE.json configs 3-5 at full size: 96 strided rows against the CPU oracle, plus
+    size-independent properties — determinism and exact linearity in a power-of-two scale."""
+    g = torch.Generator().manual_seed(1)
+    a = (torch.rand(M, K, generator=g) - 0.5).mul_(2 * 448).to(torch.float8_e4m3fn)
+    bt = (torch.rand(N, K, generator=g) - 0.5).mul_(2 * 448).to(torch.float8_e4m3fn)
+    sa = (torch.randn(M, K // 128, generator=g) * 1e-3)
+    sb = (torch.randn(K // 128, -(N // -128), generator=g) * 1e-3)
+    ad, bd = a.to(DEV), bt.to(DEV).t()
+    sad, sbd = sa.t().contiguous().to(DEV).t(), sb.to(DEV)
+    out = sgl_kernel.fp8_blockwise_scaled_mm(ad, bd, sad, sbd, torch.bfloat16)
+    out2 = sgl_kernel.fp8_blockwise_scaled_mm(ad, bd, sad, sbd, torch.bfloat16)
+    out4 = sgl_kernel.fp8_blockwise_scaled_mm(ad, bd, (sad * 4.0).t().contiguous().t(), sbd, torch.bfloat16)
+    torch.cuda.synchronize()
+    assert torch.equal(out, out2), "non-deterministic"
+    assert torch.equal(out4.float(), out.float() * 4.0), "not linear in a power-of-two scale"
+    rows = torch.unique(torch.cat([torch.arange(0, M, max(1, M // 96)), torch.tensor([M - 1])]))
+    ref = O.baseline_scaled_mm(a[rows], bt.t(), sa[rows], sb, torch.bfloat16)
+    check(out[rows.to(DEV)].cpu(), ref)
+
+
+def test_empty_and_degenerate():
+    a, b, sa, sb = O.make_gemm_inputs(0, 256, 512, seed=0)
+    out = sgl_kernel.fp8_blockwise_scaled_mm(a.to(DEV), b.t().contiguous().to(DEV).t(), sa.to(DEV), sb.to(DEV), torch.bfloat16)
+    assert out.shape == (0, 256)
+
+
+def test_error_behaviour():
+    a, b, sa, sb = O.make_gemm_inputs(8, 256, 512, seed=0)
+    ad, bd = a.to(DEV), b.t().contiguous().to(DEV).t()
+    sad, sbd = sa.to(DEV), sb.to(DEV)
+    f = sgl_kernel.fp8_blockwise_scaled_mm
+    with pytest.raises(RuntimeError, match="column major"):
+        f(ad, bd.contiguous(), sad, sbd, torch.bfloat16)
+    with pytest.raises(RuntimeError, match="row major"):
+        f(ad.t().contiguous().t(), bd, sad, sbd, torch.bfloat16)
+    with pytest.raises(RuntimeError, match="Float8"):
+        f(ad.view(torch.uint8), bd, sad, sbd, torch.bfloat16)
+    with pytest.raises(RuntimeError, match="out_dtype"):
+        f(ad, bd, sad, sbd, torch.float32)
+    with pytest.raises(RuntimeError, match="scales_a"):
+        f(ad, bd, sad[:, :1], sbd, torch.bfloat16)
+    with pytest.raises(RuntimeError, match="cannot be multiplied"):
+        f(ad[:, :256], bd, sad, sbd, torch.bfloat16)
+
+
+def test_cuda_graph_capture():
+    a, b, sa, sb = O.make_gemm_inputs(64, 512, 1024, seed=7)
+    ad, bd = a.to(DEV), b.t().contiguous().to(DEV).t()
+    sad, sbd = sa.t().contiguous().to(DEV).t(), sb.to(DEV)
+    sgl_kernel.fp8_blockwise_scaled_mm(ad, bd, sad, sbd, torch.bfloat16)   # warm-up (sets func attributes)
+    g = torch.cuda.CUDAGraph()
+    st = torch.cuda.Stream()
+    with torch.cuda.stream(st):
+        with torch.cuda.graph(g, stream=st):
+            out = sgl_kernel.fp8_blockwise_scaled_mm(ad, bd, sad, sbd, torch.bfloat16)
+    g.replay()
+    torch.cuda.synchronize()
+    check(out.cpu(), O.baseline_scaled_mm(a, b, sa, sb, torch.bfloat16))

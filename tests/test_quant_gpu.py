@@ -1,0 +1,258 @@
+"""GPU parity tests for sgl_per_token_group_quant_8bit (through torch.ops -> C ABI -> CUDA kernel).
+Bar: BIT-EXACT codes and scales against the CPU oracle (BASELINE.json), on the shapes, seeds and
+distributions of the reference's tests/test_per_token_group_quant_8bit.py, on the committed golden
+vectors, and at BASELINE's full sizes through row-sampled exactness."""
+import numpy as np
+import pytest
+import torch
+
+from conftest import from_bits
+from oracle import torch_oracle as O
+
+import sgl_kernel
+from sgl_kernel import _lib
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda"
+EPS = 1e-10
+
+
+def run_quant(x_cpu, group, dst=torch.float8_e4m3fn, column_major=False, tma_aligned=False, ue8m0=False, **kw):
+    x = x_cpu.to(DEV)
+    q, s = sgl_kernel.per_token_group_quant_fp8(x, group, EPS, column_major, tma_aligned, ue8m0, dtype=dst,
+                                                enable_v2=kw.pop("enable_v2", False), **kw)
+    torch.cuda.synchronize()
+    return q.cpu(), s.cpu()
+
+
+def assert_bits_equal(q, s, q_ref, s_ref):
+    assert q.shape == q_ref.shape and q.dtype == q_ref.dtype
+    qa, qb = q.view(torch.uint8), q_ref.view(torch.uint8)
+    nbad = int((qa != qb).sum())
+    assert nbad == 0, f"{nbad} / {qa.numel()} codes differ"
+    sa, sb = s.contiguous().view(torch.int32), s_ref.contiguous().view(torch.int32)
+    nbad = int((sa != sb).sum())
+    assert nbad == 0, f"{nbad} / {sa.numel()} scales differ"
+
+
+# ---- golden vectors produced by the reference's own python -----------------------------------
+GOLDEN_FP8 = [("fp8_bf16_128x1024_g128", 128, torch.bfloat16), ("fp8_bf16_64x512_g64", 64, torch.bfloat16),
+              ("fp8_bf16_5x7168_g128", 128, torch.bfloat16), ("fp8_bf16_40x2048_g128", 128, torch.bfloat16),
+              ("fp8_bf16_32x256_g32", 32, torch.bfloat16), ("fp8_bf16_3x1024_g256", 256, torch.bfloat16),
+              ("fp8_bf16_2x1024_g512", 512, torch.bfloat16), ("fp8_f16_128x1024_g128", 128, torch.float16),
+              ("fp8_f32_64x512_g64", 64, torch.float32), ("fp8_bf16_64x512_g64_small", 64, torch.bfloat16),
+              ("fp8_bf16_64x512_g64_large", 64, torch.bfloat16), ("fp8_bf16_edge_8x512_g128", 128, torch.bfloat16)]
+
+
+@pytest.mark.parametrize("name,group,sdt", GOLDEN_FP8)
+@pytest.mark.parametrize("column_major,aligned", [(False, False), (True, False), (True, True)])
+def test_golden_fp8(quant_golden, name, group, sdt, column_major, aligned):
+    x = from_bits(quant_golden[name + ".x"], sdt)
+    q, s = run_quant(x, group, column_major=column_major, tma_aligned=aligned)
+    assert_bits_equal(q, s, from_bits(quant_golden[name + ".q"], torch.float8_e4m3fn),
+                      torch.from_numpy(quant_golden[name + ".s"]))
+
+
+@pytest.mark.parametrize("name,group,sdt", [("int8_bf16_128x1024_g128", 128, torch.bfloat16),
+                                            ("int8_f16_128x1024_g128", 128, torch.float16),
+                                            ("int8_bf16_16x4096_g64", 64, torch.bfloat16)])
+def test_golden_int8(quant_golden, name, group, sdt):
+    x = from_bits(quant_golden[name + ".x"], sdt)
+    q, s = run_quant(x, group, dst=torch.int8)
+    assert_bits_equal(q, s, torch.from_numpy(quant_golden[name + ".q"].view(np.int8)),
+                      torch.from_numpy(quant_golden[name + ".s"]))
+
+
+@pytest.mark.parametrize("name,group", [("ue8m0_128x1024_g128", 128), ("ue8m0_5x2048_g128", 128), ("ue8m0_32x256_g32", 32)])
+def test_golden_ue8m0_row_major_bytes(quant_golden, name, group):
+    """tests/test_per_token_group_quant_8bit.py:357-417 — exact byte compare of UE8M0 scales."""
+    x = from_bits(quant_golden[name + ".x"], torch.bfloat16).to(DEV)
+    m, k = x.shape
+    x_s = torch.empty((m, k // group), device=DEV, dtype=torch.uint8)
+    x_q = torch.empty((m, k), device=DEV, dtype=torch.float8_e4m3fn)
+    torch.ops.sgl_kernel.sgl_per_token_group_quant_8bit.default(x, x_q, x_s, group, EPS, -448.0, 448.0, True)
+    assert np.array_equal(x_s.cpu().numpy(), quant_golden[name + ".sbyte"])
+    assert np.array_equal(x_q.cpu().view(torch.uint8).numpy(), quant_golden[name + ".q"])
+
+
+def test_ue8m0_packed_column_major(quant_golden):
+    name = "ue8m0_128x1024_g128"
+    x = from_bits(quant_golden[name + ".x"], torch.bfloat16)
+    q, s = run_quant(x, 128, column_major=True, tma_aligned=True, ue8m0=True)
+    assert s.dtype == torch.int32 and s.shape == (128, 2)
+    b = s.contiguous().view(torch.uint8).view(128, 2, 4).reshape(128, 8)   # little-endian: byte j = group 4*w+j
+    assert np.array_equal(b.numpy(), quant_golden[name + ".sbyte"])
+    assert np.array_equal(q.view(torch.uint8).numpy(), quant_golden[name + ".q"])
+
+
+# ---- the reference's parametrisation (tests/test_per_token_group_quant_8bit.py:278-315), seed 42 ----
+REF_CASES = [
+    (128, 1024, 128, torch.float8_e4m3fn, torch.bfloat16, False),
+    (128, 1024, 128, torch.int8, torch.bfloat16, False),
+    (64, 512, 64, torch.float8_e4m3fn, torch.bfloat16, False),
+    (128, 2048, 128, torch.float8_e4m3fn, torch.bfloat16, False),
+    (256, 4096, 64, torch.int8, torch.bfloat16, False),
+    (128, 1024, 128, torch.float8_e4m3fn, torch.bfloat16, True),
+    (128, 1024, 128, torch.float8_e4m3fn, torch.float16, False),
+    (128, 1024, 128, torch.int8, torch.float16, False),
+    (64, 512, 64, torch.float8_e4m3fn, torch.float16, False),
+    (128, 1024, 128, torch.float8_e4m3fn, torch.float32, False),
+    (128, 1024, 128, torch.int8, torch.float32, False),
+    (64, 512, 64, torch.float8_e4m3fn, torch.float32, False),
+    (5120, 7168, 128, torch.float8_e4m3fn, torch.bfloat16, False),
+    (5120, 1536, 128, torch.float8_e4m3fn, torch.bfloat16, False),
+    (5120, 512, 128, torch.float8_e4m3fn, torch.bfloat16, False),
+    (5120, 16384, 128, torch.float8_e4m3fn, torch.bfloat16, False),
+    (5120, 18432, 128, torch.float8_e4m3fn, torch.bfloat16, False),
+    (5120, 2048, 128, torch.float8_e4m3fn, torch.bfloat16, False),
+    (40960, 2048, 128, torch.float8_e4m3fn, torch.bfloat16, False),
+    (5, 7168, 128, torch.float8_e4m3fn, torch.bfloat16, False),
+    (5, 1536, 128, torch.float8_e4m3fn, torch.bfloat16, False),
+    (5, 16384, 128, torch.float8_e4m3fn, torch.bfloat16, False),
+    (5, 18432, 128, torch.float8_e4m3fn, torch.bfloat16, False),
+    (5, 2048, 128, torch.float8_e4m3fn, torch.bfloat16, False),
+    (40, 2048, 128, torch.float8_e4m3fn, torch.bfloat16, False),
+]
+
+
+def oracle_rows(x_cpu, group, dst, rows=None):
+    xs = x_cpu if rows is None else x_cpu[rows].contiguous()
+    if dst == torch.int8:
+        return O.per_token_group_quant_int8_ref(xs, group, EPS)
+    return O.per_token_group_quant_fp8_ref(xs, group, EPS)
+
+
+@pytest.mark.parametrize("m,k,group,dst,sdt,colmajor", REF_CASES)
+def test_reference_parametrisation_bit_exact(m, k, group, dst, sdt, colmajor):
+    torch.manual_seed(42)
+    x = torch.randn(m, k, dtype=sdt)
+    q, s = run_quant(x, group, dst=dst, column_major=colmajor)
+    # rows are independent: beyond 8 M elements check an evenly strided 1/8 of the rows exactly
+    rows = None if m * k <= (8 << 20) else torch.arange(0, m, 8)
+    q_ref, s_ref = oracle_rows(x, group, dst, rows)
+    if rows is not None:
+        q, s = q[rows], s[rows]
+    assert_bits_equal(q, s, q_ref, s_ref)
+
+
+@pytest.mark.parametrize("m", [1, 2, 4, 8, 16, 32, 64, 128, 256, 512, 1024, 2048, 4096, 8192, 16384, 32768])
+@pytest.mark.parametrize("colmajor", [False, True])
+def test_baseline_sweep_k7168(m, colmajor):
+    """BASELINE.json config 2: K=7168, group 128, M = 1..32768, row- and column-major scales."""
+    torch.manual_seed(0)
+    x = torch.randn(m, 7168, dtype=torch.bfloat16)
+    q, s = run_quant(x, 128, column_major=colmajor, tma_aligned=colmajor)
+    rows = None if m <= 1024 else torch.cat([torch.arange(0, m, max(1, m // 256)), torch.tensor([m - 1])])
+    q_ref, s_ref = oracle_rows(x, 128, torch.float8_e4m3fn, rows)
+    if rows is not None:
+        q, s = q[rows], s[rows]
+    assert_bits_equal(q, s, q_ref, s_ref)
+
+
+@pytest.mark.parametrize("scale", [1e-3, 100.0, 1e-20, 3e4])
+def test_magnitude_edge_cases(scale):
+    """tests/..8bit.py:339-355 (1e-3, 100) plus sub-eps and near-bf16-max magnitudes."""
+    torch.manual_seed(42)
+    x = (torch.randn(64, 512) * scale).to(torch.bfloat16)
+    q, s = run_quant(x, 64)
+    q_ref, s_ref = O.per_token_group_quant_fp8_ref(x, 64, EPS)
+    assert_bits_equal(q, s, q_ref, s_ref)
+    assert (s > 0).all() and torch.isfinite(s).all()
+
+
+def test_zero_rows_and_empty():
+    x = torch.zeros(3, 256, dtype=torch.bfloat16)
+    q, s = run_quant(x, 128)
+    assert (q.view(torch.uint8) == 0).all()
+    assert torch.equal(s, torch.full((3, 2), EPS) / 448.0)
+    q, s = run_quant(torch.zeros(0, 256, dtype=torch.bfloat16), 128)
+    assert q.shape == (0, 256) and s.shape == (0, 2)
+
+
+def test_three_d_input():
+    torch.manual_seed(1)
+    x = torch.randn(3, 7, 512, dtype=torch.bfloat16)
+    xd = x.to(DEV)
+    q = torch.empty_like(xd, dtype=torch.float8_e4m3fn)
+    s = torch.empty(21, 4, device=DEV)
+    sgl_kernel.sgl_per_token_group_quant_8bit(xd, q, s, 128, EPS, -448.0, 448.0, enable_v2=False)
+    q_ref, s_ref = O.per_token_group_quant_fp8_ref(x.view(21, 512), 128, EPS)
+    assert_bits_equal(q.cpu().view(21, 512), s.cpu(), q_ref, s_ref)
+
+
+def test_custom_clamp_range():
+    """fp8_min/fp8_max are honoured (the reference kernel clamps before converting, :174,188)."""
+    torch.manual_seed(2)
+    x = torch.randn(16, 256, dtype=torch.bfloat16)
+    xd = x.to(DEV)
+    q = torch.empty_like(xd, dtype=torch.float8_e4m3fn)
+    s = torch.empty(16, 2, device=DEV)
+    sgl_kernel.sgl_per_token_group_quant_8bit(xd, q, s, 128, EPS, -224.0, 224.0, enable_v2=False)
+    xv = x.view(16, 2, 128)
+    scale = xv.abs().float().amax(2).clamp(min=EPS) / 224.0
+    ref = (xv / scale.unsqueeze(2)).clamp(-224.0, 224.0).to(torch.float8_e4m3fn).view(16, 256)
+    assert_bits_equal(q.cpu(), s.cpu(), ref, scale)
+
+
+def test_fused_silu_mul_v2():
+    """v2 fused path vs its oracle (tests/test_per_token_group_quant_8bit_v2.py:408-444); the
+    reference's acceptance rule for codes is `assert_all_close_or_tiny_diff` (:599-628)."""
+    torch.manual_seed(11)
+    x = torch.randn(64, 2 * 2048, dtype=torch.bfloat16)
+    q, s = run_quant(x, 128, fuse_silu_and_mul=True, enable_v2=True)
+    y = O.silu_and_mul_ref(x).contiguous()
+    q_ref, s_ref = O.per_token_group_quant_fp8_ref(y, 128, EPS)
+    torch.testing.assert_close(s, s_ref, rtol=1e-3, atol=1e-7)
+    d = (q.view(torch.uint8).to(torch.int16) - q_ref.view(torch.uint8).to(torch.int16)).abs()
+    assert int((d >= 2).sum()) == 0 and float((d == 1).sum()) / d.numel() < 0.005
+
+
+def test_division_scheme_on_device():
+    """Exactness of the 3-op division against __fdiv_rn for every bf16 numerator, on the device."""
+    torch.manual_seed(5)
+    amax = torch.randn(4096).abs().to(torch.bfloat16).float().clamp(min=EPS)
+    amax = torch.cat([amax, torch.tensor([EPS, 1.0, 448.0, 3.0e38, 1.17549435e-38 * 448, 7.0, 0.875])])
+    scales = (amax / 448.0).to(DEV)
+    bad = torch.zeros(1, dtype=torch.int64, device=DEV)
+    rc = _lib.load().sglk_debug_check_division(scales.data_ptr(), scales.numel(), bad.data_ptr(),
+                                               torch.cuda.current_stream().cuda_stream)
+    assert rc == 0
+    torch.cuda.synchronize()
+    assert int(bad.item()) == 0
+
+
+def test_error_behaviour():
+    x = torch.randn(8, 512, dtype=torch.bfloat16, device=DEV)
+    q = torch.empty(8, 512, dtype=torch.float8_e4m3fn, device=DEV)
+    s = torch.empty(8, 4, device=DEV)
+    f = torch.ops.sgl_kernel.sgl_per_token_group_quant_8bit.default
+    with pytest.raises(RuntimeError, match="contiguous"):
+        f(x.t(), q, s, 128, EPS, -448.0, 448.0, False)
+    with pytest.raises(RuntimeError, match="group_size"):
+        f(x, q, s, 100, EPS, -448.0, 448.0, False)
+    with pytest.raises(RuntimeError, match="dtype"):
+        f(x.to(torch.float64), q, s, 128, EPS, -448.0, 448.0, False)
+    with pytest.raises(RuntimeError, match="dtype"):
+        f(x, q.view(torch.uint8), s, 128, EPS, -448.0, 448.0, False)
+    with pytest.raises(RuntimeError, match="dim"):
+        f(x, q, s.view(-1), 128, EPS, -448.0, 448.0, False)
+    with pytest.raises(RuntimeError, match="masked_m"):
+        torch.ops.sgl_kernel.sgl_per_token_group_quant_8bit_v2.default(
+            x, q, s, 128, EPS, -448.0, 448.0, False, False, torch.zeros(1, device=DEV, dtype=torch.int32))
+
+
+def test_cuda_graph_capture():
+    """No allocation and no sync inside the op: capturable (SURVEY.md §8b threading/streams)."""
+    x = torch.randn(64, 1024, dtype=torch.bfloat16, device=DEV)
+    q = torch.empty(64, 1024, dtype=torch.float8_e4m3fn, device=DEV)
+    s = torch.empty(64, 8, device=DEV)
+    g = torch.cuda.CUDAGraph()
+    st = torch.cuda.Stream()
+    with torch.cuda.stream(st):
+        with torch.cuda.graph(g, stream=st):
+            sgl_kernel.sgl_per_token_group_quant_8bit(x, q, s, 128, EPS, -448.0, 448.0, enable_v2=False)
+    x.copy_(torch.randn(64, 1024, dtype=torch.bfloat16))
+    g.replay()
+    torch.cuda.synchronize()
+    q_ref, s_ref = O.per_token_group_quant_fp8_ref(x.cpu(), 128, EPS)
+    assert_bits_equal(q.cpu(), s.cpu(), q_ref, s_ref)
