@@ -1,0 +1,330 @@
+#!/usr/bin/env python
+"""bench.py — headline benchmark of the FP8 block-quantized linear hot path on B200.
+
+Workload (BASELINE.json configs[4], the largest config and the one that shards):
+    DeepSeek-V3 dense MLP prefill, M=16384 tokens, N=18432, K=7168, bf16 activations,
+    e4m3 weights with 128x128 fp32 block scales.
+A *step* is one pass of the hot path over one batch:
+    per_token_group_quant_8bit (bf16 -> e4m3 + 1x128 fp32 scales, column-major)  ->  fp8_blockwise_scaled_mm
+With --gpus N the weight is column-(N-)sharded over the N ranks (one process per GPU, torchrun),
+activations replicated; total work is fixed, so scaling is "strong".  The all-gather that
+reassembles [M, N] is timed separately ("with_all_gather") because only some consumers need it.
+
+Prints ONE JSON line (rank 0).  `--impl reference` times the reference's own CPU implementation
+(the torch oracle restated in oracle/torch_oracle.py; the reference's native code is Intel SYCL and
+cannot run here) on a bounded sample of the same workload on the host cores.
+"""
+import argparse
+import json
+import os
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path[:0] = [ROOT, os.path.join(ROOT, "sgl-kernel-xpu_b200")]
+
+M_FULL, N_FULL, K_FULL = 16384, 18432, 7168
+WORKLOAD = "dsv3_dense_mlp_prefill_M16384_N18432_K7168_group128"
+METRIC = "FP8 blockwise GEMM TFLOPS (% dense-FP8 peak); group-quant GB/s (% HBM)"
+FP8_NOMINAL_TFLOPS = 4500.0
+HBM_NOMINAL_GBS = 8000.0
+
+
+def load_peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        p = json.load(open(path))
+        return {"hbm_gbs": float(p["hbm_gbs"]), "bf16_tflops": float(p["bf16_tflops"]),
+                "bf16_tflops_sustained": float(p.get("bf16_tflops_sustained", p["bf16_tflops"])), "source": "measured"}
+    # fallback stated in /opt/skills/guides/B200_PROFILING.md
+    return {"hbm_gbs": 6650.0, "bf16_tflops": 1590.0, "bf16_tflops_sustained": 1400.0, "source": "fallback"}
+
+
+class ClockSampler(threading.Thread):
+    """Samples SM clock and throttle reasons of one GPU during the timed region (NVML)."""
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index, self.samples, self.reasons, self.max_mhz = index, [], set(), None
+        self._stop_evt = threading.Event()
+        try:
+            import pynvml
+
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+        except Exception:  # noqa: BLE001
+            self.nv = None
+
+    def run(self):
+        if self.nv is None:
+            return
+        nv = self.nv
+        names = {
+            getattr(nv, "nvmlClocksEventReasonHwSlowdown", 0x8): "hw_slowdown",
+            getattr(nv, "nvmlClocksEventReasonHwThermalSlowdown", 0x40): "hw_thermal_slowdown",
+            getattr(nv, "nvmlClocksEventReasonSwThermalSlowdown", 0x20): "sw_thermal_slowdown",
+            getattr(nv, "nvmlClocksEventReasonSwPowerCap", 0x4): "sw_power_cap",
+            getattr(nv, "nvmlClocksEventReasonHwPowerBrakeSlowdown", 0x80): "hw_power_brake",
+        }
+        while not self._stop_evt.is_set():
+            try:
+                self.samples.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
+                try:
+                    r = nv.nvmlDeviceGetCurrentClocksEventReasons(self.h)
+                except Exception:  # noqa: BLE001
+                    r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                for bit, nm in names.items():
+                    if r & bit:
+                        self.reasons.add(nm)
+            except Exception:  # noqa: BLE001
+                pass
+            time.sleep(0.02)
+
+    def stop(self):
+        self._stop_evt.set()
+        self.join(timeout=2)
+        s = sorted(self.samples)
+        return {"sm_mhz": (s[len(s) // 2] if s else None), "sm_max_mhz": self.max_mhz,
+                "reasons": sorted(self.reasons), "samples": len(s)}
+
+
+def cpu_oracle_sample(rows, reps_budget_s=12.0, min_reps=2, max_reps=8):
+    """Time the CPU oracle (quant + dequantised matmul, all host threads) on the first `rows` tokens of
+    the workload.  Returns (best seconds, reps, threads)."""
+    import torch
+
+    from oracle import torch_oracle as O
+
+    g = torch.Generator().manual_seed(42)
+    x = torch.randn(rows, K_FULL, generator=g).to(torch.bfloat16)
+    wq_t = ((torch.rand(N_FULL, K_FULL, generator=g) - 0.5) * 896).to(torch.float8_e4m3fn).t()
+    ws_t = (torch.rand(K_FULL // 128, N_FULL // 128, generator=g) + 0.5) * 1e-3
+    O.fp8_linear_ref(x[:8], wq_t[:, :256], ws_t[:, :2])  # warm the thread pool
+    best, reps, t_start = 1e30, 0, time.perf_counter()
+    while reps < min_reps or (time.perf_counter() - t_start < reps_budget_s and reps < max_reps):
+        t0 = time.perf_counter()
+        O.fp8_linear_ref(x, wq_t, ws_t)
+        best = min(best, time.perf_counter() - t0)
+        reps += 1
+    return best, reps, torch.get_num_threads()
+
+
+def run_reference(args, rank, world):
+    """The reference arm: the reference's CPU path (torch oracle) on the host cores, rank 0 only."""
+    if rank != 0:
+        return
+    import torch
+
+    rows = args.cpu_rows
+    times = []
+    for i in range(args.warmup + args.steps):
+        t, _, threads = cpu_oracle_sample(rows, reps_budget_s=0.0, min_reps=1, max_reps=1)
+        if i >= args.warmup:
+            times.append(t)
+    ms = 1e3 * sum(times) / len(times)
+    tflops = 2.0 * rows * N_FULL * K_FULL / (ms * 1e-3) / 1e12
+    sample = f"first {rows} of {M_FULL} tokens, full N={N_FULL} K={K_FULL}: oracle quant + fp32 dequant torch.mm"
+    line = {
+        "impl": "reference", "metric": METRIC, "value": tflops, "unit": "TFLOPS", "n_gpus": world,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True,
+        "scaling": "strong", "vs_baseline": None, "dtype": "fp8_e4m3 (fp32 dequantised on CPU)", "data": "synthetic",
+        "config": {"workload": WORKLOAD, "M": M_FULL, "N": N_FULL, "K": K_FULL, "group": 128,
+                   "sample_rows_per_step": rows, "parallelism": "cpu threads"},
+        "cpu_baseline": {"value": tflops, "unit": "TFLOPS", "cores": threads, "kind": "port", "sample": sample},
+        "e2e": {"value": tflops, "unit": "TFLOPS", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "host_cpus": os.cpu_count(), "torch_threads": torch.get_num_threads(),
+    }
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--cpu-rows", type=int, default=256, help="tokens in the CPU-oracle sample")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--m", type=int, default=M_FULL, help="debug only: override token count")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
+
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if args.impl == "reference":
+        return run_reference(args, rank, world)
+
+    import torch
+    import torch.distributed as dist
+
+    import sgl_kernel
+    from sgl_kernel.sharded import ColumnShardedFp8Linear, shard_bounds
+
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: the product has no CPU fallback (use --impl reference for the CPU arm)")
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    M, N, K = args.m, N_FULL, K_FULL
+    lo, hi = shard_bounds(N, world, rank)
+    n_loc = hi - lo
+
+    # synthetic data, resident in HBM before the timed region
+    g = torch.Generator(device=dev).manual_seed(1234)          # identical activations on every rank
+    x = torch.randn(M, K, generator=g, device=dev, dtype=torch.float32).to(torch.bfloat16)
+    gw = torch.Generator(device=dev).manual_seed(77 + rank)
+    wq = ((torch.rand(n_loc, K, generator=gw, device=dev) - 0.5) * 896).to(torch.float8_e4m3fn)
+    ws = (torch.rand(-(n_loc // -128), K // 128, generator=gw, device=dev) + 0.5) * 1e-3
+    layer = sgl_kernel.Fp8BlockLinear(wq, ws)
+    sharded = ColumnShardedFp8Linear(layer, N) if world > 1 else None
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)   # > 126 MB L2
+
+    xq = torch.empty(M, K, dtype=torch.float8_e4m3fn, device=dev)
+    xs = sgl_kernel.create_per_token_group_quant_fp8_output_scale((M, K), dev, 128, True, True, False)
+
+    def step():
+        sgl_kernel.sgl_per_token_group_quant_8bit(x, xq, xs, 128, 1e-10, -448.0, 448.0, enable_v2=False)
+        return layer.forward_quantized(xq, xs)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(args.warmup):
+        flush.zero_()
+        out = step()
+    barrier()
+
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    ev = [[torch.cuda.Event(enable_timing=True) for _ in range(3)] for _ in range(args.steps)]
+    barrier()
+    t_wall0 = time.perf_counter()
+    for i in range(args.steps):
+        flush.zero_()                                            # L2 flush, outside the per-step events
+        ev[i][0].record()
+        sgl_kernel.sgl_per_token_group_quant_8bit(x, xq, xs, 128, 1e-10, -448.0, 448.0, enable_v2=False)
+        ev[i][1].record()
+        out = layer.forward_quantized(xq, xs)
+        ev[i][2].record()
+    barrier()
+    t_wall = time.perf_counter() - t_wall0
+    clocks = sampler.stop()
+    t_quant = sum(e[0].elapsed_time(e[1]) for e in ev) / args.steps     # ms
+    t_gemm = sum(e[1].elapsed_time(e[2]) for e in ev) / args.steps
+    t_step = sum(e[0].elapsed_time(e[2]) for e in ev) / args.steps
+    tt = torch.tensor([t_step, t_quant, t_gemm], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+    t_step, t_quant, t_gemm = (float(v) for v in tt.tolist())
+
+    # ---- step + all-gather of the output panels (only for consumers that need [M, N]) ----
+    with_gather = None
+    if world > 1:
+        full = torch.empty(M, N, dtype=torch.bfloat16, device=dev)
+        for _ in range(2):
+            sharded.gather(step(), full)
+        barrier()
+        evg = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+        for i in range(args.steps):
+            flush.zero_()
+            evg[i][0].record()
+            sharded.gather(step(), full)
+            evg[i][1].record()
+        barrier()
+        tg = torch.tensor([sum(a.elapsed_time(b) for a, b in evg) / args.steps], device=dev, dtype=torch.float64)
+        dist.all_reduce(tg, op=dist.ReduceOp.MAX)
+        with_gather = {"ms_per_step": float(tg.item()), "value": 2.0 * M * N * K / (float(tg.item()) * 1e-3) / 1e12,
+                       "unit": "TFLOPS", "collective": "nccl all_gather_into_tensor + panel interleave copy"}
+        del full
+
+    # ---- end to end through the public API with HOST buffers (pinned), copies inside the timed region ----
+    e2e = None
+    if not args.no_e2e:
+        x_host = torch.empty(M, K, dtype=torch.bfloat16).pin_memory()
+        x_host.copy_(x)
+        out_host = torch.empty(M, n_loc, dtype=torch.bfloat16).pin_memory()
+        x_in = torch.empty_like(x)
+
+        def e2e_step():
+            x_in.copy_(x_host, non_blocking=True)
+            y = layer(x_in)                       # public API: Fp8BlockLinear.__call__ = quant op + GEMM op
+            out_host.copy_(y, non_blocking=True)
+
+        e2e_steps = max(3, min(args.steps, 10))
+        for _ in range(2):
+            e2e_step()
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(e2e_steps):
+            e2e_step()
+        e1.record()
+        barrier()
+        te = torch.tensor([e0.elapsed_time(e1) / e2e_steps], device=dev, dtype=torch.float64)
+        if world > 1:
+            dist.all_reduce(te, op=dist.ReduceOp.MAX)
+        e2e = {"value": 2.0 * M * N * K / (float(te.item()) * 1e-3) / 1e12, "unit": "TFLOPS",
+               "ms_per_step": float(te.item()), "steps": e2e_steps,
+               "h2d_bytes_per_step": int(x_host.numel() * 2 * world), "d2h_bytes_per_step": int(M * N * 2),
+               "note": "pinned host x -> HBM, quant + GEMM ops, result panel -> pinned host; bytes are whole-job (all ranks)"}
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+
+    peaks = load_peaks()
+    fp8_peak = 2.0 * peaks["bf16_tflops"]
+    gemm_tflops_rank = 2.0 * M * n_loc * K / (t_gemm * 1e-3) / 1e12
+    quant_bytes = M * K * 3 + M * (K // 128) * 4
+    quant_gbs = quant_bytes / (t_quant * 1e-3) / 1e9
+    value = 2.0 * M * N * K / (t_step * 1e-3) / 1e12
+
+    cpu_baseline = None
+    if world == 1 and not args.no_cpu_baseline:
+        best, reps, threads = cpu_oracle_sample(args.cpu_rows)
+        cpu_baseline = {
+            "value": 2.0 * args.cpu_rows * N * K / best / 1e12, "unit": "TFLOPS", "cores": threads, "kind": "port",
+            "sample": f"first {args.cpu_rows} of {M} tokens, full N={N} K={K}: oracle quant + fp32 dequant torch.mm, "
+                      f"best of {reps} ({best:.2f} s each)", "host_cpus": os.cpu_count(),
+        }
+
+    line = {
+        "metric": METRIC, "value": value, "unit": "TFLOPS", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": t_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+        "dtype": "fp8_e4m3 x fp8_e4m3 -> fp32 accumulate -> bf16", "data": "synthetic",
+        "config": {"workload": WORKLOAD, "M": M, "N": N, "K": K, "group": 128, "n_per_rank": n_loc,
+                   "parallelism": f"column(N)-sharded x{world}, activations replicated" if world > 1 else "single GPU",
+                   "step": "per_token_group_quant_8bit (col-major scales) + fp8_blockwise_scaled_mm, no collective in value",
+                   "l2": "256 MiB flush between steps (outside the events); inputs 235 MB + weights > L2",
+                   "gemm_variant": sgl_kernel._lib.load().sglk_gemm_variant_name(
+                       sgl_kernel._lib.load().sglk_gemm_pick_variant(M, n_loc, K)).decode()},
+        "gemm_tflops": 2.0 * M * N * K / (t_gemm * 1e-3) / 1e12, "gemm_ms": t_gemm,
+        "quant_gbps": quant_gbs, "quant_ms": t_quant,
+        "roofline": {"bound": "tensor", "achieved": gemm_tflops_rank, "peak": fp8_peak, "unit": "TFLOP/s",
+                     "frac": gemm_tflops_rank / fp8_peak, "traffic": None,
+                     "kernel": "fp8_blockwise_gemm_kernel", "algorithmic_flops_per_launch": 2.0 * M * n_loc * K,
+                     "peak_source": f"2 x {peaks['source']} cuBLAS bf16 burst ({peaks['bf16_tflops']} TF/s): fp8 dense = 2x bf16 rate; "
+                                    f"frac of nominal 4500 TF/s = {gemm_tflops_rank / FP8_NOMINAL_TFLOPS:.3f}"},
+        "roofline_quant": {"bound": "hbm", "achieved": quant_gbs, "peak": peaks["hbm_gbs"], "unit": "GB/s",
+                           "frac": quant_gbs / peaks["hbm_gbs"], "traffic": None, "kernel": "ptgq_kernel",
+                           "algorithmic_bytes_per_launch": quant_bytes,
+                           "peak_source": f"{peaks['source']} copy bandwidth; frac of nominal 8000 GB/s = {quant_gbs / HBM_NOMINAL_GBS:.3f}"},
+        "cpu_baseline": cpu_baseline, "e2e": e2e, "with_all_gather": with_gather,
+        "gpu_launches": 2 * args.steps * world, "clocks": clocks, "wall_s_timed_region": t_wall,
+    }
+    print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -108,7 +108,7 @@ __device__ __forceinline__ void tile_coords(int tile, const GemmParams& p, int& 
   nb = in_g / rows;
 }
 
-template <int BLOCK_N, int kStages, int kCG, typename OutT, bool kTmaStore>
+template <int BLOCK_N, int kStages, int kCG, typename OutT, bool kTmaStore, bool kDiagNoPromote = false>
 __global__ void __launch_bounds__(kNumThreads, 1)
 fp8_blockwise_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
                           const __grid_constant__ CUtensorMap tmap_c, const GemmParams p) {
@@ -267,6 +267,9 @@ fp8_blockwise_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gr
         ptx::mbar_wait(tfull_bar(acc), acc_phase);
         ptx::tc_fence_after();
         const uint32_t taddr = tmem_base + lane_base + uint32_t(acc * BLOCK_N + half * NC);
+        if constexpr (kDiagNoPromote) {   // diagnostic variant: TMA + MMA pipeline only, output is meaningless
+          accum[0] += s + float(taddr);
+        } else {
         uint32_t v[2][32];
         ptx::tmem_ld_32x32(taddr, v[0]);
         ptx::tmem_ld_wait(v[0]);
@@ -278,6 +281,7 @@ fp8_blockwise_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gr
           for (int i = 0; i < 32; i += 2)
             ptx::fma2(accum[c * 32 + i], accum[c * 32 + i + 1], v[c & 1][i], v[c & 1][i + 1], s);
           if (c + 1 < NC / 32) ptx::tmem_ld_wait(v[(c + 1) & 1]);
+        }
         }
         // all of this warp's reads of the stage are complete: hand it back to the MMA issuer
         ptx::tc_fence_before();
@@ -395,14 +399,15 @@ static const Variant kVariants[] = {
     {"n256_s6_cta2_direct", 256, 6, 2, false},
     {"n128_s8_cta2_tma", 128, 8, 2, true},
     {"n64_s8_cta1_direct", 64, 8, 1, false},
+    {"diag_n256_s6_cta2_mma_only", 256, 6, 2, false},   // NOT a product path: skips promotion, wrong results
 };
 constexpr int kNumVariants = int(sizeof(kVariants) / sizeof(kVariants[0]));
 
-template <int BLOCK_N, int kStages, int kCG, typename OutT, bool kTmaStore>
+template <int BLOCK_N, int kStages, int kCG, typename OutT, bool kTmaStore, bool kDiag = false>
 static int launch_variant(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& tc, const GemmParams& p,
                           int num_sms, cudaStream_t st) {
   using C = Cfg<BLOCK_N, kCG>;
-  auto kern = fp8_blockwise_gemm_kernel<BLOCK_N, kStages, kCG, OutT, kTmaStore>;
+  auto kern = fp8_blockwise_gemm_kernel<BLOCK_N, kStages, kCG, OutT, kTmaStore, kDiag>;
   constexpr int smem = C::smem_bytes(kStages);
   static_assert(smem <= 232448, "shared memory budget");
   static bool configured = false;   // per instantiation
@@ -442,6 +447,7 @@ static int launch_by_id(int v, const CUtensorMap& ta, const CUtensorMap& tb, con
     case 4: return launch_variant<256, 6, 2, OutT, false>(ta, tb, tc, p, num_sms, st);
     case 5: return launch_variant<128, 8, 2, OutT, true>(ta, tb, tc, p, num_sms, st);
     case 6: return launch_variant<64, 8, 1, OutT, false>(ta, tb, tc, p, num_sms, st);
+    case 7: return launch_variant<256, 6, 2, OutT, false, true>(ta, tb, tc, p, num_sms, st);
     default: return SGLK_E_VARIANT;
   }
 }

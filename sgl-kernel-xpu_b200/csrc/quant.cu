@@ -97,7 +97,9 @@ __device__ __forceinline__ float div_exact(float x, float s, float r) {
   if constexpr (kExactFast) {
     const float q0 = x * r;
     const float e = __fmaf_rn(-q0, s, x);
-    return __fmaf_rn(e, r, q0);
+    const float q1 = __fmaf_rn(e, r, q0);
+    // x = -0.0 makes e = +0 and q1 = +0; RN(x/s) keeps the sign (code 0x80), so copy it (one LOP3)
+    return __uint_as_float((__float_as_uint(q1) & 0x7FFFFFFFu) | (__float_as_uint(x) & 0x80000000u));
   } else {
     return __fdiv_rn(x, s);
   }
