@@ -143,10 +143,11 @@ SGLK_API const char* sglk_gemm_variant_name(int variant);
 /* the variant the heuristic would pick for a problem */
 SGLK_API int sglk_gemm_pick_variant(int64_t M, int64_t N, int64_t K);
 
-/* Device self-check of the quant kernel's division scheme against __fdiv_rn over every bf16
- * numerator for `num_scales` scales; writes the mismatch count to *mismatches (device ptr). */
-SGLK_API int sglk_debug_check_division(const float* scales, int64_t num_scales, unsigned long long* mismatches,
-                              void* stream);
+/* Device self-check of the quant kernel's division scheme against __fdiv_rn over every 16-bit
+ * numerator (numerator_dtype = SGLK_BF16 or SGLK_F16) for `num_scales` scales; adds the number of
+ * differing e4m3 codes to *mismatches (device ptr). */
+SGLK_API int sglk_debug_check_division(const float* scales, int64_t num_scales, int numerator_dtype,
+                              unsigned long long* mismatches, void* stream);
 
 #ifdef __cplusplus
 }

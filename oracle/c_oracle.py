@@ -38,7 +38,7 @@ def lib() -> ctypes.CDLL:
         L.oracle_blockwise_scaled_mm.argtypes = [ctypes.c_void_p] * 4 + [ctypes.c_int64] * 7 + [ctypes.c_void_p]
         L.oracle_check_division_scheme.restype = ctypes.c_int64
         L.oracle_check_division_scheme.argtypes = [ctypes.c_uint32, ctypes.c_uint32, ctypes.c_float,
-                                                   ctypes.c_float, ctypes.POINTER(ctypes.c_int64)]
+                                                   ctypes.c_float, ctypes.c_int, ctypes.POINTER(ctypes.c_int64)]
         _lib = L
     return _lib
 
@@ -73,7 +73,7 @@ def blockwise_scaled_mm(a: np.ndarray, bt: np.ndarray, sa: np.ndarray, sb: np.nd
     return out
 
 
-def check_division_scheme(amax_lo: int, amax_hi: int, qmax: float = 448.0, eps: float = 1e-10):
+def check_division_scheme(amax_lo: int, amax_hi: int, qmax: float = 448.0, eps: float = 1e-10, src_f16: bool = False):
     n = ctypes.c_int64(0)
-    bad = lib().oracle_check_division_scheme(amax_lo, amax_hi, qmax, eps, ctypes.byref(n))
+    bad = lib().oracle_check_division_scheme(amax_lo, amax_hi, qmax, eps, int(src_f16), ctypes.byref(n))
     return int(bad), int(n.value)

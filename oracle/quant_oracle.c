@@ -159,24 +159,32 @@ void oracle_blockwise_scaled_mm(const uint8_t* A, const uint8_t* Bt, const float
 
 /*
  * Arithmetic check for the CUDA kernel's division scheme (DESIGN.md "quant kernel"):
- *   r = RN(1/s);  q0 = RN(x*r);  e = fma(-q0, s, x);  q1 = fma(e, r, q0)
- * must equal RN(x/s) wherever the e4m3 result can depend on it.  Sweeps every finite bf16 x
- * against the scale produced by every bf16 amax in [amax_lo, amax_hi) (bit patterns), and
- * returns the number of (x, amax) pairs with |x| <= amax whose e4m3 codes differ.
+ *   scale: q0 = RN(amax*rq); scale = fma(fma(-q0, qmax, amax), rq, q0)      with rq = RN(1/qmax)
+ *   codes: r = RN(1/s);  q0 = RN(x*r);  e = fma(q0, -s, x);  q1 = fma(e, r, q0)
+ * The scale must equal RN(amax/qmax) bit for bit, and RNE_e4m3(q1) must equal RNE_e4m3(RN(x/s)).
+ * Sweeps every finite 16-bit x (bf16 when src_f16 == 0, IEEE half otherwise) with |x| <= amax against
+ * every 16-bit amax whose bit pattern lies in [amax_lo, amax_hi); returns the number of mismatches.
+ * (x >= 0 only: the scheme is sign-symmetric and the kernel copies the sign bit from x.)
  */
-int64_t oracle_check_division_scheme(uint32_t amax_lo, uint32_t amax_hi, float qmax, float eps,
+int64_t oracle_check_division_scheme(uint32_t amax_lo, uint32_t amax_hi, float qmax, float eps, int src_f16,
                                      int64_t* n_checked) {
   int64_t bad = 0, n = 0;
+  const float rq = 1.0f / qmax;
   for (uint32_t ab = amax_lo; ab < amax_hi; ++ab) {
-    float amax = bf16_to_f32((uint16_t)ab);
+    float amax = src_f16 ? f16_to_f32((uint16_t)ab) : bf16_to_f32((uint16_t)ab);
     if (isnan(amax) || isinf(amax)) continue;
-    float s = (amax < eps ? eps : amax) / qmax;      /* clamp(min=eps) as in the quant oracle */
+    if (amax < eps) amax = eps;                        /* clamp(min=eps) as in the quant oracle */
+    float s = amax / qmax;
+    float sq0 = amax * rq;
+    float s2 = fmaf(fmaf(-sq0, qmax, amax), rq, sq0);
+    ++n;
+    if (f32_as_u32(s) != f32_as_u32(s2)) ++bad;
     float r = 1.0f / s;
-    for (uint32_t xb = 0; xb <= ab; ++xb) {            /* positive x with |x| <= amax; sign symmetric */
-      float x = bf16_to_f32((uint16_t)xb);
+    for (uint32_t xb = 0; xb <= ab; ++xb) {            /* positive x with |x| <= amax */
+      float x = src_f16 ? f16_to_f32((uint16_t)xb) : bf16_to_f32((uint16_t)xb);
       float exact = x / s;
       float q0 = x * r;
-      float e = fmaf(-q0, s, x);
+      float e = fmaf(q0, -s, x);
       float q1 = fmaf(e, r, q0);
       ++n;
       if (oracle_f32_to_e4m3fn(exact) != oracle_f32_to_e4m3fn(q1)) ++bad;

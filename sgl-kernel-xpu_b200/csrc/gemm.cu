@@ -259,31 +259,15 @@ fp8_blockwise_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gr
       float accum[NC];
 #pragma unroll
       for (int i = 0; i < NC; ++i) accum[i] = 0.0f;
-      float s_next = (row_ok ? __ldg(sa_ptr) : 0.0f) * __ldg(sb_ptr);
-      for (int kb = 0; kb < num_kb; ++kb) {
-        const float s = s_next;
-        if (kb + 1 < num_kb)
-          s_next = (row_ok ? __ldg(sa_ptr + int64_t(kb + 1) * p.sa_sk) : 0.0f) * __ldg(sb_ptr + int64_t(kb + 1) * p.sb_sk);
-        ptx::mbar_wait(tfull_bar(acc), acc_phase);
-        ptx::tc_fence_after();
-        const uint32_t taddr = tmem_base + lane_base + uint32_t(acc * BLOCK_N + half * NC);
-        if constexpr (kDiagNoPromote) {   // diagnostic variant: TMA + MMA pipeline only, output is meaningless
-          accum[0] += s + float(taddr);
-        } else {
-        uint32_t v[2][32];
-        ptx::tmem_ld_32x32(taddr, v[0]);
-        ptx::tmem_ld_wait(v[0]);
-#pragma unroll
-        for (int c = 0; c < NC / 32; ++c) {
-          // double-buffered: fetch chunk c+1 while chunk c is folded into the accumulators
-          if (c + 1 < NC / 32) ptx::tmem_ld_32x32(taddr + uint32_t((c + 1) * 32), v[(c + 1) & 1]);
-#pragma unroll
-          for (int i = 0; i < 32; i += 2)
-            ptx::fma2(accum[c * 32 + i], accum[c * 32 + i + 1], v[c & 1][i], v[c & 1][i + 1], s);
-          if (c + 1 < NC / 32) ptx::tmem_ld_wait(v[(c + 1) & 1]);
-        }
-        }
-        // all of this warp's reads of the stage are complete: hand it back to the MMA issuer
+      // Scale prefetch, two K blocks ahead, kept as raw loads: the product is formed only at the top
+      // of the iteration that uses it, so no instruction ever waits on an in-flight global load
+      // (an in-order warp that multiplies right after the load stalls ~1 us per K block — measured).
+      auto ld_sa = [&](int kb) { return (row_ok && kb < num_kb) ? __ldg(sa_ptr + int64_t(kb) * p.sa_sk) : 0.0f; };
+      auto ld_sb = [&](int kb) { return kb < num_kb ? __ldg(sb_ptr + int64_t(kb) * p.sb_sk) : 0.0f; };
+      float sa0 = ld_sa(0), sb0 = ld_sb(0), sa1 = ld_sa(1), sb1 = ld_sb(1);
+      constexpr int NCH = NC / 32;           // 32-column TMEM chunks per K block for this warp
+      auto release_stage = [&]() {
+        // every tcgen05.ld of this warp on the stage has completed: hand it back to the MMA issuer
         ptx::tc_fence_before();
         __syncwarp();
         if (lane == 0) {
@@ -291,6 +275,76 @@ fp8_blockwise_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gr
           else ptx::mbar_arrive(tempty_bar(acc));
         }
         if (++acc == kAccStages) { acc = 0; acc_phase ^= 1; }
+      };
+      auto stage_addr = [&]() { return tmem_base + lane_base + uint32_t(acc * BLOCK_N + half * NC); };
+      uint32_t v[2][32];
+      if constexpr (kDiagNoPromote) {        // diagnostic variant: TMA + MMA pipeline only, output is meaningless
+        for (int kb = 0; kb < num_kb; ++kb) {
+          ptx::mbar_wait(tfull_bar(acc), acc_phase);
+          ptx::tc_fence_after();
+          accum[0] += sa0 * sb0 + float(stage_addr());
+          release_stage();
+        }
+      } else if constexpr (NCH % 2 == 0) {
+        // Software pipeline across K blocks: chunk c+1 is in flight while chunk c is folded in, the
+        // stage is released as soon as its last chunk is in registers (before that chunk's FMAs),
+        // and the first chunk of the NEXT K block is requested before the last FMAs of this one.
+        ptx::mbar_wait(tfull_bar(acc), acc_phase);
+        ptx::tc_fence_after();
+        uint32_t taddr = stage_addr();
+        ptx::tmem_ld_32x32(taddr, v[0]);
+        for (int kb = 0; kb < num_kb; ++kb) {
+          const float s = sa0 * sb0;
+          sa0 = sa1; sb0 = sb1;
+          sa1 = ld_sa(kb + 2); sb1 = ld_sb(kb + 2);
+#pragma unroll
+          for (int c = 0; c < NCH; ++c) {
+            ptx::tmem_ld_wait(v[c & 1]);
+            bool deferred = false;
+            if (c + 1 < NCH) {
+              ptx::tmem_ld_32x32(taddr + uint32_t((c + 1) * 32), v[(c + 1) & 1]);
+            } else {
+              release_stage();
+              if (kb + 1 < num_kb) {
+                taddr = stage_addr();
+                if (ptx::mbar_try_wait(tfull_bar(acc), acc_phase)) {
+                  ptx::tc_fence_after();
+                  ptx::tmem_ld_32x32(taddr, v[0]);
+                } else {
+                  deferred = true;
+                }
+              }
+            }
+#pragma unroll
+            for (int i = 0; i < 32; i += 2)
+              ptx::fma2(accum[c * 32 + i], accum[c * 32 + i + 1], v[c & 1][i], v[c & 1][i + 1], s);
+            if (deferred) {
+              ptx::mbar_wait(tfull_bar(acc), acc_phase);
+              ptx::tc_fence_after();
+              ptx::tmem_ld_32x32(taddr, v[0]);
+            }
+          }
+        }
+      } else {
+        for (int kb = 0; kb < num_kb; ++kb) {
+          const float s = sa0 * sb0;
+          sa0 = sa1; sb0 = sb1;
+          sa1 = ld_sa(kb + 2); sb1 = ld_sb(kb + 2);
+          ptx::mbar_wait(tfull_bar(acc), acc_phase);
+          ptx::tc_fence_after();
+          const uint32_t taddr = stage_addr();
+          ptx::tmem_ld_32x32(taddr, v[0]);
+          ptx::tmem_ld_wait(v[0]);
+#pragma unroll
+          for (int c = 0; c < NCH; ++c) {
+            if (c + 1 < NCH) ptx::tmem_ld_32x32(taddr + uint32_t((c + 1) * 32), v[(c + 1) & 1]);
+            else release_stage();
+#pragma unroll
+            for (int i = 0; i < 32; i += 2)
+              ptx::fma2(accum[c * 32 + i], accum[c * 32 + i + 1], v[c & 1][i], v[c & 1][i + 1], s);
+            if (c + 1 < NCH) ptx::tmem_ld_wait(v[(c + 1) & 1]);
+          }
+        }
       }
       // ---------------- write the finished 32 x NC sub-tile ----------------
       if constexpr (kTmaStore) {

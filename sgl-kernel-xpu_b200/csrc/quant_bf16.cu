@@ -1,0 +1,10 @@
+// Instantiations of the quant kernel for bf16 inputs (one TU per dtype keeps the build parallel).
+#include "quant_kernel.cuh"
+
+namespace sglk {
+int quant_launch_bf16(bool fuse, int64_t group, int out_dtype, int layout, const void* x, void* q, void* s,
+                      const QuantParams& p, cudaStream_t st) {
+  if (fuse) return launch_dtype<__nv_bfloat16, true>(group, out_dtype, layout, x, q, s, p, st);
+  return launch_dtype<__nv_bfloat16, false>(group, out_dtype, layout, x, q, s, p, st);
+}
+}  // namespace sglk

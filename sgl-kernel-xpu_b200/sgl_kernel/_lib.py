@@ -36,7 +36,7 @@ SYMBOLS = {
     "sglk_gemm_num_variants": (_i32, []),
     "sglk_gemm_variant_name": (ctypes.c_char_p, [_i32]),
     "sglk_gemm_pick_variant": (_i32, [_i64, _i64, _i64]),
-    "sglk_debug_check_division": (_i32, [_vp, _i64, _vp, _vp]),
+    "sglk_debug_check_division": (_i32, [_vp, _i64, _i32, _vp, _vp]),
 }
 
 _lib = None

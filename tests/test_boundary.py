@@ -57,7 +57,7 @@ def test_c_abi_rejects_bad_arguments_before_launch():
     assert q(p, p, p, 3, 2, 128, _lib.BF16, _lib.E4M3, 1e-10, -448.0, 448.0, 0, 0, 0, None) == -4         # groups % row
     assert q(p, p, p, 1, 1, 128, _lib.BF16, _lib.E4M3, 1e-10, -448.0, 448.0, 0, 9, 0, None) == -6         # layout
     assert q(p, p, p, 1, 1, 128, _lib.BF16, _lib.E4M3, 1e-10, -448.0, 448.0, 1, 0, 0, None) == -6         # ue8m0 vs layout
-    assert q(p + 2, p, p, 1, 1, 128, _lib.BF16, _lib.E4M3, 1e-10, -448.0, 448.0, 0, 0, 0, None) == -5     # alignment
+    assert q(p + 1, p, p, 1, 1, 128, _lib.BF16, _lib.E4M3, 1e-10, -448.0, 448.0, 0, 0, 0, None) == -5     # element alignment
     assert q(p, p, p, 0, 1, 128, _lib.BF16, _lib.E4M3, 1e-10, -448.0, 448.0, 0, 0, 0, None) == 0          # empty: no-op
     g = lib.sglk_fp8_blockwise_scaled_mm
     assert g(p, p, p, p, p, 4, 128, 100, 112, 112, 128, 1, 4, 1, 1, _lib.BF16, None) == -5                # K % 16

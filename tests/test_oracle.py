@@ -149,4 +149,12 @@ def test_division_scheme_exact_on_sampled_scales():
         b, c = c_oracle.check_division_scheme(lo, lo + 0x40)
         bad += b
         n += c
+    for lo in (0x0000, 0x0400, 0x2000, 0x3C00, 0x5000, 0x7B00):          # IEEE half numerators
+        b, c = c_oracle.check_division_scheme(lo, lo + 0x40, src_f16=True)
+        bad += b
+        n += c
+    for qmax in (127.0, 224.0):                                          # int8 / custom clamp ranges: scale division
+        b, c = c_oracle.check_division_scheme(0x3F00, 0x3F40, qmax=qmax)
+        bad += b
+        n += c
     assert n > 1_000_000 and bad == 0

@@ -169,6 +169,22 @@ def test_zero_rows_and_empty():
     assert q.shape == (0, 256) and s.shape == (0, 2)
 
 
+def test_misaligned_views_use_generic_kernel():
+    """An input view that is only 2-byte aligned (and codes 1-byte aligned) still quantises on the
+    device, bit-exactly (alignment-agnostic kernel; no CPU fallback)."""
+    torch.manual_seed(4)
+    x = torch.randn(9, 512, dtype=torch.bfloat16)
+    buf = torch.empty(9 * 512 + 8, dtype=torch.bfloat16, device=DEV)
+    xv = buf[1:1 + 9 * 512].view(9, 512)
+    xv.copy_(x)
+    qbuf = torch.empty(9 * 512 + 16, dtype=torch.float8_e4m3fn, device=DEV)
+    qv = qbuf[3:3 + 9 * 512].view(9, 512)
+    s = torch.empty(9, 4, device=DEV)
+    sgl_kernel.sgl_per_token_group_quant_8bit(xv, qv, s, 128, EPS, -448.0, 448.0, enable_v2=False)
+    q_ref, s_ref = O.per_token_group_quant_fp8_ref(x, 128, EPS)
+    assert_bits_equal(qv.cpu().contiguous(), s.cpu(), q_ref, s_ref)
+
+
 def test_three_d_input():
     torch.manual_seed(1)
     x = torch.randn(3, 7, 512, dtype=torch.bfloat16)
@@ -213,12 +229,13 @@ def test_division_scheme_on_device():
     amax = torch.randn(4096).abs().to(torch.bfloat16).float().clamp(min=EPS)
     amax = torch.cat([amax, torch.tensor([EPS, 1.0, 448.0, 3.0e38, 1.17549435e-38 * 448, 7.0, 0.875])])
     scales = (amax / 448.0).to(DEV)
-    bad = torch.zeros(1, dtype=torch.int64, device=DEV)
-    rc = _lib.load().sglk_debug_check_division(scales.data_ptr(), scales.numel(), bad.data_ptr(),
-                                               torch.cuda.current_stream().cuda_stream)
-    assert rc == 0
-    torch.cuda.synchronize()
-    assert int(bad.item()) == 0
+    for dt in (_lib.BF16, _lib.F16):
+        bad = torch.zeros(1, dtype=torch.int64, device=DEV)
+        rc = _lib.load().sglk_debug_check_division(scales.data_ptr(), scales.numel(), dt, bad.data_ptr(),
+                                                   torch.cuda.current_stream().cuda_stream)
+        assert rc == 0
+        torch.cuda.synchronize()
+        assert int(bad.item()) == 0
 
 
 def test_error_behaviour():
