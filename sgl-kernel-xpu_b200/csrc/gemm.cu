@@ -61,7 +61,9 @@ struct Cfg {
   static constexpr int TMEM_COLS = kAccStages * BLOCK_N;       // 256 or 512: power of two
   static constexpr int STORE_BYTES = kNumEpiWarps * 32 * kStoreBoxCols * 2;   // 32 KB
   static constexpr int BAR_BYTES = 1024;
-  static constexpr int smem_bytes(int stages) { return 1024 + stages * STAGE_BYTES + STORE_BYTES + BAR_BYTES; }
+  static constexpr int smem_bytes(int stages, bool tma_store) {
+    return 1024 + stages * STAGE_BYTES + (tma_store ? STORE_BYTES : 0) + BAR_BYTES;
+  }
   static_assert(BLOCK_N % 64 == 0 && BLOCK_N <= 256, "BLOCK_N");
   static constexpr bool kCanTmaStore = (NC % kStoreBoxCols) == 0;
   static_assert((TMEM_COLS & (TMEM_COLS - 1)) == 0 && TMEM_COLS >= 32 && TMEM_COLS <= 512, "TMEM columns");
@@ -108,7 +110,9 @@ __device__ __forceinline__ void tile_coords(int tile, const GemmParams& p, int& 
   nb = in_g / rows;
 }
 
-template <int BLOCK_N, int kStages, int kCG, typename OutT, bool kTmaStore, bool kDiagNoPromote = false>
+// kDiag (diagnostics only, results are NOT the op's): 1 = skip the promotion arithmetic, 2 = accumulate all of K in
+// TMEM like an unscaled GEMM (one accumulator hand-off per tile) — both measure ceilings of the TMA/MMA pipeline.
+template <int BLOCK_N, int kStages, int kCG, typename OutT, bool kTmaStore, int kDiag = 0>
 __global__ void __launch_bounds__(kNumThreads, 1)
 fp8_blockwise_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
                           const __grid_constant__ CUtensorMap tmap_c, const GemmParams p) {
@@ -121,7 +125,7 @@ fp8_blockwise_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gr
   // 128B-swizzled TMA/UMMA tiles need 1024-byte alignment
   const uint32_t smem_base = (ptx::smem_u32(smem_raw) + 1023u) & ~1023u;
   const uint32_t smem_store = smem_base + kStages * C::STAGE_BYTES;
-  const uint32_t bar_base = smem_store + C::STORE_BYTES;
+  const uint32_t bar_base = smem_store + (kTmaStore ? C::STORE_BYTES : 0);
   auto full_bar = [&](int s) { return bar_base + 8u * s; };
   auto empty_bar = [&](int s) { return bar_base + 8u * (kStages + s); };
   auto tfull_bar = [&](int s) { return bar_base + 8u * (2 * kStages + s); };
@@ -170,7 +174,7 @@ fp8_blockwise_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gr
   if (warp == 0) {
     // =========================== TMA producer ===========================
     ptx::reg_dealloc<56>();
-    if (lane == 0) {
+    {
       const uint64_t pol_a = ptx::policy_evict_normal();
       const uint64_t pol_b = ptx::policy_evict_normal();
       int stage = 0;
@@ -184,17 +188,20 @@ fp8_blockwise_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gr
           ptx::mbar_wait(empty_bar(stage), phase ^ 1);
           const uint32_t sa_addr = smem_base + stage * C::STAGE_BYTES;
           const uint32_t sb_addr = sa_addr + C::A_BYTES;
-          if constexpr (kCG == 1) {
-            ptx::mbar_arrive_expect_tx(full_bar(stage), C::STAGE_BYTES);
-            ptx::tma_load_2d(&tmap_a, full_bar(stage), sa_addr, kb * BLOCK_K, m0, pol_a);
-            ptx::tma_load_2d(&tmap_b, full_bar(stage), sb_addr, kb * BLOCK_K, n0, pol_b);
-          } else {
-            // both CTAs' bytes are counted on the leader's barrier
-            const uint32_t leader_full = full_bar(stage) & 0xFEFFFFFFu;
-            if (is_leader) ptx::mbar_arrive_expect_tx(full_bar(stage), 2 * C::STAGE_BYTES);
-            ptx::tma_load_2d_pair(&tmap_a, leader_full, sa_addr, kb * BLOCK_K, m0, pol_a);
-            ptx::tma_load_2d_pair(&tmap_b, leader_full, sb_addr, kb * BLOCK_K, n0, pol_b);
+          if (ptx::elect_one()) {
+            if constexpr (kCG == 1) {
+              ptx::mbar_arrive_expect_tx(full_bar(stage), C::STAGE_BYTES);
+              ptx::tma_load_2d(&tmap_a, full_bar(stage), sa_addr, kb * BLOCK_K, m0, pol_a);
+              ptx::tma_load_2d(&tmap_b, full_bar(stage), sb_addr, kb * BLOCK_K, n0, pol_b);
+            } else {
+              // both CTAs' bytes are counted on the leader's barrier
+              const uint32_t leader_full = full_bar(stage) & 0xFEFFFFFFu;
+              if (is_leader) ptx::mbar_arrive_expect_tx(full_bar(stage), 2 * C::STAGE_BYTES);
+              ptx::tma_load_2d_pair(&tmap_a, leader_full, sa_addr, kb * BLOCK_K, m0, pol_a);
+              ptx::tma_load_2d_pair(&tmap_b, leader_full, sb_addr, kb * BLOCK_K, n0, pol_b);
+            }
           }
+          __syncwarp();
           if (++stage == kStages) { stage = 0; phase ^= 1; }
         }
       }
@@ -203,29 +210,39 @@ fp8_blockwise_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gr
   } else if (warp == 1) {
     // =========================== MMA issuer (leader CTA only) ===========================
     ptx::reg_dealloc<56>();
-    if (is_leader && lane == 0) {
+    // The whole warp walks the loop convergently and one elected lane issues: descriptors, barrier
+    // addresses and TMEM addresses then live in uniform registers (a lane-0-only branch made ptxas wrap
+    // every tcgen05.mma in an ELECT/R2UR loop and the issuing thread became the bottleneck — profile r1b).
+    if (is_leader) {
       constexpr uint32_t idesc = make_idesc(BLOCK_M * kCG, BLOCK_N);
+      const uint32_t tmem_base_u = __shfl_sync(0xFFFFFFFFu, tmem_base, 0);
+      const uint64_t desc_hi = make_smem_desc(0);
       int stage = 0, acc = 0;
       uint32_t phase = 0, acc_phase = 0;
       for (int tile = worker; tile < num_tiles; tile += num_workers) {
         for (int kb = 0; kb < num_kb; ++kb) {
           // accumulator stage drained by every epilogue warp (of both CTAs)?
-          ptx::mbar_wait(tempty_bar(acc), acc_phase ^ 1);
+          if (kDiag != 2 || kb == 0) ptx::mbar_wait(tempty_bar(acc), acc_phase ^ 1);
           ptx::mbar_wait(full_bar(stage), phase);
           ptx::tc_fence_after();
           const uint32_t sa_addr = smem_base + stage * C::STAGE_BYTES;
-          const uint64_t da = make_smem_desc(sa_addr);
-          const uint64_t db = make_smem_desc(sa_addr + C::A_BYTES);
-          const uint32_t d_tmem = tmem_base + uint32_t(acc * BLOCK_N);
+          const uint64_t da = desc_hi | uint64_t((sa_addr & 0x3FFFFu) >> 4);
+          const uint64_t db = desc_hi | uint64_t(((sa_addr + C::A_BYTES) & 0x3FFFFu) >> 4);
+          const uint32_t d_tmem = tmem_base_u + uint32_t(acc * BLOCK_N);
+          const bool last_of_tile = kDiag == 2 && kb + 1 < num_kb;
+          if (ptx::elect_one()) {
 #pragma unroll
-          for (int k = 0; k < BLOCK_K / UMMA_K; ++k) {
-            // +32 B along K inside the swizzle atom = +2 in the descriptor's 16-byte address units
-            ptx::mma_f8f6f4<kCG>(d_tmem, da + uint64_t(k * (UMMA_K >> 4)), db + uint64_t(k * (UMMA_K >> 4)), idesc,
-                                 k > 0 ? 1u : 0u);
+            for (int k = 0; k < BLOCK_K / UMMA_K; ++k) {
+              // +32 B along K inside the swizzle atom = +2 in the descriptor's 16-byte address units
+              ptx::mma_f8f6f4<kCG>(d_tmem, da + uint64_t(k * (UMMA_K >> 4)), db + uint64_t(k * (UMMA_K >> 4)), idesc,
+                                   (k > 0 || (kDiag == 2 && kb > 0)) ? 1u : 0u);
+            }
+            ptx::tc_commit<kCG>(empty_bar(stage));               // smem stage reusable once these MMAs have read it
+            if (!last_of_tile) ptx::tc_commit<kCG>(tfull_bar(acc));   // partial for this K block complete
           }
-          ptx::tc_commit<kCG>(empty_bar(stage));   // smem stage reusable once these MMAs have read it
-          ptx::tc_commit<kCG>(tfull_bar(acc));     // partial for this K block complete
+          __syncwarp();
           if (++stage == kStages) { stage = 0; phase ^= 1; }
+          if (last_of_tile) continue;
           if (++acc == kAccStages) { acc = 0; acc_phase ^= 1; }
         }
       }
@@ -278,13 +295,25 @@ fp8_blockwise_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gr
       };
       auto stage_addr = [&]() { return tmem_base + lane_base + uint32_t(acc * BLOCK_N + half * NC); };
       uint32_t v[2][32];
-      if constexpr (kDiagNoPromote) {        // diagnostic variant: TMA + MMA pipeline only, output is meaningless
+      if constexpr (kDiag == 1) {            // diagnostic: TMA + MMA pipeline with the per-block hand-off, no arithmetic
         for (int kb = 0; kb < num_kb; ++kb) {
           ptx::mbar_wait(tfull_bar(acc), acc_phase);
           ptx::tc_fence_after();
           accum[0] += sa0 * sb0 + float(stage_addr());
           release_stage();
         }
+      } else if constexpr (kDiag == 2) {     // diagnostic: unscaled GEMM, one hand-off per tile
+        ptx::mbar_wait(tfull_bar(acc), acc_phase);
+        ptx::tc_fence_after();
+        const uint32_t taddr = stage_addr();
+#pragma unroll
+        for (int c = 0; c < NCH; ++c) {
+          ptx::tmem_ld_32x32(taddr + uint32_t(c * 32), v[0]);
+          ptx::tmem_ld_wait(v[0]);
+#pragma unroll
+          for (int i = 0; i < 32; ++i) accum[c * 32 + i] = __uint_as_float(v[0][i]) * (sa0 * sb0);
+        }
+        release_stage();
       } else if constexpr (NCH % 2 == 0) {
         // Software pipeline across K blocks: chunk c+1 is in flight while chunk c is folded in, the
         // stage is released as soon as its last chunk is in registers (before that chunk's FMAs),
@@ -293,10 +322,7 @@ fp8_blockwise_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gr
         ptx::tc_fence_after();
         uint32_t taddr = stage_addr();
         ptx::tmem_ld_32x32(taddr, v[0]);
-        for (int kb = 0; kb < num_kb; ++kb) {
-          const float s = sa0 * sb0;
-          sa0 = sa1; sb0 = sb1;
-          sa1 = ld_sa(kb + 2); sb1 = ld_sb(kb + 2);
+        auto promote = [&](const float s, const bool more) {
 #pragma unroll
           for (int c = 0; c < NCH; ++c) {
             ptx::tmem_ld_wait(v[c & 1]);
@@ -305,7 +331,7 @@ fp8_blockwise_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gr
               ptx::tmem_ld_32x32(taddr + uint32_t((c + 1) * 32), v[(c + 1) & 1]);
             } else {
               release_stage();
-              if (kb + 1 < num_kb) {
+              if (more) {
                 taddr = stage_addr();
                 if (ptx::mbar_try_wait(tfull_bar(acc), acc_phase)) {
                   ptx::tc_fence_after();
@@ -323,6 +349,18 @@ fp8_blockwise_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gr
               ptx::tc_fence_after();
               ptx::tmem_ld_32x32(taddr, v[0]);
             }
+          }
+        };
+        // two K blocks per trip so the scale registers rotate by name (no register moves that would
+        // touch a load still in flight): each pair is reloaded right after its use, two blocks ahead
+        for (int kb = 0; kb < num_kb; kb += 2) {
+          const float s_even = sa0 * sb0;
+          sa0 = ld_sa(kb + 2); sb0 = ld_sb(kb + 2);
+          promote(s_even, kb + 1 < num_kb);
+          if (kb + 1 < num_kb) {
+            const float s_odd = sa1 * sb1;
+            sa1 = ld_sa(kb + 3); sb1 = ld_sb(kb + 3);
+            promote(s_odd, kb + 2 < num_kb);
           }
         }
       } else {
@@ -453,16 +491,20 @@ static const Variant kVariants[] = {
     {"n256_s6_cta2_direct", 256, 6, 2, false},
     {"n128_s8_cta2_tma", 128, 8, 2, true},
     {"n64_s8_cta1_direct", 64, 8, 1, false},
-    {"diag_n256_s6_cta2_mma_only", 256, 6, 2, false},   // NOT a product path: skips promotion, wrong results
+    {"diag_n256_s6_cta2_nopromote", 256, 6, 2, false},   // NOT product paths: diagnostics with wrong results
+    {"diag_n256_s6_cta2_plain_gemm", 256, 6, 2, true},
+    {"diag_n256_s7_cta2_plain_gemm", 256, 7, 2, false},
+    {"diag_n256_s4_cta2_plain_gemm", 256, 4, 2, false},
+    {"diag_n256_s7_cta2_nopromote", 256, 7, 2, false},
 };
 constexpr int kNumVariants = int(sizeof(kVariants) / sizeof(kVariants[0]));
 
-template <int BLOCK_N, int kStages, int kCG, typename OutT, bool kTmaStore, bool kDiag = false>
+template <int BLOCK_N, int kStages, int kCG, typename OutT, bool kTmaStore, int kDiag = 0>
 static int launch_variant(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& tc, const GemmParams& p,
                           int num_sms, cudaStream_t st) {
   using C = Cfg<BLOCK_N, kCG>;
   auto kern = fp8_blockwise_gemm_kernel<BLOCK_N, kStages, kCG, OutT, kTmaStore, kDiag>;
-  constexpr int smem = C::smem_bytes(kStages);
+  constexpr int smem = C::smem_bytes(kStages, kTmaStore);
   static_assert(smem <= 232448, "shared memory budget");
   static bool configured = false;   // per instantiation
   if (!configured) {
@@ -501,7 +543,11 @@ static int launch_by_id(int v, const CUtensorMap& ta, const CUtensorMap& tb, con
     case 4: return launch_variant<256, 6, 2, OutT, false>(ta, tb, tc, p, num_sms, st);
     case 5: return launch_variant<128, 8, 2, OutT, true>(ta, tb, tc, p, num_sms, st);
     case 6: return launch_variant<64, 8, 1, OutT, false>(ta, tb, tc, p, num_sms, st);
-    case 7: return launch_variant<256, 6, 2, OutT, false, true>(ta, tb, tc, p, num_sms, st);
+    case 7: return launch_variant<256, 6, 2, OutT, false, 1>(ta, tb, tc, p, num_sms, st);
+    case 8: return launch_variant<256, 6, 2, OutT, true, 2>(ta, tb, tc, p, num_sms, st);
+    case 9: return launch_variant<256, 7, 2, OutT, false, 2>(ta, tb, tc, p, num_sms, st);
+    case 10: return launch_variant<256, 4, 2, OutT, false, 2>(ta, tb, tc, p, num_sms, st);
+    case 11: return launch_variant<256, 7, 2, OutT, false, 1>(ta, tb, tc, p, num_sms, st);
     default: return SGLK_E_VARIANT;
   }
 }
