@@ -27,6 +27,10 @@ sys.path[:0] = [ROOT, os.path.join(ROOT, "sgl-kernel-xpu_b200")]
 M_FULL, N_FULL, K_FULL = 16384, 18432, 7168
 WORKLOAD = "dsv3_dense_mlp_prefill_M16384_N18432_K7168_group128"
 METRIC = "FP8 blockwise GEMM TFLOPS (% dense-FP8 peak); group-quant GB/s (% HBM)"
+# dram__bytes_read.sum + dram__bytes_write.sum per launch from the `ncu --set full` captures of this command
+# (profiles/r01_gemm_ncu_metrics.csv, profiles/r01_quant_ncu_metrics.csv); algorithmic: 853 MB / 356 MB
+GEMM_DRAM_TRAFFIC_BYTES = 1_188_787_000 + 585_974_784
+QUANT_DRAM_TRAFFIC_BYTES = 234_941_440 + 66_020_608
 FP8_NOMINAL_TFLOPS = 4500.0
 HBM_NOMINAL_GBS = 8000.0
 
@@ -81,7 +85,7 @@ class ClockSampler(threading.Thread):
                         self.reasons.add(nm)
             except Exception:  # noqa: BLE001
                 pass
-            time.sleep(0.02)
+            time.sleep(0.001)
 
     def stop(self):
         self._stop_evt.set()
@@ -91,7 +95,7 @@ class ClockSampler(threading.Thread):
                 "reasons": sorted(self.reasons), "samples": len(s)}
 
 
-def cpu_oracle_sample(rows, reps_budget_s=12.0, min_reps=2, max_reps=8):
+def cpu_oracle_sample(rows, reps_budget_s=12.0, min_reps=2, max_reps=16):
     """Time the CPU oracle (quant + dequantised matmul, all host threads) on the first `rows` tokens of
     the workload.  Returns (best seconds, reps, threads)."""
     import torch
@@ -143,10 +147,10 @@ def run_reference(args, rank, world):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--steps", type=int, default=50)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--cpu-rows", type=int, default=256, help="tokens in the CPU-oracle sample")
+    ap.add_argument("--cpu-rows", type=int, default=1024, help="tokens in the CPU-oracle sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--m", type=int, default=M_FULL, help="debug only: override token count")
@@ -310,12 +314,14 @@ def main():
         "gemm_tflops": 2.0 * M * N * K / (t_gemm * 1e-3) / 1e12, "gemm_ms": t_gemm,
         "quant_gbps": quant_gbs, "quant_ms": t_quant,
         "roofline": {"bound": "tensor", "achieved": gemm_tflops_rank, "peak": fp8_peak, "unit": "TFLOP/s",
-                     "frac": gemm_tflops_rank / fp8_peak, "traffic": None,
+                     "frac": gemm_tflops_rank / fp8_peak,
+                     "traffic": (GEMM_DRAM_TRAFFIC_BYTES if (world == 1 and M == M_FULL) else None),
                      "kernel": "fp8_blockwise_gemm_kernel", "algorithmic_flops_per_launch": 2.0 * M * n_loc * K,
                      "peak_source": f"2 x {peaks['source']} cuBLAS bf16 burst ({peaks['bf16_tflops']} TF/s): fp8 dense = 2x bf16 rate; "
                                     f"frac of nominal 4500 TF/s = {gemm_tflops_rank / FP8_NOMINAL_TFLOPS:.3f}"},
         "roofline_quant": {"bound": "hbm", "achieved": quant_gbs, "peak": peaks["hbm_gbs"], "unit": "GB/s",
-                           "frac": quant_gbs / peaks["hbm_gbs"], "traffic": None, "kernel": "ptgq_kernel",
+                           "frac": quant_gbs / peaks["hbm_gbs"],
+                           "traffic": (QUANT_DRAM_TRAFFIC_BYTES if M == M_FULL else None), "kernel": "ptgq_kernel",
                            "algorithmic_bytes_per_launch": quant_bytes,
                            "peak_source": f"{peaks['source']} copy bandwidth; frac of nominal 8000 GB/s = {quant_gbs / HBM_NOMINAL_GBS:.3f}"},
         "cpu_baseline": cpu_baseline, "e2e": e2e, "with_all_gather": with_gather,
