@@ -128,14 +128,22 @@ SGLK_API int sglk_fp8_blockwise_scaled_mm(const void* A, const void* B, const fl
                                  int64_t sb_stride_k, int64_t sb_stride_n, int out_dtype,
                                  void* stream);
 
-/* Same, with an explicit kernel variant (tile shape / CTA pairing) for tests and tuning.
- * variant = -1 selects the heuristic used by sglk_fp8_blockwise_scaled_mm.
- * num_sms <= 0 uses every SM of the current device. */
+/* Same, with an explicit kernel variant (tile shape / CTA pairing) for tests and tuning, and an
+ * optional device workspace that enables stream-K scheduling (decode shapes, ragged last waves):
+ * variant = -1 selects the heuristic used by sglk_fp8_blockwise_scaled_mm;
+ * num_sms <= 0 uses every SM of the current device;
+ * workspace: >= sglk_gemm_workspace_bytes(...) bytes, 16-byte aligned, whose first MiB (the tile
+ * counters) is ZERO on entry — the kernel leaves it zero, so one zero-initialised buffer can be
+ * reused by consecutive launches (of any shape) on the same stream.  NULL disables stream-K. */
 SGLK_API int sglk_fp8_blockwise_scaled_mm_ex(const void* A, const void* B, const float* sa, const float* sb,
                                     void* C, int64_t M, int64_t N, int64_t K, int64_t lda,
                                     int64_t ldb, int64_t ldc, int64_t sa_stride_m,
                                     int64_t sa_stride_k, int64_t sb_stride_k, int64_t sb_stride_n,
-                                    int out_dtype, int variant, int num_sms, void* stream);
+                                    int out_dtype, int variant, int num_sms, void* workspace,
+                                    int64_t workspace_bytes, void* stream);
+
+/* bytes of workspace with which the call above would use stream-K (0: it would not) */
+SGLK_API int64_t sglk_gemm_workspace_bytes(int64_t M, int64_t N, int64_t K, int variant, int num_sms);
 
 /* number of GEMM variants compiled in, and a printable name for each ("" if out of range) */
 SGLK_API int sglk_gemm_num_variants(void);

@@ -38,6 +38,8 @@ constexpr int UMMA_K = 32;     // K per tcgen05.mma for 8-bit operands
 constexpr int kNumEpiWarps = 8;
 constexpr int kNumThreads = 128 + kNumEpiWarps * 32;   // 4 control warps + 8 epilogue warps
 constexpr int kStoreBoxCols = 64;                      // bf16 columns per TMA store box (128 B)
+constexpr int kMaxStages = 16;                         // barrier slots reserved for the smem ring
+constexpr int kMaxDynSmem = 232448;                    // 227 KB
 
 struct GemmParams {
   const float* sa;
@@ -48,6 +50,51 @@ struct GemmParams {
   int64_t sa_sm, sa_sk, sb_sk, sb_sn;
   int32_t num_m_blocks, num_n_blocks, num_k_blocks, num_sb_cols;
   int32_t group_m;   // tile rasterisation: tiles of `group_m` consecutive m-blocks share B panels in L2
+  // stream-K (decode shapes / ragged waves): the (tile, K-block) units are cut into one contiguous
+  // range per worker; tiles shared by several workers are summed through `ws_partials` by whichever
+  // worker arrives last (fixed summation order -> deterministic)
+  int32_t stream_k;
+  uint32_t stage_tx_bytes;   // bytes TMA delivers per stage to the (leader's) full barrier
+  uint32_t stage_bytes;      // smem bytes of one ring stage = a_slot_bytes + B tile bytes (multiple of 1024)
+  uint32_t a_slot_bytes;     // smem reserved for the A tile of a stage (rows that exist, rounded to 1 KB)
+  int32_t num_stages;
+  int32_t* ws_counters;   // [num_tiles][kCG*8], zero on entry, reset by the reducer
+  float* ws_partials;     // [2*workers][kCG*8][NC/4][32] float4
+};
+
+// One worker's walk over its share of the problem: whole tiles round-robin, or a contiguous range of
+// (tile, K-block) units.  Producer, MMA issuer and epilogue warps all run the same iterator.
+struct WorkIter {
+  int64_t cur, end;
+  int step, num_kb;
+  bool stream_k;
+  __device__ WorkIter(const GemmParams& p, int worker, int num_workers, int num_tiles) {
+    num_kb = p.num_k_blocks;
+    stream_k = p.stream_k != 0;
+    if (stream_k) {
+      const int64_t total = int64_t(num_tiles) * num_kb;
+      cur = total * worker / num_workers;
+      end = total * (worker + 1) / num_workers;
+      step = 0;
+    } else {
+      cur = worker; end = num_tiles; step = num_workers;
+    }
+  }
+  // next segment: tile index and K-block range [kb0, kb1); `first` = first segment of this worker
+  __device__ bool next(int& tile, int& kb0, int& kb1) {
+    if (cur >= end) return false;
+    if (stream_k) {
+      tile = int(cur / num_kb);
+      kb0 = int(cur - int64_t(tile) * num_kb);
+      const int64_t left = end - cur;
+      kb1 = left < int64_t(num_kb - kb0) ? kb0 + int(left) : num_kb;
+      cur += kb1 - kb0;
+    } else {
+      tile = int(cur); kb0 = 0; kb1 = num_kb;
+      cur += step;
+    }
+    return true;
+  }
 };
 
 template <int BLOCK_N, int kCG>
@@ -124,13 +171,17 @@ fp8_blockwise_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gr
   extern __shared__ uint8_t smem_raw[];
   // 128B-swizzled TMA/UMMA tiles need 1024-byte alignment
   const uint32_t smem_base = (ptx::smem_u32(smem_raw) + 1023u) & ~1023u;
-  const uint32_t smem_store = smem_base + kStages * C::STAGE_BYTES;
+  // the ring is sized on the host: `num_stages` stages of `stage_bytes` (A slot cut to the rows that
+  // exist for decode shapes, so more weight bytes are in flight), at most kMaxStages
+  const int nstages = p.num_stages;
+  const uint32_t stage_bytes = p.stage_bytes;
+  const uint32_t smem_store = smem_base + uint32_t(nstages) * stage_bytes;
   const uint32_t bar_base = smem_store + (kTmaStore ? C::STORE_BYTES : 0);
   auto full_bar = [&](int s) { return bar_base + 8u * s; };
-  auto empty_bar = [&](int s) { return bar_base + 8u * (kStages + s); };
-  auto tfull_bar = [&](int s) { return bar_base + 8u * (2 * kStages + s); };
-  auto tempty_bar = [&](int s) { return bar_base + 8u * (2 * kStages + kAccStages + s); };
-  const uint32_t tmem_slot = bar_base + 8u * (2 * kStages + 2 * kAccStages);
+  auto empty_bar = [&](int s) { return bar_base + 8u * (kMaxStages + s); };
+  auto tfull_bar = [&](int s) { return bar_base + 8u * (2 * kMaxStages + s); };
+  auto tempty_bar = [&](int s) { return bar_base + 8u * (2 * kMaxStages + kAccStages + s); };
+  const uint32_t tmem_slot = bar_base + 8u * (2 * kMaxStages + 2 * kAccStages);
   uint8_t* smem_gen = smem_raw + (smem_base - ptx::smem_u32(smem_raw));   // generic pointer to smem_base
 
   const int warp = threadIdx.x >> 5;
@@ -144,7 +195,7 @@ fp8_blockwise_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gr
     if (kTmaStore) ptx::prefetch_tensormap(&tmap_c);
   }
   if (warp == 1 && lane == 0) {
-    for (int s = 0; s < kStages; ++s) {
+    for (int s = 0; s < nstages; ++s) {
       ptx::mbar_init(full_bar(s), 1);                    // one arrive.expect_tx by the (leader's) producer
       ptx::mbar_init(empty_bar(s), 1);                   // one tcgen05.commit
     }
@@ -179,30 +230,32 @@ fp8_blockwise_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gr
       const uint64_t pol_b = ptx::policy_evict_normal();
       int stage = 0;
       uint32_t phase = 0;
-      for (int tile = worker; tile < num_tiles; tile += num_workers) {
+      WorkIter it(p, worker, num_workers, num_tiles);
+      int tile, kb0, kb1;
+      while (it.next(tile, kb0, kb1)) {
         int mb, nb;
         tile_coords(tile, p, mb, nb);
         const int m0 = mb * (BLOCK_M * kCG) + int(cta_rank) * BLOCK_M;
         const int n0 = nb * BLOCK_N + int(cta_rank) * C::LOAD_N;
-        for (int kb = 0; kb < num_kb; ++kb) {
+        for (int kb = kb0; kb < kb1; ++kb) {
           ptx::mbar_wait(empty_bar(stage), phase ^ 1);
-          const uint32_t sa_addr = smem_base + stage * C::STAGE_BYTES;
-          const uint32_t sb_addr = sa_addr + C::A_BYTES;
+          const uint32_t sa_addr = smem_base + stage * stage_bytes;
+          const uint32_t sb_addr = sa_addr + p.a_slot_bytes;
           if (ptx::elect_one()) {
             if constexpr (kCG == 1) {
-              ptx::mbar_arrive_expect_tx(full_bar(stage), C::STAGE_BYTES);
+              ptx::mbar_arrive_expect_tx(full_bar(stage), p.stage_tx_bytes);
               ptx::tma_load_2d(&tmap_a, full_bar(stage), sa_addr, kb * BLOCK_K, m0, pol_a);
               ptx::tma_load_2d(&tmap_b, full_bar(stage), sb_addr, kb * BLOCK_K, n0, pol_b);
             } else {
               // both CTAs' bytes are counted on the leader's barrier
               const uint32_t leader_full = full_bar(stage) & 0xFEFFFFFFu;
-              if (is_leader) ptx::mbar_arrive_expect_tx(full_bar(stage), 2 * C::STAGE_BYTES);
+              if (is_leader) ptx::mbar_arrive_expect_tx(full_bar(stage), p.stage_tx_bytes);
               ptx::tma_load_2d_pair(&tmap_a, leader_full, sa_addr, kb * BLOCK_K, m0, pol_a);
               ptx::tma_load_2d_pair(&tmap_b, leader_full, sb_addr, kb * BLOCK_K, n0, pol_b);
             }
           }
           __syncwarp();
-          if (++stage == kStages) { stage = 0; phase ^= 1; }
+          if (++stage == nstages) { stage = 0; phase ^= 1; }
         }
       }
     }
@@ -219,29 +272,31 @@ fp8_blockwise_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gr
       const uint64_t desc_hi = make_smem_desc(0);
       int stage = 0, acc = 0;
       uint32_t phase = 0, acc_phase = 0;
-      for (int tile = worker; tile < num_tiles; tile += num_workers) {
-        for (int kb = 0; kb < num_kb; ++kb) {
+      WorkIter it(p, worker, num_workers, num_tiles);
+      int tile, kb0, kb1;
+      while (it.next(tile, kb0, kb1)) {
+        for (int kb = kb0; kb < kb1; ++kb) {
           // accumulator stage drained by every epilogue warp (of both CTAs)?
-          if (kDiag != 2 || kb == 0) ptx::mbar_wait(tempty_bar(acc), acc_phase ^ 1);
+          if (kDiag != 2 || kb == kb0) ptx::mbar_wait(tempty_bar(acc), acc_phase ^ 1);
           ptx::mbar_wait(full_bar(stage), phase);
           ptx::tc_fence_after();
-          const uint32_t sa_addr = smem_base + stage * C::STAGE_BYTES;
+          const uint32_t sa_addr = smem_base + stage * stage_bytes;
           const uint64_t da = desc_hi | uint64_t((sa_addr & 0x3FFFFu) >> 4);
-          const uint64_t db = desc_hi | uint64_t(((sa_addr + C::A_BYTES) & 0x3FFFFu) >> 4);
+          const uint64_t db = desc_hi | uint64_t(((sa_addr + p.a_slot_bytes) & 0x3FFFFu) >> 4);
           const uint32_t d_tmem = tmem_base_u + uint32_t(acc * BLOCK_N);
-          const bool last_of_tile = kDiag == 2 && kb + 1 < num_kb;
+          const bool last_of_tile = kDiag == 2 && kb + 1 < kb1;
           if (ptx::elect_one()) {
 #pragma unroll
             for (int k = 0; k < BLOCK_K / UMMA_K; ++k) {
               // +32 B along K inside the swizzle atom = +2 in the descriptor's 16-byte address units
               ptx::mma_f8f6f4<kCG>(d_tmem, da + uint64_t(k * (UMMA_K >> 4)), db + uint64_t(k * (UMMA_K >> 4)), idesc,
-                                   (k > 0 || (kDiag == 2 && kb > 0)) ? 1u : 0u);
+                                   (k > 0 || (kDiag == 2 && kb > kb0)) ? 1u : 0u);
             }
             ptx::tc_commit<kCG>(empty_bar(stage));               // smem stage reusable once these MMAs have read it
             if (!last_of_tile) ptx::tc_commit<kCG>(tfull_bar(acc));   // partial for this K block complete
           }
           __syncwarp();
-          if (++stage == kStages) { stage = 0; phase ^= 1; }
+          if (++stage == nstages) { stage = 0; phase ^= 1; }
           if (last_of_tile) continue;
           if (++acc == kAccStages) { acc = 0; acc_phase ^= 1; }
         }
@@ -261,7 +316,10 @@ fp8_blockwise_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gr
     const uint32_t my_store = smem_store + ew * (32 * kStoreBoxCols * 2);
     int acc = 0;
     uint32_t acc_phase = 0;
-    for (int tile = worker; tile < num_tiles; tile += num_workers) {
+    WorkIter it(p, worker, num_workers, num_tiles);
+    int tile, kb0, kb1;
+    bool first_segment = true;
+    while (it.next(tile, kb0, kb1)) {
       int mb, nb;
       tile_coords(tile, p, mb, nb);
       const int m0 = mb * (BLOCK_M * kCG) + int(cta_rank) * BLOCK_M;
@@ -279,9 +337,9 @@ fp8_blockwise_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gr
       // Scale prefetch, two K blocks ahead, kept as raw loads: the product is formed only at the top
       // of the iteration that uses it, so no instruction ever waits on an in-flight global load
       // (an in-order warp that multiplies right after the load stalls ~1 us per K block — measured).
-      auto ld_sa = [&](int kb) { return (row_ok && kb < num_kb) ? __ldg(sa_ptr + int64_t(kb) * p.sa_sk) : 0.0f; };
-      auto ld_sb = [&](int kb) { return kb < num_kb ? __ldg(sb_ptr + int64_t(kb) * p.sb_sk) : 0.0f; };
-      float sa0 = ld_sa(0), sb0 = ld_sb(0), sa1 = ld_sa(1), sb1 = ld_sb(1);
+      auto ld_sa = [&](int kb) { return (row_ok && kb < kb1) ? __ldg(sa_ptr + int64_t(kb) * p.sa_sk) : 0.0f; };
+      auto ld_sb = [&](int kb) { return kb < kb1 ? __ldg(sb_ptr + int64_t(kb) * p.sb_sk) : 0.0f; };
+      float sa0 = ld_sa(kb0), sb0 = ld_sb(kb0), sa1 = ld_sa(kb0 + 1), sb1 = ld_sb(kb0 + 1);
       constexpr int NCH = NC / 32;           // 32-column TMEM chunks per K block for this warp
       auto release_stage = [&]() {
         // every tcgen05.ld of this warp on the stage has completed: hand it back to the MMA issuer
@@ -296,7 +354,7 @@ fp8_blockwise_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gr
       auto stage_addr = [&]() { return tmem_base + lane_base + uint32_t(acc * BLOCK_N + half * NC); };
       uint32_t v[2][32];
       if constexpr (kDiag == 1) {            // diagnostic: TMA + MMA pipeline with the per-block hand-off, no arithmetic
-        for (int kb = 0; kb < num_kb; ++kb) {
+        for (int kb = kb0; kb < kb1; ++kb) {
           ptx::mbar_wait(tfull_bar(acc), acc_phase);
           ptx::tc_fence_after();
           accum[0] += sa0 * sb0 + float(stage_addr());
@@ -353,18 +411,18 @@ fp8_blockwise_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gr
         };
         // two K blocks per trip so the scale registers rotate by name (no register moves that would
         // touch a load still in flight): each pair is reloaded right after its use, two blocks ahead
-        for (int kb = 0; kb < num_kb; kb += 2) {
+        for (int kb = kb0; kb < kb1; kb += 2) {
           const float s_even = sa0 * sb0;
           sa0 = ld_sa(kb + 2); sb0 = ld_sb(kb + 2);
-          promote(s_even, kb + 1 < num_kb);
-          if (kb + 1 < num_kb) {
+          promote(s_even, kb + 1 < kb1);
+          if (kb + 1 < kb1) {
             const float s_odd = sa1 * sb1;
             sa1 = ld_sa(kb + 3); sb1 = ld_sb(kb + 3);
-            promote(s_odd, kb + 2 < num_kb);
+            promote(s_odd, kb + 2 < kb1);
           }
         }
       } else {
-        for (int kb = 0; kb < num_kb; ++kb) {
+        for (int kb = kb0; kb < kb1; ++kb) {
           const float s = sa0 * sb0;
           sa0 = sa1; sb0 = sb1;
           sa1 = ld_sa(kb + 2); sb1 = ld_sb(kb + 2);
@@ -384,7 +442,52 @@ fp8_blockwise_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gr
           }
         }
       }
+      // ---------------- stream-K: a tile shared with other workers is completed by the last arriver ----------------
+      bool write_out = true;
+      if (p.stream_k && (kb0 != 0 || kb1 != num_kb)) {
+        const int64_t total = int64_t(num_tiles) * num_kb;
+        auto range_begin = [&](int w) { return total * w / num_workers; };
+        auto owner = [&](int64_t u) { return int(((u + 1) * num_workers + total - 1) / total) - 1; };
+        const int c_first = owner(int64_t(tile) * num_kb), c_last = owner(int64_t(tile + 1) * num_kb - 1);
+        auto slot_of = [&](int c) { return 2 * c + ((int(range_begin(c) / num_kb) == tile) ? 0 : 1); };
+        constexpr int kWarpFloats = NC * 32;                         // one warp's 32 x NC partial
+        auto part_ptr = [&](int c) {
+          return p.ws_partials + (int64_t(slot_of(c)) * (kCG * kNumEpiWarps) + int(cta_rank) * kNumEpiWarps + ew) * kWarpFloats;
+        };
+        (void)first_segment;
+        float4* mine = reinterpret_cast<float4*>(part_ptr(worker));
+        if (row_ok) {
+#pragma unroll
+          for (int j = 0; j < NC / 4; ++j)
+            __stcg(mine + j * 32 + lane, make_float4(accum[4 * j], accum[4 * j + 1], accum[4 * j + 2], accum[4 * j + 3]));
+        }
+        __threadfence();
+        __syncwarp();
+        int32_t* cnt = p.ws_counters + int64_t(tile) * (kCG * kNumEpiWarps) + int(cta_rank) * kNumEpiWarps + ew;
+        int arrived = 0;
+        if (lane == 0) arrived = atomicAdd(cnt, 1);
+        arrived = __shfl_sync(0xFFFFFFFFu, arrived, 0);
+        write_out = arrived == c_last - c_first;                     // everyone else's partial is already visible
+        if (write_out) {
+          __threadfence();
+          if (lane == 0) *cnt = 0;                                   // leave the counters zeroed for the next launch
+#pragma unroll
+          for (int i = 0; i < NC; ++i) accum[i] = 0.0f;
+          for (int c = c_first; c <= c_last; ++c) {                  // fixed order: bit-reproducible
+            const float4* src = reinterpret_cast<const float4*>(part_ptr(c));
+            if (row_ok) {
+#pragma unroll
+              for (int j = 0; j < NC / 4; ++j) {
+                const float4 t = __ldcg(src + j * 32 + lane);
+                accum[4 * j] += t.x; accum[4 * j + 1] += t.y; accum[4 * j + 2] += t.z; accum[4 * j + 3] += t.w;
+              }
+            }
+          }
+        }
+      }
+      first_segment = false;
       // ---------------- write the finished 32 x NC sub-tile ----------------
+      if (!write_out) continue;
       if constexpr (kTmaStore) {
 #pragma unroll
         for (int cb = 0; cb < NC / kStoreBoxCols; ++cb) {
@@ -498,24 +601,22 @@ static const Variant kVariants[] = {
     {"diag_n256_s7_cta2_nopromote", 256, 7, 2, false},
 };
 constexpr int kNumVariants = int(sizeof(kVariants) / sizeof(kVariants[0]));
+constexpr int kNumProductVariants = 7;   // the rest are diagnostics
+constexpr int64_t kCounterAreaBytes = 1 << 20;   // first MiB of a stream-K workspace: tile counters (zero between launches)
 
 template <int BLOCK_N, int kStages, int kCG, typename OutT, bool kTmaStore, int kDiag = 0>
 static int launch_variant(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& tc, const GemmParams& p,
-                          int num_sms, cudaStream_t st) {
+                          int workers, cudaStream_t st) {
   using C = Cfg<BLOCK_N, kCG>;
   auto kern = fp8_blockwise_gemm_kernel<BLOCK_N, kStages, kCG, OutT, kTmaStore, kDiag>;
-  constexpr int smem = C::smem_bytes(kStages, kTmaStore);
-  static_assert(smem <= 232448, "shared memory budget");
+  constexpr int smem = kMaxDynSmem;
+  (void)sizeof(C);
   static bool configured = false;   // per instantiation
   if (!configured) {
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
     if (e != cudaSuccess) return int(e);
     configured = true;
   }
-  const int tiles = p.num_m_blocks * p.num_n_blocks;
-  int workers = num_sms / kCG;
-  if (workers > tiles) workers = tiles;
-  if (workers < 1) workers = 1;
   cudaLaunchConfig_t cfg;
   memset(&cfg, 0, sizeof(cfg));
   cfg.gridDim = dim3(unsigned(workers * kCG));
@@ -534,7 +635,7 @@ static int launch_variant(const CUtensorMap& ta, const CUtensorMap& tb, const CU
 
 template <typename OutT>
 static int launch_by_id(int v, const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& tc,
-                        const GemmParams& p, int num_sms, cudaStream_t st) {
+                        const GemmParams& p, int num_sms, cudaStream_t st) {   // num_sms == workers here
   switch (v) {
     case 0: return launch_variant<128, 6, 1, OutT, true>(ta, tb, tc, p, num_sms, st);
     case 1: return launch_variant<128, 6, 1, OutT, false>(ta, tb, tc, p, num_sms, st);
@@ -558,16 +659,48 @@ static bool tma_store_ok(const void* C, int64_t ldc, int out_bytes) {
 
 static int pick_variant(int64_t M, int64_t N, int64_t K) {
   (void)K;
-  if (M > 128 && N >= 256 && M * N >= int64_t(148) * 128 * 256) return 3;   // paired 256x256 tiles
-  if (M > 128) return 0;
-  // decode: weight streaming; more, narrower tiles keep every SM pulling on HBM
-  if (N >= 148 * 128) return 0;
-  return 6;
+  if (M > 128 && N >= 256) return 3;   // paired 256x256 tiles (one pair covers 256 rows)
+  // M <= 128 (decode): one m-block; 128-wide tiles, balanced over the SMs by stream-K
+  return 0;
+}
+
+struct Plan {
+  int variant, workers, stream_k;
+  int32_t num_m_blocks, num_n_blocks, num_k_blocks;
+  int64_t counter_bytes, partial_bytes;
+};
+
+// Tile shape, worker count and whether to cut the work stream-K style.  Stream-K is used when whole
+// tiles would leave the last wave under 90 % full (decode shapes: N=24576 -> 1.3 waves of 128-wide
+// tiles, N=2112 -> 17 tiles for 148 SMs) and a workspace is available.
+static Plan make_plan(int64_t M, int64_t N, int64_t K, int variant, int num_sms, bool have_ws) {
+  Plan pl;
+  pl.variant = variant;
+  const Variant v = kVariants[variant];
+  pl.num_m_blocks = int32_t((M + BLOCK_M * v.cg - 1) / (BLOCK_M * v.cg));
+  pl.num_n_blocks = int32_t((N + v.block_n - 1) / v.block_n);
+  pl.num_k_blocks = int32_t((K + BLOCK_K - 1) / BLOCK_K);
+  const int64_t tiles = int64_t(pl.num_m_blocks) * pl.num_n_blocks;
+  int w0 = num_sms / v.cg;
+  if (w0 < 1) w0 = 1;
+  const int64_t waves = (tiles + w0 - 1) / w0;
+  const double eff = double(tiles) / double(waves * w0);
+  const int64_t units = tiles * pl.num_k_blocks;
+  pl.stream_k = (have_ws && variant < kNumProductVariants && pl.num_k_blocks >= 2 && eff < 0.9 && units >= w0) ? 1 : 0;
+  pl.workers = int(pl.stream_k ? w0 : (tiles < w0 ? tiles : w0));
+  if (pl.workers < 1) pl.workers = 1;
+  // the counter area has a FIXED size so that launches with different tilings can share one workspace:
+  // partials of one launch must never land where another launch expects zeroed counters
+  pl.counter_bytes = kCounterAreaBytes;
+  if (tiles * v.cg * kNumEpiWarps * 4 > kCounterAreaBytes) { pl.stream_k = 0; pl.workers = int(tiles < w0 ? tiles : w0); }
+  pl.partial_bytes = int64_t(2) * pl.workers * v.cg * kNumEpiWarps * 32 * (v.block_n / 2) * 4;
+  return pl;
 }
 
 static int gemm_entry(const void* A, const void* B, const float* sa, const float* sb, void* Cout, int64_t M,
                       int64_t N, int64_t K, int64_t lda, int64_t ldb, int64_t ldc, int64_t sa_sm, int64_t sa_sk,
-                      int64_t sb_sk, int64_t sb_sn, int out_dtype, int variant, int num_sms, void* stream) {
+                      int64_t sb_sk, int64_t sb_sn, int out_dtype, int variant, int num_sms, void* workspace,
+                      int64_t workspace_bytes, void* stream) {
   if (M < 0 || N < 0 || K < 0) return SGLK_E_SHAPE;
   if (out_dtype != SGLK_BF16 && out_dtype != SGLK_F16) return SGLK_E_DTYPE;
   if (M == 0 || N == 0) return SGLK_OK;
@@ -595,14 +728,38 @@ static int gemm_entry(const void* A, const void* B, const float* sa, const float
   p.sa = sa; p.sb = sb; p.C = Cout;
   p.M = M; p.N = N; p.K = K; p.ldc = ldc;
   p.sa_sm = sa_sm; p.sa_sk = sa_sk; p.sb_sk = sb_sk; p.sb_sn = sb_sn;
-  p.num_m_blocks = int32_t((M + BLOCK_M * v.cg - 1) / (BLOCK_M * v.cg));
-  p.num_n_blocks = int32_t((N + v.block_n - 1) / v.block_n);
-  p.num_k_blocks = int32_t((K + BLOCK_K - 1) / BLOCK_K);
+  Plan pl = make_plan(M, N, K, variant, num_sms, workspace != nullptr);
+  if (pl.stream_k && (workspace_bytes < pl.counter_bytes + pl.partial_bytes || (reinterpret_cast<uintptr_t>(workspace) & 15)))
+    pl = make_plan(M, N, K, variant, num_sms, false);
+  p.num_m_blocks = pl.num_m_blocks;
+  p.num_n_blocks = pl.num_n_blocks;
+  p.num_k_blocks = pl.num_k_blocks;
   p.num_sb_cols = int32_t((N + 127) / 128);
   p.group_m = 8;
+  p.stream_k = pl.stream_k;
+  p.ws_counters = pl.stream_k ? static_cast<int32_t*>(workspace) : nullptr;
+  p.ws_partials = pl.stream_k ? reinterpret_cast<float*>(static_cast<char*>(workspace) + pl.counter_bytes) : nullptr;
 
+  // Decode (M < 128): only load the rows that exist.  TMA zero-fills out-of-bounds rows of a box at
+  // ~20 clk per row (measured: M=1 ran 2x slower than M=128), so the A box is cut to round_up(M, 8) rows;
+  // the MMA still reads 128 rows of smem, the stale ones only feed accumulator lanes that are never stored.
+  const uint32_t a_rows = (v.cg == 1 && M < BLOCK_M) ? uint32_t((M + 7) / 8 * 8) : uint32_t(BLOCK_M);
+  const uint32_t b_bytes = uint32_t(v.block_n / v.cg) * BLOCK_K;
+  p.stage_tx_bytes = uint32_t(v.cg) * (a_rows * BLOCK_K + b_bytes);
+  p.a_slot_bytes = (a_rows * BLOCK_K + 1023u) & ~1023u;
+  p.stage_bytes = p.a_slot_bytes + b_bytes;
+  {
+    // what follows the ring: the TMA-store staging boxes, or (direct store) nothing — but the MMA reads a
+    // full 16 KB of A rows from every stage, so the last stage needs that much addressable smem behind it
+    const int tail = v.tma_store ? 32768 : 16384;
+    int n = (kMaxDynSmem - 1024 /*alignment slack*/ - 1024 /*barriers*/ - tail) / int(p.stage_bytes);
+    if (n > kMaxStages) n = kMaxStages;
+    if (n > v.stages && a_rows == uint32_t(BLOCK_M)) n = v.stages;   // prefill: the tuned depth of the variant
+    if (n < 2) return SGLK_E_SHAPE;
+    p.num_stages = n;
+  }
   CUtensorMap ta, tb, tc;
-  if (!make_tmap_2d(&ta, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, A, uint64_t(M), uint64_t(K), uint64_t(lda), BLOCK_M, BLOCK_K))
+  if (!make_tmap_2d(&ta, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, A, uint64_t(M), uint64_t(K), uint64_t(lda), a_rows, BLOCK_K))
     return SGLK_E_DRIVER;
   if (!make_tmap_2d(&tb, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, B, uint64_t(N), uint64_t(K), uint64_t(ldb),
                     uint32_t(v.block_n / v.cg), BLOCK_K))
@@ -613,8 +770,8 @@ static int gemm_entry(const void* A, const void* B, const float* sa, const float
   } else {
     tc = ta;   // unused by the kernel
   }
-  if (out_dtype == SGLK_BF16) return launch_by_id<__nv_bfloat16>(variant, ta, tb, tc, p, num_sms, st);
-  return launch_by_id<__half>(variant, ta, tb, tc, p, num_sms, st);
+  if (out_dtype == SGLK_BF16) return launch_by_id<__nv_bfloat16>(variant, ta, tb, tc, p, pl.workers, st);
+  return launch_by_id<__half>(variant, ta, tb, tc, p, pl.workers, st);
 }
 
 }  // namespace sglk
@@ -623,9 +780,18 @@ extern "C" int sglk_fp8_blockwise_scaled_mm_ex(const void* A, const void* B, con
                                                int64_t M, int64_t N, int64_t K, int64_t lda, int64_t ldb, int64_t ldc,
                                                int64_t sa_stride_m, int64_t sa_stride_k, int64_t sb_stride_k,
                                                int64_t sb_stride_n, int out_dtype, int variant, int num_sms,
-                                               void* stream) {
+                                               void* workspace, int64_t workspace_bytes, void* stream) {
   return sglk::gemm_entry(A, B, sa, sb, C, M, N, K, lda, ldb, ldc, sa_stride_m, sa_stride_k, sb_stride_k,
-                          sb_stride_n, out_dtype, variant, num_sms, stream);
+                          sb_stride_n, out_dtype, variant, num_sms, workspace, workspace_bytes, stream);
+}
+
+extern "C" int64_t sglk_gemm_workspace_bytes(int64_t M, int64_t N, int64_t K, int variant, int num_sms) {
+  if (M <= 0 || N <= 0 || K <= 0) return 0;
+  if (variant < 0) variant = sglk::pick_variant(M, N, K);
+  if (variant >= sglk::kNumVariants) return 0;
+  if (num_sms <= 0) num_sms = sglk::device_sm_count();
+  const sglk::Plan pl = sglk::make_plan(M, N, K, variant, num_sms, true);
+  return pl.stream_k ? pl.counter_bytes + pl.partial_bytes : 0;
 }
 
 extern "C" int sglk_fp8_blockwise_scaled_mm(const void* A, const void* B, const float* sa, const float* sb, void* C,
@@ -633,7 +799,7 @@ extern "C" int sglk_fp8_blockwise_scaled_mm(const void* A, const void* B, const 
                                             int64_t sa_stride_m, int64_t sa_stride_k, int64_t sb_stride_k,
                                             int64_t sb_stride_n, int out_dtype, void* stream) {
   return sglk::gemm_entry(A, B, sa, sb, C, M, N, K, lda, ldb, ldc, sa_stride_m, sa_stride_k, sb_stride_k,
-                          sb_stride_n, out_dtype, -1, 0, stream);
+                          sb_stride_n, out_dtype, -1, 0, nullptr, 0, stream);
 }
 
 extern "C" int sglk_gemm_num_variants(void) { return sglk::kNumVariants; }

@@ -146,7 +146,22 @@ def _gemm_checks(mat_a, mat_b, scales_a, scales_b, out_dtype):
     return M, N, K
 
 
-def _gemm(mat_a, mat_b, scales_a, scales_b, out_dtype, variant: int = -1, num_sms: int = 0):
+# Stream-K workspaces: one zero-initialised buffer per (device, stream), grown on demand.  The kernel
+# leaves the counter region zeroed, so the buffer is reused by consecutive launches on its stream
+# (the same per-process cache idea as the reference's `_get_cache_buf`, python/sgl_kernel/gemm.py:80).
+_workspaces = {}
+
+
+def _get_workspace(device: torch.device, stream_ptr: int, nbytes: int) -> torch.Tensor:
+    key = (device.index, stream_ptr)
+    ws = _workspaces.get(key)
+    if ws is None or ws.numel() < nbytes:
+        ws = torch.zeros(max(nbytes, 1 << 20), dtype=torch.uint8, device=device)
+        _workspaces[key] = ws
+    return ws
+
+
+def _gemm(mat_a, mat_b, scales_a, scales_b, out_dtype, variant: int = -1, num_sms: int = 0, stream_k: bool = True):
     """fp8_blockwise_scaled_mm, include/sgl_kernel_ops.h:581-586 (allocates and returns C)."""
     _check(mat_a.is_cuda and mat_b.is_cuda and scales_a.is_cuda and scales_b.is_cuda,
            "fp8_blockwise_scaled_mm: tensors must be CUDA tensors")
@@ -160,10 +175,17 @@ def _gemm(mat_a, mat_b, scales_a, scales_b, out_dtype, variant: int = -1, num_sm
            "mat_a / mat_b rows must be 16-byte aligned")
     lib = _lib.load()
     with torch.cuda.device(mat_a.device):
+        stream = _stream_ptr(mat_a)
+        ws_ptr, ws_bytes = None, 0
+        if stream_k:
+            need = lib.sglk_gemm_workspace_bytes(M, N, K, variant, num_sms)
+            if need > 0:
+                ws = _get_workspace(mat_a.device, stream, need)
+                ws_ptr, ws_bytes = ws.data_ptr(), ws.numel()
         rc = lib.sglk_fp8_blockwise_scaled_mm_ex(
             mat_a.data_ptr(), mat_b.data_ptr(), scales_a.data_ptr(), scales_b.data_ptr(), out.data_ptr(),
             M, N, K, lda, ldb, out.stride(0), scales_a.stride(0), scales_a.stride(1), scales_b.stride(0),
-            scales_b.stride(1), _GEMM_OUT[out_dtype], variant, num_sms, _stream_ptr(mat_a))
+            scales_b.stride(1), _GEMM_OUT[out_dtype], variant, num_sms, ws_ptr, ws_bytes, stream)
     _lib.check(rc, "fp8_blockwise_scaled_mm")
     return out
 

@@ -66,7 +66,7 @@ def test_c_abi_rejects_bad_arguments_before_launch():
     assert g(None, p, p, p, p, 4, 128, 128, 128, 128, 128, 1, 4, 1, 1, _lib.BF16, None) == -1             # null
     assert g(p, p, p, p, p, 0, 128, 128, 128, 128, 128, 1, 4, 1, 1, _lib.BF16, None) == 0                 # empty
     ex = lib.sglk_fp8_blockwise_scaled_mm_ex
-    assert ex(p, p, p, p, p, 4, 128, 128, 128, 128, 128, 1, 4, 1, 1, _lib.BF16, 99, 0, None) == -9        # variant
+    assert ex(p, p, p, p, p, 4, 128, 128, 128, 128, 128, 1, 4, 1, 1, _lib.BF16, 99, 0, None, 0, None) == -9        # variant
 
 
 def test_schemas_are_the_reference_strings():
