@@ -142,6 +142,24 @@ SGLK_API int sglk_fp8_blockwise_scaled_mm_ex(const void* A, const void* B, const
                                     int out_dtype, int variant, int num_sms, void* workspace,
                                     int64_t workspace_bytes, void* stream);
 
+/*
+ * Fused GEMM -> all-gather for the column-(N-)sharded linear (no reference counterpart: the reference
+ * has no communication layer).  Same arithmetic as above on this rank's [K, N_local]
+ * weight panel; the epilogue TMA-stores every finished 32x64 output box to C_local AND to the same
+ * position of each peer's buffer, so the [M, N_total] result is assembled on all GPUs while the MMAs
+ * still run.  C_local / C_peers[i] point at THIS rank's panel inside each GPU's row-major [M, N_total]
+ * buffer (base + panel_offset), ldc = N_total; peers' pointers must be peer-mapped into this process
+ * (CUDA VMM / symmetric memory / IPC) and 16-byte aligned.  The caller synchronises the ranks before
+ * the buffers are read (the kernel guarantees only that its own stores have completed at kernel end).
+ * num_peers <= 7.
+ */
+SGLK_API int sglk_fp8_blockwise_scaled_mm_allgather(const void* A, const void* B, const float* sa, const float* sb,
+                                           void* C_local, void* const* C_peers, int num_peers, int64_t M,
+                                           int64_t N, int64_t K, int64_t lda, int64_t ldb, int64_t ldc,
+                                           int64_t sa_stride_m, int64_t sa_stride_k, int64_t sb_stride_k,
+                                           int64_t sb_stride_n, int out_dtype, int variant, int num_sms,
+                                           void* workspace, int64_t workspace_bytes, void* stream);
+
 /* bytes of workspace with which the call above would use stream-K (0: it would not) */
 SGLK_API int64_t sglk_gemm_workspace_bytes(int64_t M, int64_t N, int64_t K, int variant, int num_sms);
 

@@ -54,6 +54,7 @@ struct GemmParams {
   // range per worker; tiles shared by several workers are summed through `ws_partials` by whichever
   // worker arrives last (fixed summation order -> deterministic)
   int32_t stream_k;
+  int32_t num_dests;         // TMA-store destinations (1, or the group size for the fused all-gather)
   uint32_t stage_tx_bytes;   // bytes TMA delivers per stage to the (leader's) full barrier
   uint32_t stage_bytes;      // smem bytes of one ring stage = a_slot_bytes + B tile bytes (multiple of 1024)
   uint32_t a_slot_bytes;     // smem reserved for the A tile of a stage (rows that exist, rounded to 1 KB)
@@ -61,6 +62,9 @@ struct GemmParams {
   int32_t* ws_counters;   // [num_tiles][kCG*8], zero on entry, reset by the reducer
   float* ws_partials;     // [2*workers][kCG*8][NC/4][32] float4
 };
+
+constexpr int kMaxDests = 8;
+struct CMaps { CUtensorMap m[kMaxDests]; };   // output tensor maps: [0] = local C, [1..] = peers (fused all-gather)
 
 // One worker's walk over its share of the problem: whole tiles round-robin, or a contiguous range of
 // (tile, K-block) units.  Producer, MMA issuer and epilogue warps all run the same iterator.
@@ -162,7 +166,7 @@ __device__ __forceinline__ void tile_coords(int tile, const GemmParams& p, int& 
 template <int BLOCK_N, int kStages, int kCG, typename OutT, bool kTmaStore, int kDiag = 0>
 __global__ void __launch_bounds__(kNumThreads, 1)
 fp8_blockwise_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
-                          const __grid_constant__ CUtensorMap tmap_c, const GemmParams p) {
+                          const __grid_constant__ CMaps tmap_c, const GemmParams p) {
   using C = Cfg<BLOCK_N, kCG>;
   constexpr int NC = C::NC;
   constexpr int kAccStages = C::kAccStages;
@@ -192,7 +196,8 @@ fp8_blockwise_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gr
   if (warp == 0 && lane == 0) {
     ptx::prefetch_tensormap(&tmap_a);
     ptx::prefetch_tensormap(&tmap_b);
-    if (kTmaStore) ptx::prefetch_tensormap(&tmap_c);
+    if (kTmaStore)
+      for (int d = 0; d < p.num_dests; ++d) ptx::prefetch_tensormap(&tmap_c.m[d]);
   }
   if (warp == 1 && lane == 0) {
     for (int s = 0; s < nstages; ++s) {
@@ -506,7 +511,10 @@ fp8_blockwise_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gr
             ptx::fence_proxy_async_smem();
             __syncwarp();
             if (lane == 0) {
-              ptx::tma_store_2d(&tmap_c, my_store, col0 + cb * kStoreBoxCols, m0 + quarter * 32);
+              // one store per destination: this GPU's output and, for the fused all-gather, the same panel
+              // position in every peer's [M, N] buffer (peer-mapped pointers, written over NVLink)
+              for (int d = 0; d < p.num_dests; ++d)
+                ptx::tma_store_2d(&tmap_c.m[d], my_store, col0 + cb * kStoreBoxCols, m0 + quarter * 32);
               ptx::tma_store_commit();
             }
           }
@@ -605,7 +613,7 @@ constexpr int kNumProductVariants = 7;   // the rest are diagnostics
 constexpr int64_t kCounterAreaBytes = 1 << 20;   // first MiB of a stream-K workspace: tile counters (zero between launches)
 
 template <int BLOCK_N, int kStages, int kCG, typename OutT, bool kTmaStore, int kDiag = 0>
-static int launch_variant(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& tc, const GemmParams& p,
+static int launch_variant(const CUtensorMap& ta, const CUtensorMap& tb, const CMaps& tc, const GemmParams& p,
                           int workers, cudaStream_t st) {
   using C = Cfg<BLOCK_N, kCG>;
   auto kern = fp8_blockwise_gemm_kernel<BLOCK_N, kStages, kCG, OutT, kTmaStore, kDiag>;
@@ -634,7 +642,7 @@ static int launch_variant(const CUtensorMap& ta, const CUtensorMap& tb, const CU
 }
 
 template <typename OutT>
-static int launch_by_id(int v, const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& tc,
+static int launch_by_id(int v, const CUtensorMap& ta, const CUtensorMap& tb, const CMaps& tc,
                         const GemmParams& p, int num_sms, cudaStream_t st) {   // num_sms == workers here
   switch (v) {
     case 0: return launch_variant<128, 6, 1, OutT, true>(ta, tb, tc, p, num_sms, st);
@@ -700,7 +708,7 @@ static Plan make_plan(int64_t M, int64_t N, int64_t K, int variant, int num_sms,
 static int gemm_entry(const void* A, const void* B, const float* sa, const float* sb, void* Cout, int64_t M,
                       int64_t N, int64_t K, int64_t lda, int64_t ldb, int64_t ldc, int64_t sa_sm, int64_t sa_sk,
                       int64_t sb_sk, int64_t sb_sn, int out_dtype, int variant, int num_sms, void* workspace,
-                      int64_t workspace_bytes, void* stream) {
+                      int64_t workspace_bytes, void* stream, void* const* extra_dests = nullptr, int num_extra = 0) {
   if (M < 0 || N < 0 || K < 0) return SGLK_E_SHAPE;
   if (out_dtype != SGLK_BF16 && out_dtype != SGLK_F16) return SGLK_E_DTYPE;
   if (M == 0 || N == 0) return SGLK_OK;
@@ -717,6 +725,9 @@ static int gemm_entry(const void* A, const void* B, const float* sa, const float
   if (variant < 0) variant = pick_variant(M, N, K);
   if (variant >= kNumVariants) return SGLK_E_VARIANT;
   Variant v = kVariants[variant];
+  if (num_extra < 0 || num_extra > kMaxDests - 1 || (num_extra > 0 && !extra_dests)) return SGLK_E_ARG;
+  for (int d = 0; d < num_extra; ++d)
+    if (!extra_dests[d] || !tma_store_ok(extra_dests[d], ldc, 2)) return SGLK_E_STRIDE;
   if (v.tma_store && !tma_store_ok(Cout, ldc, 2)) {
     // same tile shape, predicated-store epilogue
     variant = (v.cg == 2) ? 4 : 1;
@@ -758,7 +769,9 @@ static int gemm_entry(const void* A, const void* B, const float* sa, const float
     if (n < 2) return SGLK_E_SHAPE;
     p.num_stages = n;
   }
-  CUtensorMap ta, tb, tc;
+  CUtensorMap ta, tb;
+  CMaps tc;
+  p.num_dests = 1 + num_extra;
   if (!make_tmap_2d(&ta, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, A, uint64_t(M), uint64_t(K), uint64_t(lda), a_rows, BLOCK_K))
     return SGLK_E_DRIVER;
   if (!make_tmap_2d(&tb, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, B, uint64_t(N), uint64_t(K), uint64_t(ldb),
@@ -766,9 +779,14 @@ static int gemm_entry(const void* A, const void* B, const float* sa, const float
     return SGLK_E_DRIVER;
   if (v.tma_store) {
     const CUtensorMapDataType cdt = out_dtype == SGLK_BF16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT16;
-    if (!make_tmap_2d(&tc, cdt, 2, Cout, uint64_t(M), uint64_t(N), uint64_t(ldc), 32, kStoreBoxCols)) return SGLK_E_DRIVER;
+    if (!make_tmap_2d(&tc.m[0], cdt, 2, Cout, uint64_t(M), uint64_t(N), uint64_t(ldc), 32, kStoreBoxCols)) return SGLK_E_DRIVER;
+    for (int d = 0; d < num_extra; ++d)
+      if (!make_tmap_2d(&tc.m[1 + d], cdt, 2, extra_dests[d], uint64_t(M), uint64_t(N), uint64_t(ldc), 32, kStoreBoxCols))
+        return SGLK_E_DRIVER;
+    for (int d = p.num_dests; d < kMaxDests; ++d) tc.m[d] = tc.m[0];
   } else {
-    tc = ta;   // unused by the kernel
+    if (num_extra > 0) return SGLK_E_STRIDE;   // multi-destination output needs the TMA-store epilogue
+    for (int d = 0; d < kMaxDests; ++d) tc.m[d] = ta;   // unused by the kernel
   }
   if (out_dtype == SGLK_BF16) return launch_by_id<__nv_bfloat16>(variant, ta, tb, tc, p, pl.workers, st);
   return launch_by_id<__half>(variant, ta, tb, tc, p, pl.workers, st);
@@ -783,6 +801,17 @@ extern "C" int sglk_fp8_blockwise_scaled_mm_ex(const void* A, const void* B, con
                                                void* workspace, int64_t workspace_bytes, void* stream) {
   return sglk::gemm_entry(A, B, sa, sb, C, M, N, K, lda, ldb, ldc, sa_stride_m, sa_stride_k, sb_stride_k,
                           sb_stride_n, out_dtype, variant, num_sms, workspace, workspace_bytes, stream);
+}
+
+extern "C" int sglk_fp8_blockwise_scaled_mm_allgather(const void* A, const void* B, const float* sa, const float* sb,
+                                                      void* C_local, void* const* C_peers, int num_peers, int64_t M,
+                                                      int64_t N, int64_t K, int64_t lda, int64_t ldb, int64_t ldc,
+                                                      int64_t sa_stride_m, int64_t sa_stride_k, int64_t sb_stride_k,
+                                                      int64_t sb_stride_n, int out_dtype, int variant, int num_sms,
+                                                      void* workspace, int64_t workspace_bytes, void* stream) {
+  if (variant < 0) variant = (M > 128 && N >= 256) ? 3 : 0;   // TMA-store variants only
+  return sglk::gemm_entry(A, B, sa, sb, C_local, M, N, K, lda, ldb, ldc, sa_stride_m, sa_stride_k, sb_stride_k,
+                          sb_stride_n, out_dtype, variant, num_sms, workspace, workspace_bytes, stream, C_peers, num_peers);
 }
 
 extern "C" int64_t sglk_gemm_workspace_bytes(int64_t M, int64_t N, int64_t K, int variant, int num_sms) {

@@ -190,6 +190,42 @@ def _gemm(mat_a, mat_b, scales_a, scales_b, out_dtype, variant: int = -1, num_sm
     return out
 
 
+def _gemm_allgather(mat_a, mat_b, scales_a, scales_b, out_full, col_lo: int, peer_ptrs, variant: int = -1,
+                    num_sms: int = 0):
+    """Fused GEMM -> all-gather: this rank's [M, N_local] panel is written at columns [col_lo, col_lo+N_local)
+    of `out_full` ([M, N_total], this rank's symmetric buffer) AND at the same place of every peer buffer
+    (`peer_ptrs`: base device pointers of the peers' buffers, peer-mapped into this process)."""
+    _check(mat_a.is_cuda and mat_b.is_cuda and out_full.is_cuda, "fp8_blockwise_scaled_mm: tensors must be CUDA tensors")
+    M, N, K = _gemm_checks(mat_a, mat_b, scales_a, scales_b, out_full.dtype)
+    _check(out_full.dim() == 2 and out_full.size(0) == M and out_full.stride(1) == 1, "out_full must be [M, N_total] row-major")
+    _check(0 <= col_lo and col_lo + N <= out_full.size(1), "panel does not fit in out_full")
+    _check(len(peer_ptrs) <= 7, "at most 8 GPUs")
+    if M == 0 or N == 0:
+        return out_full
+    esz = out_full.element_size()
+    ldc = out_full.stride(0)
+    lda = mat_a.stride(0) if M > 1 else max(K, 16)
+    ldb = mat_b.stride(1) if N > 1 else max(K, 16)
+    lib = _lib.load()
+    with torch.cuda.device(mat_a.device):
+        stream = _stream_ptr(mat_a)
+        ws_ptr, ws_bytes = None, 0
+        need = lib.sglk_gemm_workspace_bytes(M, N, K, variant, num_sms)
+        if need > 0:
+            ws = _get_workspace(mat_a.device, stream, need)
+            ws_ptr, ws_bytes = ws.data_ptr(), ws.numel()
+        import ctypes
+
+        peers = (ctypes.c_void_p * max(1, len(peer_ptrs)))(*[int(p) + col_lo * esz for p in peer_ptrs])
+        rc = lib.sglk_fp8_blockwise_scaled_mm_allgather(
+            mat_a.data_ptr(), mat_b.data_ptr(), scales_a.data_ptr(), scales_b.data_ptr(),
+            out_full.data_ptr() + col_lo * esz, peers, len(peer_ptrs), M, N, K, lda, ldb, ldc,
+            scales_a.stride(0), scales_a.stride(1), scales_b.stride(0), scales_b.stride(1),
+            _GEMM_OUT[out_full.dtype], variant, num_sms, ws_ptr, ws_bytes, stream)
+    _lib.check(rc, "fp8_blockwise_scaled_mm (fused all-gather)")
+    return out_full
+
+
 def _gemm_op(mat_a, mat_b, scales_a, scales_b, out_dtype):
     return _gemm(mat_a, mat_b, scales_a, scales_b, out_dtype)
 

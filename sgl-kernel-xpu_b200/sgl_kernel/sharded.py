@@ -68,6 +68,32 @@ class ColumnShardedFp8Linear:
                 out[:, lo:hi] = staged[r * m : (r + 1) * m, : hi - lo]
         return out
 
+    # ---- fused GEMM -> all-gather over NVLink peer memory -------------------------------------------
+    def enable_fused_gather(self, max_tokens: int, dtype: torch.dtype = torch.bfloat16) -> None:
+        """Allocate the symmetric [max_tokens, N] output buffer and exchange peer mappings (collective)."""
+        import torch.distributed._symmetric_memory as symm_mem
+
+        dev = self.local.weight_q.device
+        self._sym_out = symm_mem.empty((max_tokens, self.n_total), dtype=dtype, device=dev)
+        self._hdl = symm_mem.rendezvous(self._sym_out, self.group if self.group is not None else dist.group.WORLD)
+        # peers in ring order starting after this rank, so that at any instant the ranks target different receivers
+        self._peer_ptrs = [int(self._hdl.buffer_ptrs[(self.rank + i) % self.world]) for i in range(1, self.world)]
+
+    def forward_fused_gather(self, x: torch.Tensor) -> torch.Tensor:
+        """[M, N] on every rank: each rank's GEMM epilogue TMA-stores its output boxes into its own and all
+        peers' buffers while the MMAs still run; two symmetric-memory barriers bracket the step (peers done
+        reading the previous result / all panels landed).  Returns a view of the symmetric buffer."""
+        from . import _ops
+
+        m = x.shape[0]
+        out = self._sym_out[:m]
+        x_q, x_s = self.local.quantize_input(x)
+        self._hdl.barrier(channel=0)
+        lo, _ = self.bounds[self.rank]
+        _ops._gemm_allgather(x_q, self.local.weight_q.t(), x_s, self.local.weight_scale.t(), out, lo, self._peer_ptrs)
+        self._hdl.barrier(channel=1)
+        return out
+
     def forward(self, x: torch.Tensor, gather_output: bool = True) -> torch.Tensor:
         y = self.forward_local(x)
         return self.gather(y) if gather_output else y

@@ -184,6 +184,26 @@ def test_stream_k_odd_sm_counts():
         check(out.cpu(), ref)
 
 
+@pytest.mark.parametrize("M,N_total,n_lo,n_hi,K", [(300, 1024, 256, 768, 1024), (64, 4608, 2304, 4608, 2048), (1024, 768, 0, 256, 512)])
+def test_multi_destination_epilogue(M, N_total, n_lo, n_hi, K):
+    """The fused GEMM->all-gather epilogue on ONE GPU: the 'peers' are two more local [M, N_total] buffers.
+    Every destination must receive this rank's panel at columns [n_lo, n_hi) and nothing else."""
+    N = n_hi - n_lo
+    a, b, sa, sb = O.make_gemm_inputs(M, N, K, seed=11)
+    ref = O.baseline_scaled_mm(a, b, sa, sb, torch.bfloat16)
+    ad, bd = a.to(DEV), b.t().contiguous().to(DEV).t()
+    sad, sbd = sa.t().contiguous().to(DEV).t(), sb.to(DEV)
+    bufs = [torch.full((M, N_total), -7.0, dtype=torch.bfloat16, device=DEV) for _ in range(3)]
+    _ops._gemm_allgather(ad, bd, sad, sbd, bufs[0], n_lo, [bufs[1].data_ptr(), bufs[2].data_ptr()])
+    torch.cuda.synchronize()
+    for buf in bufs:
+        got = buf.cpu()
+        check(got[:, n_lo:n_hi].contiguous(), ref)
+        outside = torch.cat([got[:, :n_lo], got[:, n_hi:]], dim=1)
+        assert (outside == -7.0).all(), "epilogue wrote outside its panel"
+    assert torch.equal(bufs[0], bufs[1]) and torch.equal(bufs[0], bufs[2])
+
+
 def test_empty_and_degenerate():
     a, b, sa, sb = O.make_gemm_inputs(0, 256, 512, seed=0)
     out = sgl_kernel.fp8_blockwise_scaled_mm(a.to(DEV), b.t().contiguous().to(DEV).t(), sa.to(DEV), sb.to(DEV), torch.bfloat16)
