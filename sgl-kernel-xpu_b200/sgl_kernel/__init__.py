@@ -11,7 +11,12 @@ from .gemm import (
     sgl_per_token_group_quant_fp8,
     sgl_per_token_group_quant_int8,
 )
-from .linear import Fp8BlockLinear, create_per_token_group_quant_fp8_output_scale, per_token_group_quant_fp8
+from .linear import (
+    Fp8BlockLinear,
+    HostStreamedFp8Linear,
+    create_per_token_group_quant_fp8_output_scale,
+    per_token_group_quant_fp8,
+)
 from .sharded import ColumnShardedFp8Linear
 
 __version__ = "0.11.0+b200"
@@ -24,5 +29,6 @@ __all__ = [
     "per_token_group_quant_fp8",
     "create_per_token_group_quant_fp8_output_scale",
     "Fp8BlockLinear",
+    "HostStreamedFp8Linear",
     "ColumnShardedFp8Linear",
 ]
