@@ -696,6 +696,9 @@ static Plan make_plan(int64_t M, int64_t N, int64_t K, int variant, int num_sms,
   const int64_t units = tiles * pl.num_k_blocks;
   pl.stream_k = (have_ws && variant < kNumProductVariants && pl.num_k_blocks >= 2 && eff < 0.9 && units >= w0) ? 1 : 0;
   pl.workers = int(pl.stream_k ? w0 : (tiles < w0 ? tiles : w0));
+  // few, large tiles (N=2112: 17): more than ~4 contributors per tile makes the last arriver's sequential
+  // re-read of the partials longer than the K blocks it saves (measured: 68 workers 13.6 us, 148 workers 18.9 us)
+  if (pl.stream_k && tiles * 4 < pl.workers) pl.workers = int(tiles * 4);
   if (pl.workers < 1) pl.workers = 1;
   // the counter area has a FIXED size so that launches with different tilings can share one workspace:
   // partials of one launch must never land where another launch expects zeroed counters
