@@ -152,9 +152,14 @@ SGLK_API int sglk_fp8_blockwise_scaled_mm_ex(const void* A, const void* B, const
  * (CUDA VMM / symmetric memory / IPC) and 16-byte aligned.  The caller synchronises the ranks before
  * the buffers are read (the kernel guarantees only that its own stores have completed at kernel end).
  * num_peers <= 7.
+ * C_multicast (optional): the NVLS multicast address of the same panel position (a multicast mapping of
+ * the symmetric buffer that includes this GPU).  When non-NULL the epilogue issues multimem.st to it
+ * instead of per-peer stores — each output byte leaves this GPU once and the NVSwitch replicates it —
+ * and C_local / C_peers are not written separately.  Needs N % 8 == 0.
  */
 SGLK_API int sglk_fp8_blockwise_scaled_mm_allgather(const void* A, const void* B, const float* sa, const float* sb,
-                                           void* C_local, void* const* C_peers, int num_peers, int64_t M,
+                                           void* C_local, void* const* C_peers, int num_peers,
+                                           void* C_multicast, int64_t M,
                                            int64_t N, int64_t K, int64_t lda, int64_t ldb, int64_t ldc,
                                            int64_t sa_stride_m, int64_t sa_stride_k, int64_t sb_stride_k,
                                            int64_t sb_stride_n, int out_dtype, int variant, int num_sms,

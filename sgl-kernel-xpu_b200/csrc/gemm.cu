@@ -55,6 +55,7 @@ struct GemmParams {
   // worker arrives last (fixed summation order -> deterministic)
   int32_t stream_k;
   int32_t num_dests;         // TMA-store destinations (1, or the group size for the fused all-gather)
+  void* mc_ptr;              // NVLS multicast address of this rank's panel (fused all-gather, multicast form) or null
   uint32_t stage_tx_bytes;   // bytes TMA delivers per stage to the (leader's) full barrier
   uint32_t stage_bytes;      // smem bytes of one ring stage = a_slot_bytes + B tile bytes (multiple of 1024)
   uint32_t a_slot_bytes;     // smem reserved for the A tile of a stage (rows that exist, rounded to 1 KB)
@@ -508,14 +509,38 @@ fp8_blockwise_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gr
               const uint32_t dst = my_store + uint32_t(lane * 128 + ((j ^ (lane & 7)) << 4));
               asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(dst), "r"(w0), "r"(w1), "r"(w2), "r"(w3) : "memory");
             }
-            ptx::fence_proxy_async_smem();
-            __syncwarp();
-            if (lane == 0) {
-              // one store per destination: this GPU's output and, for the fused all-gather, the same panel
-              // position in every peer's [M, N] buffer (peer-mapped pointers, written over NVLink)
-              for (int d = 0; d < p.num_dests; ++d)
-                ptx::tma_store_2d(&tmap_c.m[d], my_store, col0 + cb * kStoreBoxCols, m0 + quarter * 32);
-              ptx::tma_store_commit();
+            if (p.mc_ptr != nullptr) {
+              // NVLS multicast form of the fused all-gather: one multimem.st per 16 bytes lands in EVERY GPU's
+              // buffer (the NVSwitch replicates), so a rank sends its panel once instead of once per peer.
+              // Read the staged box back row-contiguously: 8 lanes cover one 128-byte row segment.
+              __syncwarp();
+#pragma unroll
+              for (int i = 0; i < 8; ++i) {
+                const int r = i * 4 + (lane >> 3);
+                const int ch = lane & 7;
+                uint32_t w0, w1, w2, w3;
+                const uint32_t src = my_store + uint32_t(r * 128 + ((ch ^ (r & 7)) << 4));
+                asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(w0), "=r"(w1), "=r"(w2), "=r"(w3) : "r"(src));
+                const int grow = m0 + quarter * 32 + r;
+                const int gcol = col0 + cb * kStoreBoxCols + ch * 8;
+                if (grow < p.M && gcol + 8 <= p.N) {
+                  OutT* dst = reinterpret_cast<OutT*>(p.mc_ptr) + int64_t(grow) * p.ldc + gcol;
+                  asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};"
+                               ::"l"(dst), "f"(__uint_as_float(w0)), "f"(__uint_as_float(w1)), "f"(__uint_as_float(w2)),
+                                 "f"(__uint_as_float(w3)) : "memory");
+                }
+              }
+              __syncwarp();
+            } else {
+              ptx::fence_proxy_async_smem();
+              __syncwarp();
+              if (lane == 0) {
+                // one store per destination: this GPU's output and, for the fused all-gather, the same panel
+                // position in every peer's [M, N] buffer (peer-mapped pointers, written over NVLink)
+                for (int d = 0; d < p.num_dests; ++d)
+                  ptx::tma_store_2d(&tmap_c.m[d], my_store, col0 + cb * kStoreBoxCols, m0 + quarter * 32);
+                ptx::tma_store_commit();
+              }
             }
           }
         }
@@ -711,7 +736,8 @@ static Plan make_plan(int64_t M, int64_t N, int64_t K, int variant, int num_sms,
 static int gemm_entry(const void* A, const void* B, const float* sa, const float* sb, void* Cout, int64_t M,
                       int64_t N, int64_t K, int64_t lda, int64_t ldb, int64_t ldc, int64_t sa_sm, int64_t sa_sk,
                       int64_t sb_sk, int64_t sb_sn, int out_dtype, int variant, int num_sms, void* workspace,
-                      int64_t workspace_bytes, void* stream, void* const* extra_dests = nullptr, int num_extra = 0) {
+                      int64_t workspace_bytes, void* stream, void* const* extra_dests = nullptr, int num_extra = 0,
+                      void* mc_ptr = nullptr) {
   if (M < 0 || N < 0 || K < 0) return SGLK_E_SHAPE;
   if (out_dtype != SGLK_BF16 && out_dtype != SGLK_F16) return SGLK_E_DTYPE;
   if (M == 0 || N == 0) return SGLK_OK;
@@ -775,6 +801,8 @@ static int gemm_entry(const void* A, const void* B, const float* sa, const float
   CUtensorMap ta, tb;
   CMaps tc;
   p.num_dests = 1 + num_extra;
+  p.mc_ptr = mc_ptr;
+  if (mc_ptr && (!v.tma_store || (reinterpret_cast<uintptr_t>(mc_ptr) & 15) || N % 8 != 0 || ldc % 8 != 0)) return SGLK_E_STRIDE;
   if (!make_tmap_2d(&ta, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, A, uint64_t(M), uint64_t(K), uint64_t(lda), a_rows, BLOCK_K))
     return SGLK_E_DRIVER;
   if (!make_tmap_2d(&tb, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, B, uint64_t(N), uint64_t(K), uint64_t(ldb),
@@ -807,14 +835,16 @@ extern "C" int sglk_fp8_blockwise_scaled_mm_ex(const void* A, const void* B, con
 }
 
 extern "C" int sglk_fp8_blockwise_scaled_mm_allgather(const void* A, const void* B, const float* sa, const float* sb,
-                                                      void* C_local, void* const* C_peers, int num_peers, int64_t M,
+                                                      void* C_local, void* const* C_peers, int num_peers,
+                                                      void* C_multicast, int64_t M,
                                                       int64_t N, int64_t K, int64_t lda, int64_t ldb, int64_t ldc,
                                                       int64_t sa_stride_m, int64_t sa_stride_k, int64_t sb_stride_k,
                                                       int64_t sb_stride_n, int out_dtype, int variant, int num_sms,
                                                       void* workspace, int64_t workspace_bytes, void* stream) {
   if (variant < 0) variant = (M > 128 && N >= 256) ? 3 : 0;   // TMA-store variants only
   return sglk::gemm_entry(A, B, sa, sb, C_local, M, N, K, lda, ldb, ldc, sa_stride_m, sa_stride_k, sb_stride_k,
-                          sb_stride_n, out_dtype, variant, num_sms, workspace, workspace_bytes, stream, C_peers, num_peers);
+                          sb_stride_n, out_dtype, variant, num_sms, workspace, workspace_bytes, stream,
+                          C_multicast ? nullptr : C_peers, C_multicast ? 0 : num_peers, C_multicast);
 }
 
 extern "C" int64_t sglk_gemm_workspace_bytes(int64_t M, int64_t N, int64_t K, int variant, int num_sms) {

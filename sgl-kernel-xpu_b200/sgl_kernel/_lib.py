@@ -35,7 +35,7 @@ SYMBOLS = {
         _i32, [_vp, _vp, _vp, _vp, _vp] + [_i64] * 10 + [_i32, _i32, _i32, _vp, _i64, _vp]),
     "sglk_gemm_workspace_bytes": (_i64, [_i64, _i64, _i64, _i32, _i32]),
     "sglk_fp8_blockwise_scaled_mm_allgather": (
-        _i32, [_vp, _vp, _vp, _vp, _vp, ctypes.POINTER(_vp), _i32] + [_i64] * 10 + [_i32, _i32, _i32, _vp, _i64, _vp]),
+        _i32, [_vp, _vp, _vp, _vp, _vp, ctypes.POINTER(_vp), _i32, _vp] + [_i64] * 10 + [_i32, _i32, _i32, _vp, _i64, _vp]),
     "sglk_gemm_num_variants": (_i32, []),
     "sglk_gemm_variant_name": (ctypes.c_char_p, [_i32]),
     "sglk_gemm_pick_variant": (_i32, [_i64, _i64, _i64]),

@@ -191,7 +191,7 @@ def _gemm(mat_a, mat_b, scales_a, scales_b, out_dtype, variant: int = -1, num_sm
 
 
 def _gemm_allgather(mat_a, mat_b, scales_a, scales_b, out_full, col_lo: int, peer_ptrs, variant: int = -1,
-                    num_sms: int = 0):
+                    num_sms: int = 0, multicast_ptr: int = 0):
     """Fused GEMM -> all-gather: this rank's [M, N_local] panel is written at columns [col_lo, col_lo+N_local)
     of `out_full` ([M, N_total], this rank's symmetric buffer) AND at the same place of every peer buffer
     (`peer_ptrs`: base device pointers of the peers' buffers, peer-mapped into this process)."""
@@ -219,7 +219,8 @@ def _gemm_allgather(mat_a, mat_b, scales_a, scales_b, out_full, col_lo: int, pee
         peers = (ctypes.c_void_p * max(1, len(peer_ptrs)))(*[int(p) + col_lo * esz for p in peer_ptrs])
         rc = lib.sglk_fp8_blockwise_scaled_mm_allgather(
             mat_a.data_ptr(), mat_b.data_ptr(), scales_a.data_ptr(), scales_b.data_ptr(),
-            out_full.data_ptr() + col_lo * esz, peers, len(peer_ptrs), M, N, K, lda, ldb, ldc,
+            out_full.data_ptr() + col_lo * esz, peers, len(peer_ptrs),
+            (int(multicast_ptr) + col_lo * esz) if multicast_ptr else None, M, N, K, lda, ldb, ldc,
             scales_a.stride(0), scales_a.stride(1), scales_b.stride(0), scales_b.stride(1),
             _GEMM_OUT[out_full.dtype], variant, num_sms, ws_ptr, ws_bytes, stream)
     _lib.check(rc, "fp8_blockwise_scaled_mm (fused all-gather)")

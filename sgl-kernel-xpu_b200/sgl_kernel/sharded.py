@@ -79,10 +79,12 @@ class ColumnShardedFp8Linear:
         # peers in ring order starting after this rank, so that at any instant the ranks target different receivers
         self._peer_ptrs = [int(self._hdl.buffer_ptrs[(self.rank + i) % self.world]) for i in range(1, self.world)]
 
-    def forward_fused_gather(self, x: torch.Tensor) -> torch.Tensor:
+    def forward_fused_gather(self, x: torch.Tensor, multicast: Optional[bool] = None) -> torch.Tensor:
         """[M, N] on every rank: each rank's GEMM epilogue TMA-stores its output boxes into its own and all
         peers' buffers while the MMAs still run; two symmetric-memory barriers bracket the step (peers done
-        reading the previous result / all panels landed).  Returns a view of the symmetric buffer."""
+        reading the previous result / all panels landed).  With `multicast=True` (and NVLS available) the
+        epilogue uses multimem.st on the multicast mapping instead of one store per peer.
+        Returns a view of the symmetric buffer."""
         from . import _ops
 
         m = x.shape[0]
@@ -90,7 +92,11 @@ class ColumnShardedFp8Linear:
         x_q, x_s = self.local.quantize_input(x)
         self._hdl.barrier(channel=0)
         lo, _ = self.bounds[self.rank]
-        _ops._gemm_allgather(x_q, self.local.weight_q.t(), x_s, self.local.weight_scale.t(), out, lo, self._peer_ptrs)
+        if multicast is None:   # measured: multicast wins from 4 GPUs up (8 GPUs: 0.98 vs 1.18 ms), unicast at 2
+            multicast = self.world >= 4
+        mc = int(self._hdl.multicast_ptr) if (multicast and self._hdl.multicast_ptr) else 0
+        _ops._gemm_allgather(x_q, self.local.weight_q.t(), x_s, self.local.weight_scale.t(), out, lo, self._peer_ptrs,
+                             multicast_ptr=mc)
         self._hdl.barrier(channel=1)
         return out
 

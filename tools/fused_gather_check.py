@@ -34,11 +34,15 @@ def timeit(fn, n=20):
     e1.record(); torch.cuda.synchronize()
     t = torch.tensor([e0.elapsed_time(e1) / n], device=dev); dist.all_reduce(t, op=dist.ReduceOp.MAX)
     return float(t.item())
+out_mc = layer.forward_fused_gather(x, multicast=True).clone()
+torch.cuda.synchronize(); dist.barrier()
+same_mc = bool(torch.equal(out_mc, ref))
 t_fused = timeit(lambda: layer.forward_fused_gather(x))
+t_mc = timeit(lambda: layer.forward_fused_gather(x, multicast=True))
 t_nccl = timeit(lambda: layer(x, gather_output=True))
 t_local = timeit(lambda: layer(x, gather_output=False))
 if rank == 0:
-    print(json.dumps({"world": world, "M": M, "N": N, "K": K, "bitwise_equal_to_nccl_path": same, "ms_fused": t_fused,
+    print(json.dumps({"world": world, "M": M, "N": N, "K": K, "bitwise_equal_to_nccl_path": same, "ms_fused": t_fused, "ms_fused_multicast": t_mc, "multicast_bitwise_equal": same_mc,
                       "ms_nccl_gather": t_nccl, "ms_no_gather": t_local,
                       "tflops_fused": 2.0 * M * N * K / t_fused / 1e9, "tflops_nccl": 2.0 * M * N * K / t_nccl / 1e9}))
 all_same = torch.tensor([int(same)], device=dev); dist.all_reduce(all_same, op=dist.ReduceOp.MIN)
