@@ -196,7 +196,7 @@ def main():
 
 
     xq = torch.empty(M, K, dtype=torch.float8_e4m3fn, device=dev)
-    xs = sgl_kernel.create_per_token_group_quant_fp8_output_scale((M, K), dev, 128, True, True, False)
+    xs = sgl_kernel.create_per_token_group_quant_fp8_output_scale((M, K), dev, 128, False, False, False)
 
     def step():
         sgl_kernel.sgl_per_token_group_quant_8bit(x, xq, xs, 128, 1e-10, -448.0, 448.0, enable_v2=False)
@@ -351,7 +351,7 @@ def main():
         "dtype": "fp8_e4m3 x fp8_e4m3 -> fp32 accumulate -> bf16", "data": "synthetic",
         "config": {"workload": WORKLOAD, "M": M, "N": N, "K": K, "group": 128, "n_per_rank": n_loc,
                    "parallelism": f"column(N)-sharded x{world}, activations replicated" if world > 1 else "single GPU",
-                   "step": "per_token_group_quant_8bit (col-major scales) + fp8_blockwise_scaled_mm, no collective in value",
+                   "step": "per_token_group_quant_8bit (row-major scales) + fp8_blockwise_scaled_mm, no collective in value",
                    "l2": "256 MiB read-only flush between steps (outside the events); inputs 235 MB + weights > L2",
                    "gemm_variant": sgl_kernel._lib.load().sglk_gemm_variant_name(
                        sgl_kernel._lib.load().sglk_gemm_pick_variant(M, n_loc, K)).decode()},

@@ -40,6 +40,7 @@ constexpr int kNumThreads = 128 + kNumEpiWarps * 32;   // 4 control warps + 8 ep
 constexpr int kStoreBoxCols = 64;                      // bf16 columns per TMA store box (128 B)
 constexpr int kMaxStages = 16;                         // barrier slots reserved for the smem ring
 constexpr int kMaxDynSmem = 232448;                    // 227 KB
+constexpr int kSmemOverhead = 1024 + 2048;             // barriers + sb slots (1 KB), per-thread sa slots (2 KB); base is 1024-aligned
 
 struct GemmParams {
   const float* sa;
@@ -54,7 +55,9 @@ struct GemmParams {
   // range per worker; tiles shared by several workers are summed through `ws_partials` by whichever
   // worker arrives last (fixed summation order -> deterministic)
   int32_t stream_k;
+  int32_t scale_vec;         // scales contiguous along K blocks and 16-byte aligned: vector-load path of the promotion warps
   int32_t num_dests;         // TMA-store destinations (1, or the group size for the fused all-gather)
+  long long* dbg;            // diagnostics (kDiag == 4): per-K-block clock64 stamps of CTA 0, else null
   void* mc_ptr;              // NVLS multicast address of this rank's panel (fused all-gather, multicast form) or null
   uint32_t stage_tx_bytes;   // bytes TMA delivers per stage to the (leader's) full barrier
   uint32_t stage_bytes;      // smem bytes of one ring stage = a_slot_bytes + B tile bytes (multiple of 1024)
@@ -164,18 +167,25 @@ __device__ __forceinline__ void tile_coords(int tile, const GemmParams& p, int& 
 
 // kDiag (diagnostics only, results are NOT the op's): 1 = skip the promotion arithmetic, 2 = accumulate all of K in
 // TMEM like an unscaled GEMM (one accumulator hand-off per tile) — both measure ceilings of the TMA/MMA pipeline.
-template <int BLOCK_N, int kStages, int kCG, typename OutT, bool kTmaStore, int kDiag = 0>
+// kSplitN: each K block is issued as two N/2-wide MMA halves with their own full/empty barriers, so a half can be
+// promoted (and handed back) while the other half and the next K block are still in the tensor pipe.
+template <int BLOCK_N, int kStages, int kCG, typename OutT, bool kTmaStore, int kDiag = 0, bool kSplitN = false>
 __global__ void __launch_bounds__(kNumThreads, 1)
 fp8_blockwise_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
                           const __grid_constant__ CMaps tmap_c, const GemmParams p) {
   using C = Cfg<BLOCK_N, kCG>;
   constexpr int NC = C::NC;
   constexpr int kAccStages = C::kAccStages;
+  constexpr int kHalves = kSplitN ? 2 : 1;             // accumulator hand-off granularity: whole stage or column half
+  constexpr int kAccBars = kAccStages * kHalves;
+  static_assert(!kSplitN || (BLOCK_N == 256 && (kDiag == 0 || kDiag == 4)), "split-N is for the 256-wide product tiles");
   static_assert(!kTmaStore || C::kCanTmaStore, "TMA-store epilogue needs >= 64 columns per warp");
 
-  extern __shared__ uint8_t smem_raw[];
-  // 128B-swizzled TMA/UMMA tiles need 1024-byte alignment
-  const uint32_t smem_base = (ptx::smem_u32(smem_raw) + 1023u) & ~1023u;
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  // 128B-swizzled TMA/UMMA tiles need 1024-byte alignment.  The budget (kSmemOverhead) has no slack for a
+  // misaligned base, so fail loudly rather than run off the end of the allocation.
+  if ((ptx::smem_u32(smem_raw) & 1023u) != 0) __trap();
+  const uint32_t smem_base = ptx::smem_u32(smem_raw);
   // the ring is sized on the host: `num_stages` stages of `stage_bytes` (A slot cut to the rows that
   // exist for decode shapes, so more weight bytes are in flight), at most kMaxStages
   const int nstages = p.num_stages;
@@ -185,8 +195,12 @@ fp8_blockwise_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gr
   auto full_bar = [&](int s) { return bar_base + 8u * s; };
   auto empty_bar = [&](int s) { return bar_base + 8u * (kMaxStages + s); };
   auto tfull_bar = [&](int s) { return bar_base + 8u * (2 * kMaxStages + s); };
-  auto tempty_bar = [&](int s) { return bar_base + 8u * (2 * kMaxStages + kAccStages + s); };
-  const uint32_t tmem_slot = bar_base + 8u * (2 * kMaxStages + 2 * kAccStages);
+  auto tempty_bar = [&](int s) { return bar_base + 8u * (2 * kMaxStages + kAccBars + s); };
+  const uint32_t tmem_slot = bar_base + 8u * (2 * kMaxStages + 2 * kAccBars);
+  // scale staging for the promotion warps (filled with cp.async so no long-latency LDG sits in their
+  // in-order instruction stream): 2 x fp32 per warp for sb at bar_base + 512, 2 x fp32 per thread for sa after the KB of barriers
+  const uint32_t sb_slots = bar_base + 512u;
+  const uint32_t sa_slots = bar_base + 1024u;
   uint8_t* smem_gen = smem_raw + (smem_base - ptx::smem_u32(smem_raw));   // generic pointer to smem_base
 
   const int warp = threadIdx.x >> 5;
@@ -205,9 +219,9 @@ fp8_blockwise_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gr
       ptx::mbar_init(full_bar(s), 1);                    // one arrive.expect_tx by the (leader's) producer
       ptx::mbar_init(empty_bar(s), 1);                   // one tcgen05.commit
     }
-    for (int s = 0; s < kAccStages; ++s) {
-      ptx::mbar_init(tfull_bar(s), 1);                   // one tcgen05.commit
-      ptx::mbar_init(tempty_bar(s), kCG * kNumEpiWarps); // one arrive per epilogue warp of every CTA
+    for (int s = 0; s < kAccBars; ++s) {
+      ptx::mbar_init(tfull_bar(s), 1);                             // one tcgen05.commit
+      ptx::mbar_init(tempty_bar(s), kCG * kNumEpiWarps / kHalves); // one arrive per epilogue warp (of that half) of every CTA
     }
     ptx::fence_mbar_init();
   }
@@ -230,7 +244,7 @@ fp8_blockwise_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gr
   // (each role's code must be dominated by its own setmaxnreg, or ptxas budgets it for the minimum)
   if (warp == 0) {
     // =========================== TMA producer ===========================
-    ptx::reg_dealloc<56>();
+    ptx::reg_dealloc<40>();
     {
       const uint64_t pol_a = ptx::policy_evict_normal();
       const uint64_t pol_b = ptx::policy_evict_normal();
@@ -257,7 +271,14 @@ fp8_blockwise_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gr
               const uint32_t leader_full = full_bar(stage) & 0xFEFFFFFFu;
               if (is_leader) ptx::mbar_arrive_expect_tx(full_bar(stage), p.stage_tx_bytes);
               ptx::tma_load_2d_pair(&tmap_a, leader_full, sa_addr, kb * BLOCK_K, m0, pol_a);
-              ptx::tma_load_2d_pair(&tmap_b, leader_full, sb_addr, kb * BLOCK_K, n0, pol_b);
+              if constexpr (kSplitN) {
+                // column half h of the pair's tile = [n_tile + h*128, +128): this CTA contributes 64 rows of each half
+                const int nt = nb * BLOCK_N + int(cta_rank) * (BLOCK_N / 4);
+                ptx::tma_load_2d_pair(&tmap_b, leader_full, sb_addr, kb * BLOCK_K, nt, pol_b);
+                ptx::tma_load_2d_pair(&tmap_b, leader_full, sb_addr + (BLOCK_N / 4) * BLOCK_K, kb * BLOCK_K, nt + BLOCK_N / 2, pol_b);
+              } else {
+                ptx::tma_load_2d_pair(&tmap_b, leader_full, sb_addr, kb * BLOCK_K, n0, pol_b);
+              }
             }
           }
           __syncwarp();
@@ -268,7 +289,7 @@ fp8_blockwise_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gr
     __syncwarp();
   } else if (warp == 1) {
     // =========================== MMA issuer (leader CTA only) ===========================
-    ptx::reg_dealloc<56>();
+    ptx::reg_dealloc<40>();
     // The whole warp walks the loop convergently and one elected lane issues: descriptors, barrier
     // addresses and TMEM addresses then live in uniform registers (a lane-0-only branch made ptxas wrap
     // every tcgen05.mma in an ELECT/R2UR loop and the issuing thread became the bottleneck — profile r1b).
@@ -282,16 +303,56 @@ fp8_blockwise_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gr
       int tile, kb0, kb1;
       while (it.next(tile, kb0, kb1)) {
         for (int kb = kb0; kb < kb1; ++kb) {
-          // accumulator stage drained by every epilogue warp (of both CTAs)?
-          if (kDiag != 2 || kb == kb0) ptx::mbar_wait(tempty_bar(acc), acc_phase ^ 1);
+          if constexpr (kSplitN) {
+            ptx::mbar_wait(full_bar(stage), phase);
+            const uint32_t sa_addr = smem_base + stage * stage_bytes;
+            const uint64_t da = desc_hi | uint64_t((sa_addr & 0x3FFFFu) >> 4);
+            const uint64_t db = desc_hi | uint64_t(((sa_addr + p.a_slot_bytes) & 0x3FFFFu) >> 4);
+            constexpr uint32_t idesc_h = make_idesc(BLOCK_M * kCG, BLOCK_N / 2);
+            constexpr uint32_t kHalfBDesc = uint32_t((BLOCK_N / 2 / kCG) * BLOCK_K) >> 4;   // B rows of one half in this CTA
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {
+              ptx::mbar_wait(tempty_bar(acc * 2 + h), acc_phase ^ 1);     // that half drained by its epilogue warps?
+              if (kDiag == 4 && h == 0 && blockIdx.x == 0 && lane == 0 && kb < 64 && tile == worker) p.dbg[kb * 8 + 0] = clock64();
+              ptx::tc_fence_after();
+              const uint32_t d_tmem = tmem_base_u + uint32_t(acc * BLOCK_N + h * (BLOCK_N / 2));
+              if (ptx::elect_one()) {
+#pragma unroll
+                for (int k = 0; k < BLOCK_K / UMMA_K; ++k)
+                  ptx::mma_f8f6f4<kCG>(d_tmem, da + uint64_t(k * (UMMA_K >> 4)),
+                                       db + uint64_t(h * kHalfBDesc + k * (UMMA_K >> 4)), idesc_h, k > 0 ? 1u : 0u);
+                if (h == 1) ptx::tc_commit<kCG>(empty_bar(stage));
+                ptx::tc_commit<kCG>(tfull_bar(acc * 2 + h));
+              }
+              __syncwarp();
+            }
+            if (kDiag == 4 && blockIdx.x == 0 && lane == 0 && kb < 64 && tile == worker) p.dbg[kb * 8 + 2] = clock64();
+            if (++stage == nstages) { stage = 0; phase ^= 1; }
+            if (++acc == kAccStages) { acc = 0; acc_phase ^= 1; }
+            continue;
+          }
+          // operands first (they arrive long before the accumulator frees up), descriptors built, and only then
+          // the wait that sits on the critical ring: accumulator stage drained by every epilogue warp (of both CTAs)?
           ptx::mbar_wait(full_bar(stage), phase);
-          ptx::tc_fence_after();
           const uint32_t sa_addr = smem_base + stage * stage_bytes;
           const uint64_t da = desc_hi | uint64_t((sa_addr & 0x3FFFFu) >> 4);
           const uint64_t db = desc_hi | uint64_t(((sa_addr + p.a_slot_bytes) & 0x3FFFFu) >> 4);
+          if ((kDiag != 2 && kDiag != 3) || kb == kb0) ptx::mbar_wait(tempty_bar(acc), acc_phase ^ 1);
+          if (kDiag == 4 && blockIdx.x == 0 && lane == 0 && kb < 64 && tile == worker) p.dbg[kb * 8 + 0] = clock64();
+          ptx::tc_fence_after();
           const uint32_t d_tmem = tmem_base_u + uint32_t(acc * BLOCK_N);
-          const bool last_of_tile = kDiag == 2 && kb + 1 < kb1;
+          const bool last_of_tile = (kDiag == 2 || kDiag == 3) && kb + 1 < kb1;
           if (ptx::elect_one()) {
+            if constexpr (kDiag == 3) {   // diagnostic: unscaled GEMM issued as two N/2-wide halves (A read twice from smem)
+              constexpr uint32_t idesc_h = make_idesc(BLOCK_M * kCG, BLOCK_N / 2);
+#pragma unroll
+              for (int h = 0; h < 2; ++h)
+#pragma unroll
+                for (int k = 0; k < BLOCK_K / UMMA_K; ++k)
+                  ptx::mma_f8f6f4<kCG>(d_tmem + uint32_t(h * (BLOCK_N / 2)), da + uint64_t(k * (UMMA_K >> 4)),
+                                       db + uint64_t(h * ((BLOCK_N / 2 / kCG) * BLOCK_K >> 4) + k * (UMMA_K >> 4)), idesc_h,
+                                       (k > 0 || kb > kb0) ? 1u : 0u);
+            } else
 #pragma unroll
             for (int k = 0; k < BLOCK_K / UMMA_K; ++k) {
               // +32 B along K inside the swizzle atom = +2 in the descriptor's 16-byte address units
@@ -310,10 +371,10 @@ fp8_blockwise_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gr
     }
     __syncwarp();
   } else if (warp < 4) {
-    ptx::reg_dealloc<56>();                  // warps 2 (TMEM owner) and 3 (spare) only wait for the end
+    ptx::reg_dealloc<40>();                  // warps 2 (TMEM owner) and 3 (spare) only wait for the end
   } else {
     // =========================== promotion + epilogue warps ===========================
-    ptx::reg_alloc<224>();
+    ptx::reg_alloc<232>();
     const int ew = warp - 4;
     const int quarter = warp & 3;            // TMEM lanes this warp may touch: 32*quarter .. +31
     const int half = ew >> 2;                // which half of the tile's columns
@@ -343,17 +404,19 @@ fp8_blockwise_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gr
       // Scale prefetch, two K blocks ahead, kept as raw loads: the product is formed only at the top
       // of the iteration that uses it, so no instruction ever waits on an in-flight global load
       // (an in-order warp that multiplies right after the load stalls ~1 us per K block — measured).
-      auto ld_sa = [&](int kb) { return (row_ok && kb < kb1) ? __ldg(sa_ptr + int64_t(kb) * p.sa_sk) : 0.0f; };
-      auto ld_sb = [&](int kb) { return kb < kb1 ? __ldg(sb_ptr + int64_t(kb) * p.sb_sk) : 0.0f; };
+      const int64_t sa_sk = p.sa_sk, sb_sk = p.sb_sk;
+      auto ld_sa = [&](int kb) { return (row_ok && kb < kb1) ? __ldg(sa_ptr + int64_t(kb) * sa_sk) : 0.0f; };
+      auto ld_sb = [&](int kb) { return kb < kb1 ? __ldg(sb_ptr + int64_t(kb) * sb_sk) : 0.0f; };
       float sa0 = ld_sa(kb0), sb0 = ld_sb(kb0), sa1 = ld_sa(kb0 + 1), sb1 = ld_sb(kb0 + 1);
       constexpr int NCH = NC / 32;           // 32-column TMEM chunks per K block for this warp
+      const int hb = kSplitN ? half : 0;     // which hand-off barrier of the stage this warp uses
       auto release_stage = [&]() {
         // every tcgen05.ld of this warp on the stage has completed: hand it back to the MMA issuer
         ptx::tc_fence_before();
         __syncwarp();
         if (lane == 0) {
-          if constexpr (kCG == 2) ptx::mbar_arrive_cluster(tempty_leader + 8u * acc);
-          else ptx::mbar_arrive(tempty_bar(acc));
+          if constexpr (kCG == 2) ptx::mbar_arrive_cluster(tempty_leader + 8u * (acc * kHalves + hb));
+          else ptx::mbar_arrive(tempty_bar(acc * kHalves + hb));
         }
         if (++acc == kAccStages) { acc = 0; acc_phase ^= 1; }
       };
@@ -361,13 +424,13 @@ fp8_blockwise_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gr
       uint32_t v[2][32];
       if constexpr (kDiag == 1) {            // diagnostic: TMA + MMA pipeline with the per-block hand-off, no arithmetic
         for (int kb = kb0; kb < kb1; ++kb) {
-          ptx::mbar_wait(tfull_bar(acc), acc_phase);
+          ptx::mbar_wait(tfull_bar(acc * kHalves + hb), acc_phase);
           ptx::tc_fence_after();
           accum[0] += sa0 * sb0 + float(stage_addr());
           release_stage();
         }
-      } else if constexpr (kDiag == 2) {     // diagnostic: unscaled GEMM, one hand-off per tile
-        ptx::mbar_wait(tfull_bar(acc), acc_phase);
+      } else if constexpr (kDiag == 2 || kDiag == 3) {     // diagnostic: unscaled GEMM, one hand-off per tile
+        ptx::mbar_wait(tfull_bar(acc * kHalves + hb), acc_phase);
         ptx::tc_fence_after();
         const uint32_t taddr = stage_addr();
 #pragma unroll
@@ -382,24 +445,58 @@ fp8_blockwise_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gr
         // Software pipeline across K blocks: chunk c+1 is in flight while chunk c is folded in, the
         // stage is released as soon as its last chunk is in registers (before that chunk's FMAs),
         // and the first chunk of the NEXT K block is requested before the last FMAs of this one.
-        ptx::mbar_wait(tfull_bar(acc), acc_phase);
-        ptx::tc_fence_after();
-        uint32_t taddr = stage_addr();
-        ptx::tmem_ld_32x32(taddr, v[0]);
+        int dbg_kb = kb0;
+        // Scales travel global -> smem with cp.async (4 bytes per thread for sa, per warp for sb), two K blocks
+        // ahead, and are read back with LDS: a plain LDG here shares the 6 scoreboard slots with the tcgen05.ld
+        // stream and its L2 latency then stalls whatever instruction reuses the slot (measured 250-400 clk per block).
+        uint32_t taddr = 0;
+        const uint32_t my_sa = sa_slots + uint32_t(threadIdx.x - 128) * 8u;
+        const uint32_t my_sb = sb_slots + uint32_t(ew) * 8u;
+        // running global pointers (bumped by one K block per prefetch: nothing to rematerialise) and a slot toggle
+        const float* sa_next = sa_ptr + int64_t(kb0) * sa_sk;
+        const float* sb_next = sb_ptr + int64_t(kb0) * sb_sk;
+        int kb_next = kb0;
+        uint32_t fill_off = 0, read_off = 0;             // byte offset (0 or 4) of the slot to fill / to read next
+        auto prefetch_scales = [&]() {
+          if (kb_next < kb1) {
+            if (row_ok) ptx::cp_async4(my_sa + fill_off, sa_next);
+            if (lane == 0) ptx::cp_async4(my_sb + fill_off, sb_next);
+          }
+          ptx::cp_async_commit();
+          sa_next += sa_sk; sb_next += sb_sk; ++kb_next; fill_off ^= 4u;
+        };
+        auto staged_scale = [&]() {
+          ptx::cp_async_wait<1>();                       // the group of this K block has landed (one more may be in flight)
+          if (kDiag == 4 && blockIdx.x == 0 && ew == 0 && lane == 0 && dbg_kb < 64 && tile == worker) p.dbg[dbg_kb * 8 + 2] = clock64();
+          __syncwarp();                                  // lane 0's sb copy visible to the warp
+          const float s = ptx::lds_f32(my_sa + read_off) * ptx::lds_f32(my_sb + read_off);
+          read_off ^= 4u;
+          __syncwarp();                                  // everyone has read the slot before it is refilled
+          prefetch_scales();
+          return s;
+        };
         auto promote = [&](const float s, const bool more) {
+          const bool stamp = kDiag == 4 && blockIdx.x == 0 && ew == 0 && lane == 0 && dbg_kb < 64 && tile == worker;
 #pragma unroll
           for (int c = 0; c < NCH; ++c) {
+            if (stamp && c == 0) p.dbg[dbg_kb * 8 + 1] = clock64();       // loop top: about to wait for the first chunk
             ptx::tmem_ld_wait(v[c & 1]);
+            if (stamp && c == 0) p.dbg[dbg_kb * 8 + 3] = clock64();       // first chunk of this K block in registers
             bool deferred = false;
             if (c + 1 < NCH) {
               ptx::tmem_ld_32x32(taddr + uint32_t((c + 1) * 32), v[(c + 1) & 1]);
             } else {
+              if (stamp) p.dbg[dbg_kb * 8 + 4] = clock64();                 // last chunk in registers: stage released
               release_stage();
+              if (stamp) p.dbg[dbg_kb * 8 + 5] = clock64();                 // after fence + arrive
               if (more) {
                 taddr = stage_addr();
-                if (ptx::mbar_try_wait(tfull_bar(acc), acc_phase)) {
+                // (polling this barrier a chunk earlier, with try_wait or test_wait, was measured slower: the
+                //  probe either suspends the warp or sits in front of the FMAs it was meant to overlap)
+                if (ptx::mbar_try_wait(tfull_bar(acc * kHalves + hb), acc_phase)) {
                   ptx::tc_fence_after();
                   ptx::tmem_ld_32x32(taddr, v[0]);
+                  if (stamp) p.dbg[dbg_kb * 8 + 7] = clock64();             // next block's first tcgen05.ld issued
                 } else {
                   deferred = true;
                 }
@@ -409,30 +506,58 @@ fp8_blockwise_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gr
             for (int i = 0; i < 32; i += 2)
               ptx::fma2(accum[c * 32 + i], accum[c * 32 + i + 1], v[c & 1][i], v[c & 1][i + 1], s);
             if (deferred) {
-              ptx::mbar_wait(tfull_bar(acc), acc_phase);
+              ptx::mbar_wait(tfull_bar(acc * kHalves + hb), acc_phase);
               ptx::tc_fence_after();
               ptx::tmem_ld_32x32(taddr, v[0]);
             }
           }
+          if (stamp) p.dbg[dbg_kb * 8 + 6] = clock64();                     // FMAs of this K block done
+          ++dbg_kb;
         };
         // two K blocks per trip so the scale registers rotate by name (no register moves that would
         // touch a load still in flight): each pair is reloaded right after its use, two blocks ahead
-        for (int kb = kb0; kb < kb1; kb += 2) {
-          const float s_even = sa0 * sb0;
-          sa0 = ld_sa(kb + 2); sb0 = ld_sb(kb + 2);
-          promote(s_even, kb + 1 < kb1);
-          if (kb + 1 < kb1) {
-            const float s_odd = sa1 * sb1;
-            sa1 = ld_sa(kb + 3); sb1 = ld_sb(kb + 3);
-            promote(s_odd, kb + 2 < kb1);
+        if (p.scale_vec) {
+          // Scales contiguous along K blocks (row-major sa as the quant op writes by default; sb as the
+          // weight-scale view gives it): one 16-byte load per FOUR K blocks per thread, fetched a whole group
+          // ahead into registers — no per-block load, wait or smem round trip in the promotion loop.
+          const float4* sa4 = reinterpret_cast<const float4*>(sa_ptr);
+          const float4* sb4 = reinterpret_cast<const float4*>(sb_ptr);
+          int g = kb0 >> 2;
+          const int g_end = (kb1 + 3) >> 2;
+          float4 a_nx = row_ok ? __ldg(sa4 + g) : make_float4(0.f, 0.f, 0.f, 0.f);
+          float4 b_nx = __ldg(sb4 + g);
+          ptx::mbar_wait(tfull_bar(acc * kHalves + hb), acc_phase);
+          ptx::tc_fence_after();
+          taddr = stage_addr();
+          ptx::tmem_ld_32x32(taddr, v[0]);
+          for (; g < g_end; ++g) {
+            const float s0 = a_nx.x * b_nx.x, s1 = a_nx.y * b_nx.y, s2 = a_nx.z * b_nx.z, s3 = a_nx.w * b_nx.w;
+            if (g + 1 < g_end) {
+              if (row_ok) a_nx = __ldg(sa4 + g + 1);
+              b_nx = __ldg(sb4 + g + 1);
+            }
+            const int kb = g << 2;
+            if (kb >= kb0 && kb < kb1) promote(s0, kb + 1 < kb1);
+            if (kb + 1 >= kb0 && kb + 1 < kb1) promote(s1, kb + 2 < kb1);
+            if (kb + 2 >= kb0 && kb + 2 < kb1) promote(s2, kb + 3 < kb1);
+            if (kb + 3 >= kb0 && kb + 3 < kb1) promote(s3, kb + 4 < kb1);
           }
+        } else {
+          prefetch_scales();
+          prefetch_scales();
+          ptx::mbar_wait(tfull_bar(acc * kHalves + hb), acc_phase);
+          ptx::tc_fence_after();
+          taddr = stage_addr();
+          ptx::tmem_ld_32x32(taddr, v[0]);
+          for (int kb = kb0; kb < kb1; ++kb) promote(staged_scale(), kb + 1 < kb1);
+          ptx::cp_async_wait<0>();
         }
       } else {
         for (int kb = kb0; kb < kb1; ++kb) {
           const float s = sa0 * sb0;
           sa0 = sa1; sb0 = sb1;
           sa1 = ld_sa(kb + 2); sb1 = ld_sb(kb + 2);
-          ptx::mbar_wait(tfull_bar(acc), acc_phase);
+          ptx::mbar_wait(tfull_bar(acc * kHalves + hb), acc_phase);
           ptx::tc_fence_after();
           const uint32_t taddr = stage_addr();
           ptx::tmem_ld_32x32(taddr, v[0]);
@@ -632,16 +757,21 @@ static const Variant kVariants[] = {
     {"diag_n256_s7_cta2_plain_gemm", 256, 7, 2, false},
     {"diag_n256_s4_cta2_plain_gemm", 256, 4, 2, false},
     {"diag_n256_s7_cta2_nopromote", 256, 7, 2, false},
+    {"diag_n256_s6_cta2_plain_gemm_splitN", 256, 6, 2, true},
+    {"n256_s6_cta2_tma_splitn", 256, 6, 2, true},
+    {"n256_s4_cta1_tma_splitn", 256, 4, 1, true},
+    {"diag_n256_s6_cta2_timestamps", 256, 6, 2, true},
+    {"diag_n256_s6_cta2_splitn_timestamps", 256, 6, 2, true},
 };
 constexpr int kNumVariants = int(sizeof(kVariants) / sizeof(kVariants[0]));
-constexpr int kNumProductVariants = 7;   // the rest are diagnostics
+constexpr int kNumProductVariants = 7;   // ids 0..6; 7..12 are diagnostics; 13, 14 are product variants again
 constexpr int64_t kCounterAreaBytes = 1 << 20;   // first MiB of a stream-K workspace: tile counters (zero between launches)
 
-template <int BLOCK_N, int kStages, int kCG, typename OutT, bool kTmaStore, int kDiag = 0>
+template <int BLOCK_N, int kStages, int kCG, typename OutT, bool kTmaStore, int kDiag = 0, bool kSplitN = false>
 static int launch_variant(const CUtensorMap& ta, const CUtensorMap& tb, const CMaps& tc, const GemmParams& p,
                           int workers, cudaStream_t st) {
   using C = Cfg<BLOCK_N, kCG>;
-  auto kern = fp8_blockwise_gemm_kernel<BLOCK_N, kStages, kCG, OutT, kTmaStore, kDiag>;
+  auto kern = fp8_blockwise_gemm_kernel<BLOCK_N, kStages, kCG, OutT, kTmaStore, kDiag, kSplitN>;
   constexpr int smem = kMaxDynSmem;
   (void)sizeof(C);
   static bool configured = false;   // per instantiation
@@ -682,6 +812,11 @@ static int launch_by_id(int v, const CUtensorMap& ta, const CUtensorMap& tb, con
     case 9: return launch_variant<256, 7, 2, OutT, false, 2>(ta, tb, tc, p, num_sms, st);
     case 10: return launch_variant<256, 4, 2, OutT, false, 2>(ta, tb, tc, p, num_sms, st);
     case 11: return launch_variant<256, 7, 2, OutT, false, 1>(ta, tb, tc, p, num_sms, st);
+    case 12: return launch_variant<256, 6, 2, OutT, true, 3>(ta, tb, tc, p, num_sms, st);
+    case 13: return launch_variant<256, 6, 2, OutT, true, 0, true>(ta, tb, tc, p, num_sms, st);
+    case 14: return launch_variant<256, 4, 1, OutT, true, 0, true>(ta, tb, tc, p, num_sms, st);
+    case 15: return launch_variant<256, 6, 2, OutT, true, 4>(ta, tb, tc, p, num_sms, st);
+    case 16: return launch_variant<256, 6, 2, OutT, true, 4, true>(ta, tb, tc, p, num_sms, st);
     default: return SGLK_E_VARIANT;
   }
 }
@@ -719,7 +854,7 @@ static Plan make_plan(int64_t M, int64_t N, int64_t K, int variant, int num_sms,
   const int64_t waves = (tiles + w0 - 1) / w0;
   const double eff = double(tiles) / double(waves * w0);
   const int64_t units = tiles * pl.num_k_blocks;
-  pl.stream_k = (have_ws && variant < kNumProductVariants && pl.num_k_blocks >= 2 && eff < 0.9 && units >= w0) ? 1 : 0;
+  pl.stream_k = (have_ws && (variant < kNumProductVariants || variant >= 13) && pl.num_k_blocks >= 2 && eff < 0.9 && units >= w0) ? 1 : 0;
   pl.workers = int(pl.stream_k ? w0 : (tiles < w0 ? tiles : w0));
   // few, large tiles (N=2112: 17): more than ~4 contributors per tile makes the last arriver's sequential
   // re-read of the partials longer than the K blocks it saves (measured: 68 workers 13.6 us, 148 workers 18.9 us)
@@ -779,6 +914,11 @@ static int gemm_entry(const void* A, const void* B, const float* sa, const float
   p.stream_k = pl.stream_k;
   p.ws_counters = pl.stream_k ? static_cast<int32_t*>(workspace) : nullptr;
   p.ws_partials = pl.stream_k ? reinterpret_cast<float*>(static_cast<char*>(workspace) + pl.counter_bytes) : nullptr;
+  p.dbg = nullptr;
+  if (variant == 15 || variant == 16) {   // timestamps diagnostic: the stamps go to the start of the partials area of the workspace
+    if (!workspace || workspace_bytes < kCounterAreaBytes + 64 * 8 * 8) return SGLK_E_ARG;
+    p.dbg = reinterpret_cast<long long*>(static_cast<char*>(workspace) + kCounterAreaBytes);
+  }
 
   // Decode (M < 128): only load the rows that exist.  TMA zero-fills out-of-bounds rows of a box at
   // ~20 clk per row (measured: M=1 ran 2x slower than M=128), so the A box is cut to round_up(M, 8) rows;
@@ -792,7 +932,7 @@ static int gemm_entry(const void* A, const void* B, const float* sa, const float
     // what follows the ring: the TMA-store staging boxes, or (direct store) nothing — but the MMA reads a
     // full 16 KB of A rows from every stage, so the last stage needs that much addressable smem behind it
     const int tail = v.tma_store ? 32768 : 16384;
-    int n = (kMaxDynSmem - 1024 /*alignment slack*/ - 1024 /*barriers*/ - tail) / int(p.stage_bytes);
+    int n = (kMaxDynSmem - kSmemOverhead - tail) / int(p.stage_bytes);
     if (n > kMaxStages) n = kMaxStages;
     if (n > v.stages && a_rows == uint32_t(BLOCK_M)) n = v.stages;   // prefill: the tuned depth of the variant
     if (n < 2) return SGLK_E_SHAPE;
@@ -802,11 +942,14 @@ static int gemm_entry(const void* A, const void* B, const float* sa, const float
   CMaps tc;
   p.num_dests = 1 + num_extra;
   p.mc_ptr = mc_ptr;
+  p.scale_vec = (sa_sk == 1 && sb_sk == 1 && p.num_k_blocks % 4 == 0 && sa_sm % 4 == 0 && sb_sn % 4 == 0 &&
+                 (reinterpret_cast<uintptr_t>(sa) & 15) == 0 && (reinterpret_cast<uintptr_t>(sb) & 15) == 0) ? 1 : 0;
   if (mc_ptr && (!v.tma_store || (reinterpret_cast<uintptr_t>(mc_ptr) & 15) || N % 8 != 0 || ldc % 8 != 0)) return SGLK_E_STRIDE;
   if (!make_tmap_2d(&ta, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, A, uint64_t(M), uint64_t(K), uint64_t(lda), a_rows, BLOCK_K))
     return SGLK_E_DRIVER;
+  const bool split_b_boxes = (variant == 13 || variant == 16);   // pair + split-N: two 64-row boxes per CTA per stage
   if (!make_tmap_2d(&tb, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, B, uint64_t(N), uint64_t(K), uint64_t(ldb),
-                    uint32_t(v.block_n / v.cg), BLOCK_K))
+                    uint32_t(v.block_n / v.cg / (split_b_boxes ? 2 : 1)), BLOCK_K))
     return SGLK_E_DRIVER;
   if (v.tma_store) {
     const CUtensorMapDataType cdt = out_dtype == SGLK_BF16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT16;

@@ -55,7 +55,7 @@ SHAPES = [(1, 128, 512), (5, 512, 1024), (127, 256, 512), (128, 128, 7168), (129
           (512, 2112, 1024), (1024, 1024, 512), (64, 4096, 128)]
 
 
-@pytest.mark.parametrize("variant", range(7))
+@pytest.mark.parametrize("variant", list(range(7)) + [13, 14])
 @pytest.mark.parametrize("M,N,K", SHAPES)
 def test_every_variant(variant, M, N, K):
     if variant >= n_variants():
@@ -117,6 +117,23 @@ def test_row_major_activation_scales():
     check(out.cpu(), ref)
 
 
+@pytest.mark.parametrize("M,N,K", [(1, 2112, 7168), (64, 24576, 2048), (200, 512, 1024), (300, 1280, 4096), (1024, 1024, 512),
+                                   (129, 384, 1536), (16, 4096, 7168)])
+@pytest.mark.parametrize("variant", [-1, 0, 2, 3])
+def test_k_contiguous_scales_vector_path(M, N, K, variant):
+    """scales_a row-major (the quant op's default output) and scales_b contiguous along K blocks (the view of a
+    [N/128, K/128] weight-scale tensor): the promotion warps' 16-byte-per-4-blocks path, incl. stream-K segments that
+    start in the middle of a group of four (K=1536 has 12 blocks: vector path; the others too)."""
+    a, b, sa, sb = O.make_gemm_inputs(M, N, K, seed=M + K)
+    ref = O.baseline_scaled_mm(a, b, sa, sb, torch.bfloat16)
+    sad = sa.contiguous().to(DEV)                           # [M, G] row-major
+    sbd = sb.t().contiguous().to(DEV).t()                   # (kb, nb) at nb*G + kb
+    assert sad.stride(1) == 1 and (sbd.stride(0) == 1 or sbd.shape[0] == 1)
+    out = _ops._gemm(a.to(DEV), b.t().contiguous().to(DEV).t(), sad, sbd, torch.bfloat16, variant)
+    torch.cuda.synchronize()
+    check(out.cpu(), ref)
+
+
 BIG = [("llama3_70b_gate_up", 8192, 28672, 8192), ("dsv3_mlp", 16384, 18432, 7168), ("dsv3_decode_wide", 256, 24576, 7168),
        ("dsv3_decode_ragged", 256, 2112, 7168), ("dsv3_decode_m1", 1, 24576, 7168)]
 
@@ -148,7 +165,7 @@ STREAMK = [(1, 2112, 7168), (16, 24576, 7168), (64, 2112, 7168), (130, 4096, 204
 
 
 @pytest.mark.parametrize("M,N,K", STREAMK)
-@pytest.mark.parametrize("variant", [-1, 0, 2, 3, 5, 6])
+@pytest.mark.parametrize("variant", [-1, 0, 2, 3, 5, 6, 13, 14])
 def test_stream_k_matches_whole_tiles_and_oracle(M, N, K, variant):
     """Stream-K scheduling (tiles cut across CTAs, summed through the workspace by the last arriver)
     gives the oracle's answer, is bit-reproducible, and leaves its counters zeroed for the next launch."""
