@@ -412,8 +412,8 @@ fp8_blockwise_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gr
       const int hb = kSplitN ? half : 0;     // which hand-off barrier of the stage this warp uses
       auto release_stage = [&]() {
         // every tcgen05.ld of this warp on the stage has completed: hand it back to the MMA issuer
+        // (tcgen05.wait::ld is warp-aligned: every lane's loads are complete here, no extra warp sync needed)
         ptx::tc_fence_before();
-        __syncwarp();
         if (lane == 0) {
           if constexpr (kCG == 2) ptx::mbar_arrive_cluster(tempty_leader + 8u * (acc * kHalves + hb));
           else ptx::mbar_arrive(tempty_bar(acc * kHalves + hb));
@@ -482,34 +482,37 @@ fp8_blockwise_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gr
             if (stamp && c == 0) p.dbg[dbg_kb * 8 + 1] = clock64();       // loop top: about to wait for the first chunk
             ptx::tmem_ld_wait(v[c & 1]);
             if (stamp && c == 0) p.dbg[dbg_kb * 8 + 3] = clock64();       // first chunk of this K block in registers
-            bool deferred = false;
             if (c + 1 < NCH) {
               ptx::tmem_ld_32x32(taddr + uint32_t((c + 1) * 32), v[(c + 1) & 1]);
             } else {
               if (stamp) p.dbg[dbg_kb * 8 + 4] = clock64();                 // last chunk in registers: stage released
               release_stage();
               if (stamp) p.dbg[dbg_kb * 8 + 5] = clock64();                 // after fence + arrive
+              // Probe the next accumulator's barrier, fold in the first half of this chunk while the probe is in
+              // flight (its ~100-clk round trip is otherwise dead time in this in-order warp), then request the next
+              // block's first chunk and finish the second half under that load.
+              bool ready = false;
               if (more) {
                 taddr = stage_addr();
-                // (polling this barrier a chunk earlier, with try_wait or test_wait, was measured slower: the
-                //  probe either suspends the warp or sits in front of the FMAs it was meant to overlap)
-                if (ptx::mbar_try_wait(tfull_bar(acc * kHalves + hb), acc_phase)) {
-                  ptx::tc_fence_after();
-                  ptx::tmem_ld_32x32(taddr, v[0]);
-                  if (stamp) p.dbg[dbg_kb * 8 + 7] = clock64();             // next block's first tcgen05.ld issued
-                } else {
-                  deferred = true;
-                }
+                ready = ptx::mbar_try_wait(tfull_bar(acc * kHalves + hb), acc_phase);
               }
+#pragma unroll
+              for (int i = 0; i < 16; i += 2)
+                ptx::fma2(accum[c * 32 + i], accum[c * 32 + i + 1], v[c & 1][i], v[c & 1][i + 1], s);
+              if (more) {
+                if (!ready) ptx::mbar_wait(tfull_bar(acc * kHalves + hb), acc_phase);
+                ptx::tc_fence_after();
+                ptx::tmem_ld_32x32(taddr, v[0]);
+                if (stamp) p.dbg[dbg_kb * 8 + 7] = clock64();               // next block's first tcgen05.ld issued
+              }
+#pragma unroll
+              for (int i = 16; i < 32; i += 2)
+                ptx::fma2(accum[c * 32 + i], accum[c * 32 + i + 1], v[c & 1][i], v[c & 1][i + 1], s);
+              continue;
             }
 #pragma unroll
             for (int i = 0; i < 32; i += 2)
               ptx::fma2(accum[c * 32 + i], accum[c * 32 + i + 1], v[c & 1][i], v[c & 1][i + 1], s);
-            if (deferred) {
-              ptx::mbar_wait(tfull_bar(acc * kHalves + hb), acc_phase);
-              ptx::tc_fence_after();
-              ptx::tmem_ld_32x32(taddr, v[0]);
-            }
           }
           if (stamp) p.dbg[dbg_kb * 8 + 6] = clock64();                     // FMAs of this K block done
           ++dbg_kb;
