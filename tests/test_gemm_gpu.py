@@ -134,6 +134,28 @@ def test_k_contiguous_scales_vector_path(M, N, K, variant):
     check(out.cpu(), ref)
 
 
+@pytest.mark.parametrize("M,N,K", [(512, 512, 512), (2048, 4608, 7168), (4099, 2112, 1536), (4099, 7168, 5632), (8192, 2112, 9216)])
+@pytest.mark.parametrize("variant", [-1, 0, 3])
+def test_scale_relayout_path(M, N, K, variant):
+    """M-major scales_a / [G, NB] scales_b (the reference test's layouts, tests/test_fp8_blockwise_gemm.py:23-41) at
+    prefill M: with a workspace the op re-lays the scales out K-block-contiguous first.  Same bits as the call that
+    is handed K-contiguous scales; the call without a workspace (cp.async-staged scale path, no stream-K) agrees with
+    the oracle too.  The first three shapes are below the size where the re-layout pays and do not take it."""
+    a, b, sa, sb = O.make_gemm_inputs(M, N, K, seed=M + N)
+    ref = O.baseline_scaled_mm(a, b, sa, sb, torch.bfloat16)
+    ad, bd = a.to(DEV), b.t().contiguous().to(DEV).t()
+    sa_mmaj = sa.t().contiguous().to(DEV).t()               # (m, kb) at kb*M + m
+    sb_rows = sb.contiguous().to(DEV)                       # (kb, nb) at kb*NB + nb
+    assert sa_mmaj.stride(0) == 1 and sb_rows.stride(1) == 1
+    out = _ops._gemm(ad, bd, sa_mmaj, sb_rows, torch.bfloat16, variant)
+    out_nows = _ops._gemm(ad, bd, sa_mmaj, sb_rows, torch.bfloat16, variant, stream_k=False)
+    out_vec = _ops._gemm(ad, bd, sa.contiguous().to(DEV), sb.t().contiguous().to(DEV).t(), torch.bfloat16, variant)
+    torch.cuda.synchronize()
+    check(out.cpu(), ref)
+    assert torch.equal(out, out_vec)
+    check(out_nows.cpu(), ref)
+
+
 BIG = [("llama3_70b_gate_up", 8192, 28672, 8192), ("dsv3_mlp", 16384, 18432, 7168), ("dsv3_decode_wide", 256, 24576, 7168),
        ("dsv3_decode_ragged", 256, 2112, 7168), ("dsv3_decode_m1", 1, 24576, 7168)]
 
