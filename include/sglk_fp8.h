@@ -165,7 +165,9 @@ SGLK_API int sglk_fp8_blockwise_scaled_mm_allgather(const void* A, const void* B
                                            int64_t sb_stride_n, int out_dtype, int variant, int num_sms,
                                            void* workspace, int64_t workspace_bytes, void* stream);
 
-/* bytes of workspace with which the call above would use stream-K (0: it would not) */
+/* bytes of workspace the call above can make use of (0: none): [1 MiB tile counters][stream-K partials, if the
+ * scheduler would cut tiles][K-block-contiguous copies of sa / sb, for prefill-sized problems whose scales are not
+ * already laid out that way] */
 SGLK_API int64_t sglk_gemm_workspace_bytes(int64_t M, int64_t N, int64_t K, int variant, int num_sms);
 
 /* number of GEMM variants compiled in, and a printable name for each ("" if out of range) */
@@ -173,6 +175,10 @@ SGLK_API int sglk_gemm_num_variants(void);
 SGLK_API const char* sglk_gemm_variant_name(int variant);
 /* the variant the heuristic would pick for a problem */
 SGLK_API int sglk_gemm_pick_variant(int64_t M, int64_t N, int64_t K);
+
+/* Test hook: how the GEMM decides on stream-K when it has a workspace.  0 (default): cost model; 1: whenever the
+ * shape allows it (tests exercise the fixup on small shapes); -1: never.  Process-wide; returns the previous mode. */
+SGLK_API int sglk_debug_set_stream_k_mode(int mode);
 
 /* Device self-check of the quant kernel's division scheme against __fdiv_rn over every 16-bit
  * numerator (numerator_dtype = SGLK_BF16 or SGLK_F16) for `num_scales` scales; adds the number of

@@ -866,9 +866,14 @@ struct Plan {
   int64_t counter_bytes, partial_bytes;
 };
 
-// Tile shape, worker count and whether to cut the work stream-K style.  Stream-K is used when whole
-// tiles would leave the last wave under 90 % full (decode shapes: N=24576 -> 1.3 waves of 128-wide
-// tiles, N=2112 -> 17 tiles for 148 SMs) and a workspace is available.
+// Tile shape, worker count and whether to cut the work stream-K style (needs a workspace).  Cost model in units of
+// one K block of one tile: whole tiles cost waves * G per worker; stream-K costs ceil(tiles * G / workers) plus the
+// fixup — partials written, fenced and re-read by the last arriver while the MMA pipe idles (the accumulators live
+// in the epilogue warps' registers).  Measured on B200 the fixup is ~15 us for the 256-wide pair tiles (128 KB of
+// fp32 partial per CTA), i.e. ~30 K blocks; it scales with the partial size.  Decode shapes win clearly (N=24576:
+// 1.3 waves of 128-wide tiles, N=2112: 17 tiles for 148 SMs); short-K prefill shapes (4096x7168x2048: 75.8 us
+// stream-K vs 67.6 us whole tiles) do not and stay on whole tiles.
+static int g_stream_k_mode = 0;   // sglk_debug_set_stream_k_mode: 0 cost model, 1 whenever possible, -1 never
 static Plan make_plan(int64_t M, int64_t N, int64_t K, int variant, int num_sms, bool have_ws) {
   Plan pl;
   pl.variant = variant;
@@ -882,7 +887,10 @@ static Plan make_plan(int64_t M, int64_t N, int64_t K, int variant, int num_sms,
   const int64_t waves = (tiles + w0 - 1) / w0;
   const double eff = double(tiles) / double(waves * w0);
   const int64_t units = tiles * pl.num_k_blocks;
-  pl.stream_k = (have_ws && (variant < kNumProductVariants || variant >= 13) && pl.num_k_blocks >= 2 && eff < 0.9 && units >= w0) ? 1 : 0;
+  const int64_t sk_workers = tiles * 4 < w0 ? tiles * 4 : w0;
+  const int64_t sk_cost = (units + sk_workers - 1) / sk_workers + 30 * v.block_n / 256;
+  const bool possible = have_ws && (variant < kNumProductVariants || variant >= 13) && pl.num_k_blocks >= 2 && eff < 0.9 && units >= w0;
+  pl.stream_k = (possible && g_stream_k_mode >= 0 && (g_stream_k_mode > 0 || sk_cost < waves * pl.num_k_blocks)) ? 1 : 0;
   pl.workers = int(pl.stream_k ? w0 : (tiles < w0 ? tiles : w0));
   // few, large tiles (N=2112: 17): more than ~4 contributors per tile makes the last arriver's sequential
   // re-read of the partials longer than the K blocks it saves (measured: 68 workers 13.6 us, 148 workers 18.9 us)
@@ -1040,6 +1048,12 @@ extern "C" int sglk_fp8_blockwise_scaled_mm_allgather(const void* A, const void*
   return sglk::gemm_entry(A, B, sa, sb, C_local, M, N, K, lda, ldb, ldc, sa_stride_m, sa_stride_k, sb_stride_k,
                           sb_stride_n, out_dtype, variant, num_sms, workspace, workspace_bytes, stream,
                           C_multicast ? nullptr : C_peers, C_multicast ? 0 : num_peers, C_multicast);
+}
+
+extern "C" int sglk_debug_set_stream_k_mode(int mode) {
+  const int prev = sglk::g_stream_k_mode;
+  sglk::g_stream_k_mode = mode > 0 ? 1 : (mode < 0 ? -1 : 0);
+  return prev;
 }
 
 extern "C" int64_t sglk_gemm_workspace_bytes(int64_t M, int64_t N, int64_t K, int variant, int num_sms) {

@@ -120,7 +120,7 @@ def test_row_major_activation_scales():
 @pytest.mark.parametrize("M,N,K", [(1, 2112, 7168), (64, 24576, 2048), (200, 512, 1024), (300, 1280, 4096), (1024, 1024, 512),
                                    (129, 384, 1536), (16, 4096, 7168)])
 @pytest.mark.parametrize("variant", [-1, 0, 2, 3])
-def test_k_contiguous_scales_vector_path(M, N, K, variant):
+def test_k_contiguous_scales_vector_path(M, N, K, variant, force_stream_k):
     """scales_a row-major (the quant op's default output) and scales_b contiguous along K blocks (the view of a
     [N/128, K/128] weight-scale tensor): the promotion warps' 16-byte-per-4-blocks path, incl. stream-K segments that
     start in the middle of a group of four (K=1536 has 12 blocks: vector path; the others too)."""
@@ -182,13 +182,22 @@ def test_baseline_full_sizes(name, M, N, K):
     check(out[rows.to(DEV)].cpu(), ref)
 
 
+@pytest.fixture
+def force_stream_k():
+    """Stream-K whenever the shape allows it (the cost model keeps small test shapes on whole tiles)."""
+    lib = _lib.load()
+    prev = lib.sglk_debug_set_stream_k_mode(1)
+    yield
+    lib.sglk_debug_set_stream_k_mode(prev)
+
+
 STREAMK = [(1, 2112, 7168), (16, 24576, 7168), (64, 2112, 7168), (130, 4096, 2048), (256, 2112, 7168), (300, 1280, 4096),
            (128, 3200, 1024)]
 
 
 @pytest.mark.parametrize("M,N,K", STREAMK)
 @pytest.mark.parametrize("variant", [-1, 0, 2, 3, 5, 6, 13, 14])
-def test_stream_k_matches_whole_tiles_and_oracle(M, N, K, variant):
+def test_stream_k_matches_whole_tiles_and_oracle(M, N, K, variant, force_stream_k):
     """Stream-K scheduling (tiles cut across CTAs, summed through the workspace by the last arriver)
     gives the oracle's answer, is bit-reproducible, and leaves its counters zeroed for the next launch."""
     lib = _lib.load()
@@ -210,7 +219,7 @@ def test_stream_k_matches_whole_tiles_and_oracle(M, N, K, variant):
         assert need > 0, "decode shapes are expected to take the stream-K path"
 
 
-def test_stream_k_odd_sm_counts():
+def test_stream_k_odd_sm_counts(force_stream_k):
     """Unit ranges that start and end in the middle of tiles, for several worker counts."""
     M, N, K = 40, 1664, 2304
     a, b, sa, sb = O.make_gemm_inputs(M, N, K, seed=5)
