@@ -338,7 +338,7 @@ fp8_blockwise_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gr
           const uint64_t da = desc_hi | uint64_t((sa_addr & 0x3FFFFu) >> 4);
           const uint64_t db = desc_hi | uint64_t(((sa_addr + p.a_slot_bytes) & 0x3FFFFu) >> 4);
           if ((kDiag != 2 && kDiag != 3) || kb == kb0) ptx::mbar_wait(tempty_bar(acc), acc_phase ^ 1);
-          if (kDiag == 4 && blockIdx.x == 0 && lane == 0 && kb < 64 && tile == worker) p.dbg[kb * 8 + 0] = clock64();
+          if (kDiag >= 4 && blockIdx.x == 0 && lane == 0 && kb < 64 && tile == worker) p.dbg[kb * 8 + 0] = clock64();
           ptx::tc_fence_after();
           const uint32_t d_tmem = tmem_base_u + uint32_t(acc * BLOCK_N);
           const bool last_of_tile = (kDiag == 2 || kDiag == 3) && kb + 1 < kb1;
@@ -363,6 +363,23 @@ fp8_blockwise_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gr
             if (!last_of_tile) ptx::tc_commit<kCG>(tfull_bar(acc));   // partial for this K block complete
           }
           __syncwarp();
+          if (kDiag >= 4 && blockIdx.x == 0 && lane == 0 && kb < 64 && tile == worker) p.dbg[kb * 8 + 1] = clock64();   // MMAs + commits issued
+          if constexpr (kDiag == 10) {
+            // diagnostic: fully serialised — wait for this block's own commit before going on: the period is then
+            // issue + MMA execution + commit-to-observer latency
+            ptx::mbar_wait(tfull_bar(acc), acc_phase);
+            if (blockIdx.x == 0 && lane == 0 && kb < 64 && tile == worker) p.dbg[kb * 8 + 2] = clock64();
+          } else
+          if constexpr (kDiag >= 4) {
+            // timeline diagnostic: when does the commit of the PREVIOUS K block's MMAs land, as seen by a spinning
+            // thread?  (MMA(kb) is queued behind it, so this wait never delays the next issue.)
+            if (kb > kb0) {
+              const int pa = acc ^ 1;
+              const uint32_t pp = (acc == 0) ? (acc_phase ^ 1) : acc_phase;
+              ptx::mbar_wait(tfull_bar(pa), pp);
+              if (blockIdx.x == 0 && lane == 0 && kb - 1 < 64 && tile == worker) p.dbg[(kb - 1) * 8 + 2] = clock64();
+            }
+          }
           if (++stage == nstages) { stage = 0; phase ^= 1; }
           if (last_of_tile) continue;
           if (++acc == kAccStages) { acc = 0; acc_phase ^= 1; }
@@ -422,7 +439,25 @@ fp8_blockwise_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gr
       };
       auto stage_addr = [&]() { return tmem_base + lane_base + uint32_t(acc * BLOCK_N + half * NC); };
       uint32_t v[2][32];
-      if constexpr (kDiag == 1) {            // diagnostic: TMA + MMA pipeline with the per-block hand-off, no arithmetic
+      if constexpr (kDiag == 9) {   // diagnostic: immediate hand-off, then the promotion's FMA volume on stale registers
+        ptx::mbar_wait(tfull_bar(acc * kHalves + hb), acc_phase);
+        ptx::tc_fence_after();
+        ptx::tmem_ld_32x32(stage_addr(), v[0]);
+        ptx::tmem_ld_32x32(stage_addr() + 32u, v[1]);
+        ptx::tmem_ld_wait(v[0]);
+        ptx::tmem_ld_wait(v[1]);
+        for (int kb = kb0; kb < kb1; ++kb) {
+          ptx::mbar_wait(tfull_bar(acc * kHalves + hb), acc_phase);
+          ptx::tc_fence_after();
+          release_stage();
+          const float s = sa0 * sb0 + float(kb);
+#pragma unroll
+          for (int c = 0; c < NCH; ++c)
+#pragma unroll
+            for (int i = 0; i < 32; i += 2)
+              ptx::fma2(accum[c * 32 + i], accum[c * 32 + i + 1], v[c & 1][i], v[c & 1][i + 1], s);
+        }
+      } else if constexpr (kDiag == 1 || kDiag == 5 || kDiag == 10) {            // diagnostic: TMA + MMA pipeline with the per-block hand-off, no arithmetic
         for (int kb = kb0; kb < kb1; ++kb) {
           ptx::mbar_wait(tfull_bar(acc * kHalves + hb), acc_phase);
           ptx::tc_fence_after();
@@ -475,15 +510,17 @@ fp8_blockwise_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gr
           prefetch_scales();
           return s;
         };
-        auto promote = [&](const float s, const bool more) {
-          const bool stamp = kDiag == 4 && blockIdx.x == 0 && ew == 0 && lane == 0 && dbg_kb < 64 && tile == worker;
+        float4 a_nx, b_nx;                               // vector path: the next group's raw scales
+        const float4* sa4n = nullptr;
+        const float4* sb4n = nullptr;
+        auto promote = [&](const float s, const bool more, const bool fetch = false) {
+          const bool stamp = (kDiag == 4 || kDiag >= 6) && blockIdx.x == 0 && ew == 0 && lane == 0 && dbg_kb < 64 && tile == worker;
 #pragma unroll
           for (int c = 0; c < NCH; ++c) {
-            if (stamp && c == 0) p.dbg[dbg_kb * 8 + 1] = clock64();       // loop top: about to wait for the first chunk
-            ptx::tmem_ld_wait(v[c & 1]);
+            if constexpr (kDiag != 7 && kDiag != 8) ptx::tmem_ld_wait(v[c & 1]);
             if (stamp && c == 0) p.dbg[dbg_kb * 8 + 3] = clock64();       // first chunk of this K block in registers
             if (c + 1 < NCH) {
-              ptx::tmem_ld_32x32(taddr + uint32_t((c + 1) * 32), v[(c + 1) & 1]);
+              if constexpr (kDiag != 7 && kDiag != 8) ptx::tmem_ld_32x32(taddr + uint32_t((c + 1) * 32), v[(c + 1) & 1]);
             } else {
               if (stamp) p.dbg[dbg_kb * 8 + 4] = clock64();                 // last chunk in registers: stage released
               release_stage();
@@ -496,23 +533,33 @@ fp8_blockwise_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gr
                 taddr = stage_addr();
                 ready = ptx::mbar_try_wait(tfull_bar(acc * kHalves + hb), acc_phase);
               }
+              // the next group's scales are requested here, in the shadow of the hand-off wait, not at the group's
+              // loop top where the issue sits between this warp's first tcgen05.ld and its FMAs
+              if (fetch) {
+                a_nx = __ldg(sa4n);
+                b_nx = __ldg(sb4n);
+              }
+              if (kDiag != 6 && !(kDiag == 8 && (warp & 3) == 1))
 #pragma unroll
               for (int i = 0; i < 16; i += 2)
                 ptx::fma2(accum[c * 32 + i], accum[c * 32 + i + 1], v[c & 1][i], v[c & 1][i + 1], s);
               if (more) {
                 if (!ready) ptx::mbar_wait(tfull_bar(acc * kHalves + hb), acc_phase);
                 ptx::tc_fence_after();
-                ptx::tmem_ld_32x32(taddr, v[0]);
+                if constexpr (kDiag != 7 && kDiag != 8) ptx::tmem_ld_32x32(taddr, v[0]);
                 if (stamp) p.dbg[dbg_kb * 8 + 7] = clock64();               // next block's first tcgen05.ld issued
               }
+              if (kDiag != 6 && !(kDiag == 8 && (warp & 3) == 1))
 #pragma unroll
               for (int i = 16; i < 32; i += 2)
                 ptx::fma2(accum[c * 32 + i], accum[c * 32 + i + 1], v[c & 1][i], v[c & 1][i + 1], s);
               continue;
             }
+            if (kDiag != 6 && !(kDiag == 8 && (warp & 3) == 1))
 #pragma unroll
             for (int i = 0; i < 32; i += 2)
               ptx::fma2(accum[c * 32 + i], accum[c * 32 + i + 1], v[c & 1][i], v[c & 1][i + 1], s);
+            else accum[c] += s;
           }
           if (stamp) p.dbg[dbg_kb * 8 + 6] = clock64();                     // FMAs of this K block done
           ++dbg_kb;
@@ -527,23 +574,31 @@ fp8_blockwise_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gr
           const float4* sb4 = reinterpret_cast<const float4*>(sb_ptr);
           int g = kb0 >> 2;
           const int g_end = (kb1 + 3) >> 2;
-          float4 a_nx = row_ok ? __ldg(sa4 + g) : make_float4(0.f, 0.f, 0.f, 0.f);
-          float4 b_nx = __ldg(sb4 + g);
+          // (rows >= M read row 0's scales: in bounds, and those accumulator rows are never stored)
+          // running pointers, bumped by 16 bytes per group: anything derived from g is rematerialised by ptxas at
+          // every group boundary under this register pressure (S2R + LDCU + 64-bit IMAD chain, ~200 clk measured)
+          sa4n = sa4 + g;
+          sb4n = sb4 + g;
+          a_nx = __ldg(sa4n);
+          b_nx = __ldg(sb4n);
           ptx::mbar_wait(tfull_bar(acc * kHalves + hb), acc_phase);
           ptx::tc_fence_after();
           taddr = stage_addr();
           ptx::tmem_ld_32x32(taddr, v[0]);
+          if constexpr (kDiag == 7 || kDiag == 8) {     // diagnostic: FMAs on two chunks fetched once, no tcgen05.ld in the loop
+            ptx::tmem_ld_32x32(taddr + 32u, v[1]);
+            ptx::tmem_ld_wait(v[0]);
+            ptx::tmem_ld_wait(v[1]);
+          }
           for (; g < g_end; ++g) {
             const float s0 = a_nx.x * b_nx.x, s1 = a_nx.y * b_nx.y, s2 = a_nx.z * b_nx.z, s3 = a_nx.w * b_nx.w;
-            if (g + 1 < g_end) {
-              if (row_ok) a_nx = __ldg(sa4 + g + 1);
-              b_nx = __ldg(sb4 + g + 1);
-            }
+            ++sa4n; ++sb4n;
             const int kb = g << 2;
             if (kb >= kb0 && kb < kb1) promote(s0, kb + 1 < kb1);
             if (kb + 1 >= kb0 && kb + 1 < kb1) promote(s1, kb + 2 < kb1);
             if (kb + 2 >= kb0 && kb + 2 < kb1) promote(s2, kb + 3 < kb1);
-            if (kb + 3 >= kb0 && kb + 3 < kb1) promote(s3, kb + 4 < kb1);
+            // a following group exists exactly when block kb+4 is in range, and then block kb+3 is too
+            if (kb + 3 >= kb0 && kb + 3 < kb1) promote(s3, kb + 4 < kb1, kb + 4 < kb1);
           }
         } else {
           prefetch_scales();
@@ -789,6 +844,12 @@ static const Variant kVariants[] = {
     {"n256_s4_cta1_tma_splitn", 256, 4, 1, true},
     {"diag_n256_s6_cta2_timestamps", 256, 6, 2, true},
     {"diag_n256_s6_cta2_splitn_timestamps", 256, 6, 2, true},
+    {"diag_n256_s6_cta2_nopromote_timestamps", 256, 6, 2, true},
+    {"diag_n256_s6_cta2_ldtm_only_timestamps", 256, 6, 2, true},
+    {"diag_n256_s6_cta2_fma_only_timestamps", 256, 6, 2, true},
+    {"diag_n256_s6_cta2_fma_only_not_on_mma_scheduler_timestamps", 256, 6, 2, true},
+    {"diag_n256_s6_cta2_handoff_then_fma_timestamps", 256, 6, 2, true},
+    {"diag_n256_s6_cta2_serialised_timestamps", 256, 6, 2, true},
 };
 constexpr int kNumVariants = int(sizeof(kVariants) / sizeof(kVariants[0]));
 constexpr int kNumProductVariants = 7;   // ids 0..6; 7..12 are diagnostics; 13, 14 are product variants again
@@ -844,6 +905,12 @@ static int launch_by_id(int v, const CUtensorMap& ta, const CUtensorMap& tb, con
     case 14: return launch_variant<256, 4, 1, OutT, true, 0, true>(ta, tb, tc, p, num_sms, st);
     case 15: return launch_variant<256, 6, 2, OutT, true, 4>(ta, tb, tc, p, num_sms, st);
     case 16: return launch_variant<256, 6, 2, OutT, true, 4, true>(ta, tb, tc, p, num_sms, st);
+    case 17: return launch_variant<256, 6, 2, OutT, true, 5>(ta, tb, tc, p, num_sms, st);
+    case 18: return launch_variant<256, 6, 2, OutT, true, 6>(ta, tb, tc, p, num_sms, st);
+    case 19: return launch_variant<256, 6, 2, OutT, true, 7>(ta, tb, tc, p, num_sms, st);
+    case 20: return launch_variant<256, 6, 2, OutT, true, 8>(ta, tb, tc, p, num_sms, st);
+    case 21: return launch_variant<256, 6, 2, OutT, true, 9>(ta, tb, tc, p, num_sms, st);
+    case 22: return launch_variant<256, 6, 2, OutT, true, 10>(ta, tb, tc, p, num_sms, st);
     default: return SGLK_E_VARIANT;
   }
 }
@@ -960,7 +1027,7 @@ static int gemm_entry(const void* A, const void* B, const float* sa, const float
                             (reinterpret_cast<uintptr_t>(sa) & 15) == 0 && (reinterpret_cast<uintptr_t>(sb) & 15) == 0;
     const int64_t base = pl.stream_k ? pl.counter_bytes + pl.partial_bytes : kCounterAreaBytes;
     if (!vec_layout && pl.scale_bytes > 0 && workspace && workspace_bytes >= base + pl.scale_bytes &&
-        (reinterpret_cast<uintptr_t>(workspace) & 15) == 0 && variant != 15 && variant != 16) {
+        (reinterpret_cast<uintptr_t>(workspace) & 15) == 0 && variant < 15) {
       const int G = pl.num_k_blocks, NB = p.num_sb_cols;
       float* sa_t = reinterpret_cast<float*>(static_cast<char*>(workspace) + base);
       float* sb_t = sa_t + (int64_t(M) * G * 4 + 255) / 256 * 64;
@@ -975,7 +1042,7 @@ static int gemm_entry(const void* A, const void* B, const float* sa, const float
     }
   }
   p.dbg = nullptr;
-  if (variant == 15 || variant == 16) {   // timestamps diagnostic: the stamps go to the start of the partials area of the workspace
+  if (variant >= 15) {   // timestamps diagnostic: the stamps go to the start of the partials area of the workspace
     if (!workspace || workspace_bytes < kCounterAreaBytes + 64 * 8 * 8) return SGLK_E_ARG;
     p.dbg = reinterpret_cast<long long*>(static_cast<char*>(workspace) + kCounterAreaBytes);
   }
