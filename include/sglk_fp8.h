@@ -110,6 +110,30 @@ SGLK_API int sglk_silu_mul_per_token_group_quant_8bit(const void* input, void* o
                                              int64_t scale_stride, void* stream);
 
 /*
+ * Replaces: at::native::xpu::sgl_per_token_group_quant_8bit_v2, whole surface
+ *   /root/reference/src/sycl/per_token_group_quant_8bit_v2.cpp:714-843 (host), :176-330 (compute),
+ *   :464-563 (masked MoE layout), schema src/torch_extension_sycl.cc:399-402.
+ * input    : [num_experts, tokens_per_expert, hidden] (hidden*2 = gate|up when fuse_silu_and_mul), contiguous;
+ *            num_experts == 1 unless masked_m is given
+ * output_q : [num_experts, tokens_per_expert, hidden] codes
+ * output_s : row-major layouts as in the v1 entry point.  Column-major layouts use the v2 op's addressing: the scale
+ *            of (token t, group g) is written where the LOGICAL element (flat / G, flat % G), flat = t + g*tokens_per_expert,
+ *            of the column-major tensor lives ((flat % G) [/4] * scale_stride + flat / G, + e*scale_expert_stride) —
+ *            the "interleaved" pattern the reference's tests de-interleave
+ *            (tests/test_per_token_group_quant_8bit_v2.py:807-817); packed UE8M0 words also get their unused tail
+ *            bytes zeroed when G % 4 != 0 (…_v2.cpp:231-248).
+ * masked_m : optional device int32[num_experts]; tokens >= masked_m[e] of expert e are skipped (outputs untouched).
+ *            Only with column-major packed UE8M0 scales and fuse_silu_and_mul, like the reference (…_v2.cpp:779-783).
+ * scale_expert_stride : elements of the scale tensor's dtype between expert slabs (output_s.stride(0)).
+ */
+SGLK_API int sglk_per_token_group_quant_8bit_v2(const void* input, void* output_q, void* output_s,
+                                       int64_t num_experts, int64_t tokens_per_expert, int64_t hidden,
+                                       int64_t group_size, int in_dtype, int out_dtype, float eps, float min_8bit,
+                                       float max_8bit, int scale_ue8m0, int scale_layout, int64_t scale_stride,
+                                       int64_t scale_expert_stride, int fuse_silu_and_mul, const int32_t* masked_m,
+                                       void* stream);
+
+/*
  * Replaces: torch::Tensor fp8_blockwise_scaled_mm(mat_a, mat_b, scales_a, scales_b, out_dtype)
  *   declared /root/reference/include/sgl_kernel_ops.h:581-586, wrapped python/sgl_kernel/gemm.py:24-31,
  *   semantics pinned by tests/test_fp8_blockwise_gemm.py:23-63 (the reference ships no kernel).

@@ -97,6 +97,32 @@ def silu_and_mul_ref(x: torch.Tensor) -> torch.Tensor:
 # ----------------------------------------------------------------------------------------------
 # weight fabrication (test-side producers)
 # ----------------------------------------------------------------------------------------------
+def v2_column_major_interleave(s_logical: torch.Tensor) -> torch.Tensor:
+    """What the v2 op leaves in a COLUMN-major output_s, as the logical [T, G] tensor a caller indexes.
+
+    The reference kernel writes the scale of (token t, group g) to the logical slot (flat // G, flat % G) with
+    flat = t + g * T (/root/reference/src/sycl/per_token_group_quant_8bit_v2.cpp:200-229), i.e. the row-major
+    flattening of the logical tensor is the group-major list of scales.  Works on fp32 scales or UE8M0 bytes."""
+    T, G = s_logical.shape
+    return s_logical.t().contiguous().flatten().reshape(T, G)
+
+
+def v2_column_major_deinterleave(x_s: torch.Tensor) -> torch.Tensor:
+    """The inverse, exactly as the reference's test undoes it before comparing with its row-major oracle
+    (/root/reference/tests/test_per_token_group_quant_8bit_v2.py:811-817)."""
+    T, G = x_s.shape
+    return x_s.contiguous().flatten().reshape(G, T).T.contiguous()
+
+
+def unpack_ue8m0_words(x_s: torch.Tensor, num_groups: int) -> torch.Tensor:
+    """[T, ceil(G/4)] int32 words (any strides) -> [T, G] bytes, little-endian within a word
+    (`unpack_match_ref`, tests/test_per_token_group_quant_8bit_v2.py:631-704)."""
+    T = x_s.shape[0]
+    dense = torch.empty(x_s.numel(), dtype=x_s.dtype).copy_(x_s.reshape(-1))   # size-1 dims keep odd strides through .contiguous()
+    b = dense.view(torch.uint8).reshape(T, -1)
+    return b[:, :num_groups].contiguous()
+
+
 def ceil_div(a: int, b: int) -> int:
     return -(a // -b)
 

@@ -21,7 +21,9 @@ static void make_div(uint32_t d, uint32_t* mul, uint32_t* shift) {
 static int quant_dispatch(bool fuse, const void* input, void* output_q, void* output_s, int64_t num_groups,
                           int64_t groups_per_row, int64_t group_size, int64_t in_row_stride, int in_dtype,
                           int out_dtype, float eps, float min_8bit, float max_8bit, int scale_ue8m0,
-                          int scale_layout, int64_t scale_stride, void* stream) {
+                          int scale_layout, int64_t scale_stride, void* stream, int v2_interleave = 0,
+                          int64_t tokens_per_expert = 0, int64_t scale_expert_stride = 0,
+                          const int32_t* masked_m = nullptr) {
   if (num_groups < 0 || groups_per_row <= 0) return SGLK_E_SHAPE;
   if (num_groups == 0) return SGLK_OK;
   if (!input || !output_q || !output_s) return SGLK_E_NULL;
@@ -34,7 +36,7 @@ static int quant_dispatch(bool fuse, const void* input, void* output_q, void* ou
   const bool layout_is_ue8m0 = scale_layout >= SGLK_SCALE_UE8M0_ROW_MAJOR;
   if (layout_is_ue8m0 != (scale_ue8m0 != 0)) return SGLK_E_LAYOUT;
   if ((scale_layout == SGLK_SCALE_F32_COL_MAJOR || scale_layout == SGLK_SCALE_UE8M0_COL_PACKED) &&
-      scale_stride < num_groups / groups_per_row) return SGLK_E_STRIDE;
+      scale_stride < (tokens_per_expert > 0 ? tokens_per_expert : num_groups / groups_per_row)) return SGLK_E_STRIDE;
   const int esz = in_dtype == SGLK_F32 ? 4 : 2;
   if (reinterpret_cast<uintptr_t>(input) % esz != 0) return SGLK_E_STRIDE;
   if (!(max_8bit > 0.0f) || !(min_8bit < max_8bit)) return SGLK_E_ARG;
@@ -49,6 +51,10 @@ static int quant_dispatch(bool fuse, const void* input, void* output_q, void* ou
   p.eps = eps; p.qmin = min_8bit; p.qmax = max_8bit;
   p.rcp_qmax = 1.0f / max_8bit;                     // correctly rounded on the host
   p.need_clamp = (out_dtype == SGLK_INT8 || min_8bit > -448.0f || max_8bit < 448.0f) ? 1 : 0;
+  p.v2_interleave = v2_interleave;
+  p.tokens_per_expert = uint32_t(tokens_per_expert > 0 ? tokens_per_expert : num_groups / groups_per_row);
+  p.scale_expert_stride = scale_expert_stride;
+  p.masked_m = masked_m;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   switch (in_dtype) {
     case SGLK_BF16: return quant_launch_bf16(fuse, group_size, out_dtype, scale_layout, input, output_q, output_s, p, st);
@@ -99,6 +105,31 @@ extern "C" int sglk_silu_mul_per_token_group_quant_8bit(const void* input, void*
   return sglk::quant_dispatch(true, input, output_q, output_s, num_tokens * gpr, gpr, group_size, 2 * hidden,
                               in_dtype, out_dtype, eps, min_8bit, max_8bit, scale_ue8m0, scale_layout,
                               scale_stride, stream);
+}
+
+extern "C" int sglk_per_token_group_quant_8bit_v2(const void* input, void* output_q, void* output_s,
+                                                  int64_t num_experts, int64_t tokens_per_expert, int64_t hidden,
+                                                  int64_t group_size, int in_dtype, int out_dtype, float eps,
+                                                  float min_8bit, float max_8bit, int scale_ue8m0, int scale_layout,
+                                                  int64_t scale_stride, int64_t scale_expert_stride,
+                                                  int fuse_silu_and_mul, const int32_t* masked_m, void* stream) {
+  if (num_experts < 0 || tokens_per_expert < 0 || hidden <= 0 || group_size <= 0 || hidden % group_size != 0)
+    return SGLK_E_SHAPE;
+  if (num_experts * tokens_per_expert == 0) return SGLK_OK;
+  const int64_t gpr = hidden / group_size;
+  if (tokens_per_expert * gpr >= (int64_t(1) << 31)) return SGLK_E_SHAPE;        // the interleave index is 32-bit
+  const bool col = scale_layout == SGLK_SCALE_F32_COL_MAJOR || scale_layout == SGLK_SCALE_UE8M0_COL_PACKED;
+  if (masked_m != nullptr) {
+    // the reference dispatches its masked scheduler only for this combination (…_v2.cpp:779-783)
+    if (!(col && scale_ue8m0 && fuse_silu_and_mul)) return SGLK_E_LAYOUT;
+    if (scale_expert_stride < 0) return SGLK_E_STRIDE;
+  } else if (num_experts != 1) {
+    return SGLK_E_SHAPE;
+  }
+  return sglk::quant_dispatch(fuse_silu_and_mul != 0, input, output_q, output_s, num_experts * tokens_per_expert * gpr,
+                              gpr, group_size, (fuse_silu_and_mul ? 2 : 1) * hidden, in_dtype, out_dtype, eps, min_8bit,
+                              max_8bit, scale_ue8m0, scale_layout, scale_stride, stream, col ? 1 : 0,
+                              tokens_per_expert, scale_expert_stride, masked_m);
 }
 
 extern "C" int sglk_debug_check_division(const float* scales, int64_t num_scales, int numerator_dtype,

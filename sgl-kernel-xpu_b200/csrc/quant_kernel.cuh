@@ -33,6 +33,10 @@
 
 namespace sglk {
 
+__device__ __forceinline__ uint32_t fast_div(uint32_t n, uint32_t mul, uint32_t shift) {
+  return mul == 0 ? (n >> shift) : (__umulhi(n, mul) >> shift);
+}
+
 struct QuantParams {
   int64_t num_groups;       // total groups
   uint32_t groups_per_row;  // hidden / group
@@ -42,11 +46,46 @@ struct QuantParams {
   int64_t in_row_stride;    // elements between input rows (fused mode: 2*hidden)
   float eps, qmin, qmax, rcp_qmax;
   int need_clamp;           // 0 when the e4m3 satfinite conversion already implies [qmin, qmax]
+  // ---- v2 op only (sgl_per_token_group_quant_8bit_v2; zero / null for the v1 entry points) ----
+  int v2_interleave;              // column-major scales use the v2 op's "interleaved" addressing (see col_major_slot)
+  uint32_t tokens_per_expert;     // rows per expert slab (== number of tokens when there is no expert dimension)
+  int64_t scale_expert_stride;    // scale elements (floats / packed int32 words) between expert slabs
+  const int32_t* masked_m;        // masked MoE layout: only tokens [0, masked_m[e]) of expert e are quantised
 };
 
-__device__ __forceinline__ uint32_t fast_div(uint32_t n, uint32_t mul, uint32_t shift) {
-  return mul == 0 ? (n >> shift) : (__umulhi(n, mul) >> shift);
+// Where the scale of (row, col = group in row) goes for the column-major layouts: element index of the logical
+// (orow, ocol) slot, and the expert slab offset.  v1: (row, col) itself.  v2: the reference kernel flattens
+// column-major, flat = token + col * tokens_per_expert, and re-splits that index ROW-major,
+// (flat / G, flat % G) (per_token_group_quant_8bit_v2.cpp:200-229) — its tests undo exactly this
+// (tests/test_per_token_group_quant_8bit_v2.py:807-817).
+__device__ __forceinline__ void col_major_slot(const QuantParams& p, uint32_t row, uint32_t col, uint32_t& orow,
+                                               uint32_t& ocol, int64_t& slab) {
+  orow = row; ocol = col; slab = 0;
+  if (p.v2_interleave) {
+    const uint32_t e = row / p.tokens_per_expert;
+    const uint32_t flat = (row - e * p.tokens_per_expert) + col * p.tokens_per_expert;
+    orow = fast_div(flat, p.div_mul, p.div_shift);
+    ocol = flat - orow * p.groups_per_row;
+    slab = int64_t(e) * p.scale_expert_stride;
+  }
 }
+// packed UE8M0 word (orow, ocol/4) lives at (ocol/4)*stride + orow; the v2 op also zeroes the unused tail bytes of
+// the last word of a row when G % 4 != 0 (per_token_group_quant_8bit_v2.cpp:231-248)
+__device__ __forceinline__ void store_packed_ue8m0(void* s_out, const QuantParams& p, uint32_t orow, uint32_t ocol,
+                                                   int64_t slab, uint8_t e8) {
+  uint8_t* dst = reinterpret_cast<uint8_t*>(s_out) + (slab + int64_t(ocol >> 2) * p.scale_stride + orow) * 4 + (ocol & 3);
+  *dst = e8;
+  if (p.v2_interleave && ocol == p.groups_per_row - 1)
+    for (uint32_t i = (ocol & 3) + 1; i < 4; ++i) dst[i - (ocol & 3)] = 0;
+}
+// masked MoE layout: is the token that owns group `gid` below its expert's count?
+__device__ __forceinline__ bool group_active(const QuantParams& p, int64_t gid) {
+  if (p.masked_m == nullptr) return true;
+  const uint32_t row = fast_div(uint32_t(gid), p.div_mul, p.div_shift);
+  const uint32_t e = row / p.tokens_per_expert;
+  return int32_t(row - e * p.tokens_per_expert) < __ldg(p.masked_m + e);
+}
+
 
 // 32-byte streaming load: no L1 allocation, evict-first in L2 (the activations are read once; the
 // codes written next to them should stay resident for the GEMM that follows)
@@ -147,7 +186,7 @@ ptgq_kernel(const T* __restrict__ x, uint8_t* __restrict__ q, void* __restrict__
 #pragma unroll
     for (int u = 0; u < U; ++u) {
       const int64_t slot = chunk0 + u * C::kThreads + tid;
-      if (full || slot < total_slots) {
+      if ((full || slot < total_slots) && group_active(p, slot / LPG)) {
         const int64_t gid = slot / LPG;
         const int l = int(slot % LPG);
         int64_t off;
@@ -177,8 +216,8 @@ ptgq_kernel(const T* __restrict__ x, uint8_t* __restrict__ q, void* __restrict__
 #pragma unroll
     for (int u = 0; u < U; ++u) {
       const int64_t slot = chunk0 + u * C::kThreads + tid;
-      const bool valid = full || slot < total_slots;
       const int64_t gid = slot / LPG;
+      const bool valid = (full || slot < total_slots) && group_active(p, gid);   // uniform across the group's lanes
       const int l = int(slot % LPG);
       float2 f[VPL][EPV / 2];
       float amax = 0.0f;
@@ -222,11 +261,13 @@ ptgq_kernel(const T* __restrict__ x, uint8_t* __restrict__ q, void* __restrict__
         } else {
           const uint32_t row = fast_div(uint32_t(gid), p.div_mul, p.div_shift);
           const uint32_t col = uint32_t(gid) - row * p.groups_per_row;
+          uint32_t orow, ocol;
+          int64_t slab;
+          col_major_slot(p, row, col, orow, ocol, slab);
           if constexpr (kLayout == SGLK_SCALE_F32_COL_MAJOR) {
-            reinterpret_cast<float*>(s_out)[int64_t(col) * p.scale_stride + row] = scale;
-          } else {  // 4 exponent bytes per int32 word; word (row, col/4) lives at (col/4)*stride + row
-            reinterpret_cast<uint8_t*>(s_out)[(int64_t(col >> 2) * p.scale_stride + row) * 4 + (col & 3)] =
-                uint8_t(exp2s + 127);
+            reinterpret_cast<float*>(s_out)[slab + int64_t(ocol) * p.scale_stride + orow] = scale;
+          } else {  // 4 exponent bytes per int32 word
+            store_packed_ue8m0(s_out, p, orow, ocol, slab, uint8_t(exp2s + 127));
           }
         }
       }
@@ -295,7 +336,7 @@ ptgq_generic_kernel(const T* __restrict__ x, uint8_t* __restrict__ q, void* __re
   const int team = threadIdx.x >> 3, tl = threadIdx.x & 7;
   for (int64_t base = int64_t(blockIdx.x) * 32; base < p.num_groups; base += int64_t(gridDim.x) * 32) {
     const int64_t gid = base + team;
-    const bool valid = gid < p.num_groups;
+    const bool valid = gid < p.num_groups && group_active(p, gid);
     const uint32_t row = valid ? fast_div(uint32_t(gid), p.div_mul, p.div_shift) : 0;
     const uint32_t col = valid ? uint32_t(gid) - row * p.groups_per_row : 0;
     const T* src = fuse ? x + int64_t(row) * p.in_row_stride + int64_t(col) * group : x + gid * group;
@@ -320,8 +361,13 @@ ptgq_generic_kernel(const T* __restrict__ x, uint8_t* __restrict__ q, void* __re
       if (tl == 0) {
         if (layout == SGLK_SCALE_F32_ROW_MAJOR) reinterpret_cast<float*>(s_out)[gid] = scale;
         else if (layout == SGLK_SCALE_UE8M0_ROW_MAJOR) reinterpret_cast<uint8_t*>(s_out)[gid] = uint8_t(exp2s + 127);
-        else if (layout == SGLK_SCALE_F32_COL_MAJOR) reinterpret_cast<float*>(s_out)[int64_t(col) * p.scale_stride + row] = scale;
-        else reinterpret_cast<uint8_t*>(s_out)[(int64_t(col >> 2) * p.scale_stride + row) * 4 + (col & 3)] = uint8_t(exp2s + 127);
+        else {
+          uint32_t orow, ocol;
+          int64_t slab;
+          col_major_slot(p, row, col, orow, ocol, slab);
+          if (layout == SGLK_SCALE_F32_COL_MAJOR) reinterpret_cast<float*>(s_out)[slab + int64_t(ocol) * p.scale_stride + orow] = scale;
+          else store_packed_ue8m0(s_out, p, orow, ocol, slab, uint8_t(exp2s + 127));
+        }
       }
       for (int i = tl; i < group; i += 8) {
         float v = float(src[i]);

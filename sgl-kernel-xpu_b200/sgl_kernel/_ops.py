@@ -118,10 +118,66 @@ def _quant_v1(input, output_q, output_s, group_size, eps, fp8_min, fp8_max, scal
 def _quant_v2(input, output_q, output_s, group_size, eps, fp8_min, fp8_max, scale_ue8m0,
               fuse_silu_and_mul, masked_m: Optional[torch.Tensor]):
     """sgl_per_token_group_quant_8bit_v2, src/sycl/per_token_group_quant_8bit_v2.cpp:714-843.
-    The masked MoE layout (:464-563) is a 'next' row of SURVEY.md §8(f) and is rejected loudly."""
-    _check(masked_m is None, "sgl_per_token_group_quant_8bit_v2: masked_m layout is not implemented in the B200 build")
-    _quant_common(input, output_q, output_s, group_size, eps, fp8_min, fp8_max, scale_ue8m0,
-                  bool(fuse_silu_and_mul), _SUPPORTED_GROUPS_V2 + (256, 512), "sgl_per_token_group_quant_8bit_v2")
+
+    Differences from the v1 op that a caller can see, all reproduced: eps must be 1e-10 (:732) and (min, max) the
+    destination type's own range (:780-781); column-major scales are written with the op's interleaved addressing
+    (:200-229); `masked_m` selects the masked MoE layout — input [E, T, 2*hidden], 3-D output_s, only tokens
+    < masked_m[e] quantised — which the reference dispatches only for column-major packed UE8M0 scales together
+    with fuse_silu_and_mul (:783-790)."""
+    name = "sgl_per_token_group_quant_8bit_v2"
+    fuse = bool(fuse_silu_and_mul)
+    _check(abs(1e-10 - eps) < 1e-13, f"{name}: eps must be 1e-10")
+    _check(input.is_cuda and output_q.is_cuda and output_s.is_cuda, f"{name}: tensors must be CUDA tensors")
+    _check(output_q.dtype in _OUT_DTYPES, f"{name}: output_q dtype must be Int8 or Float8_e4m3fn, got {output_q.dtype}")
+    lo, hi = (-448.0, 448.0) if output_q.dtype == torch.float8_e4m3fn else (-128.0, 127.0)
+    _check(fp8_min == lo and fp8_max == hi, f"{name}: min_8bit / max_8bit must be {lo} / {hi} for {output_q.dtype}")
+    masked = masked_m is not None
+    _check(output_s.dim() == (3 if masked else 2), f"Expected output_s.dim() == {3 if masked else 2}")
+    col_major = output_s.stride(-2) < output_s.stride(-1)
+    if not masked and not col_major:       # row-major layouts: identical to the v1 op
+        _quant_common(input, output_q, output_s, group_size, eps, fp8_min, fp8_max, scale_ue8m0, fuse,
+                      _SUPPORTED_GROUPS_V2 + (256, 512), name)
+        return
+    _check(input.numel() > 0, f"{name}: empty input")
+    _check(input.is_contiguous(), "input must be contiguous")
+    _check(output_q.is_contiguous(), "output_q must be contiguous")
+    _check(input.dtype in (torch.bfloat16, torch.float16), f"{name}: input dtype must be Float16 or BFloat16, got {input.dtype}")
+    _check(group_size in _SUPPORTED_GROUPS_V2 + (256, 512), f"Unsupported group_size: {group_size}")
+    hidden = output_q.size(-1)
+    tokens = output_q.size(-2)
+    _check(hidden % group_size == 0, "hidden size must be divisible by group_size")
+    _check(input.size(-1) == hidden * (2 if fuse else 1) and input.numel() == output_q.numel() * (2 if fuse else 1),
+           "input / output_q shapes do not match")
+    if masked:
+        _check(col_major and bool(scale_ue8m0) and fuse,
+               f"{name}: masked_m needs column-major UE8M0 scales and fuse_silu_and_mul (the only masked form of the op)")
+        _check(input.dim() == 3 and output_q.dim() == 3, "masked layout: input and output_q must be [experts, tokens, hidden]")
+        experts = input.size(0)
+        _check(masked_m.is_cuda and masked_m.dtype == torch.int32 and masked_m.is_contiguous() and masked_m.numel() == experts,
+               "masked_m must be a contiguous CUDA int32 tensor with one entry per expert")
+        _check(output_s.size(0) == experts, "output_s must have one slab per expert")
+        expert_stride = output_s.stride(0)
+    else:
+        experts, expert_stride = 1, 0
+        tokens = output_q.numel() // hidden
+    if scale_ue8m0:
+        _check(output_s.dtype == torch.int32, "UE8M0 column-major scales must be packed int32")
+        layout = _lib.SCALE_UE8M0_COL_PACKED
+        _check(output_s.size(-1) * 4 >= hidden // group_size, "output_s has too few packed columns")
+    else:
+        _check(output_s.dtype == torch.float32, "output_s must be float32 unless scale_ue8m0")
+        layout = _lib.SCALE_F32_COL_MAJOR
+        _check(output_s.size(-1) >= hidden // group_size, "output_s has too few columns")
+    _check(output_s.stride(-2) == 1, "column-major output_s must have unit stride along tokens")
+    _check(output_s.size(-2) >= tokens, "output_s has fewer rows than tokens")
+    lib = _lib.load()
+    with torch.cuda.device(input.device):
+        rc = lib.sglk_per_token_group_quant_8bit_v2(
+            input.data_ptr(), output_q.data_ptr(), output_s.data_ptr(), experts, tokens, hidden, group_size,
+            _IN_DTYPES[input.dtype], _OUT_DTYPES[output_q.dtype], eps, fp8_min, fp8_max, int(bool(scale_ue8m0)),
+            layout, output_s.stride(-1), expert_stride, int(fuse), masked_m.data_ptr() if masked else None,
+            _stream_ptr(input))
+    _lib.check(rc, name)
 
 
 _GEMM_OUT = {torch.bfloat16: _lib.BF16, torch.float16: _lib.F16}

@@ -158,3 +158,17 @@ def test_division_scheme_exact_on_sampled_scales():
         bad += b
         n += c
     assert n > 1_000_000 and bad == 0
+
+
+def test_v2_interleave_matches_the_reference_comment():
+    """per_token_group_quant_8bit_v2.cpp:203-212 spells the pattern out for 2 tokens x 3 groups:
+    logical [[t0_g0, t1_g0, t0_g1], [t1_g1, t0_g2, t1_g2]]; the test-side inverse is :811-817."""
+    s = torch.tensor([[0.0, 1.0, 2.0], [10.0, 11.0, 12.0]])          # s[t, g] = 10 t + g
+    inter = O.v2_column_major_interleave(s)
+    assert inter.tolist() == [[0.0, 10.0, 1.0], [11.0, 2.0, 12.0]]
+    g = torch.Generator().manual_seed(0)
+    for T, G in [(1, 1), (5, 3), (4, 56), (127, 13)]:
+        r = torch.rand(T, G, generator=g)
+        assert torch.equal(O.v2_column_major_deinterleave(O.v2_column_major_interleave(r)), r)
+    words = torch.tensor([[0x04030201, 0x00000605]], dtype=torch.int32)
+    assert O.unpack_ue8m0_words(words, 6).tolist() == [[1, 2, 3, 4, 5, 6]]

@@ -223,6 +223,113 @@ def test_fused_silu_mul_v2():
     assert int((d >= 2).sum()) == 0 and float((d == 1).sum()) / d.numel() < 0.005
 
 
+V2_COL_SHAPES = [(1, 128), (4, 384), (16, 1536), (64, 512), (127, 1664), (128, 2048), (512, 7168), (1024, 4096)]
+
+
+@pytest.mark.parametrize("m,k", V2_COL_SHAPES)
+@pytest.mark.parametrize("group", [64, 128])
+@pytest.mark.parametrize("aligned", [False, True])
+def test_v2_column_major_scales_are_interleaved(m, k, group, aligned):
+    """v2 op, column-major fp32 scales: the reference kernel's interleaved addressing
+    (per_token_group_quant_8bit_v2.cpp:200-229).  Checked the way the reference's own test does
+    (tests/test_per_token_group_quant_8bit_v2.py:807-828: de-interleave, compare with the row-major oracle) — here
+    bit for bit — and against the forward restatement in the oracle."""
+    torch.manual_seed(m * 7 + k)
+    x = torch.randn(m, k, dtype=torch.bfloat16)
+    q, s = run_quant(x, group, column_major=True, tma_aligned=aligned, enable_v2=True)
+    q_ref, s_ref = O.per_token_group_quant_fp8_ref(x, group, EPS)
+    assert_bits_equal(q, O.v2_column_major_deinterleave(s), q_ref, s_ref)
+    assert torch.equal(s.contiguous(), O.v2_column_major_interleave(s_ref))
+
+
+@pytest.mark.parametrize("m,k", V2_COL_SHAPES + [(40, 640), (9, 896)])
+@pytest.mark.parametrize("fuse", [False, True])
+def test_v2_column_major_packed_ue8m0(m, k, fuse):
+    """v2 op, packed UE8M0 column-major scales (+ fused silu*mul): same interleave on the unpacked bytes, unused
+    tail bytes of the last word zeroed when G % 4 != 0 (…_v2.cpp:231-248).  The UE8M0 bytes are the one output the
+    reference's tests compare exactly."""
+    torch.manual_seed(m + k)
+    G = k // 128
+    x = torch.randn(m, k * (2 if fuse else 1), dtype=torch.bfloat16)
+    xd = x.to(DEV)
+    q = torch.empty(m, k, dtype=torch.float8_e4m3fn, device=DEV)
+    s = sgl_kernel.create_per_token_group_quant_fp8_output_scale((m, k), DEV, 128, True, True, True)
+    s.fill_(-1)                                        # so that zeroed tail bytes are seen to be written
+    sgl_kernel.sgl_per_token_group_quant_8bit(xd, q, s, 128, EPS, -448.0, 448.0, True, fuse, None, enable_v2=True)
+    torch.cuda.synchronize()
+    y = O.silu_and_mul_ref(x).contiguous() if fuse else x
+    q_ref, s_ref = O.per_token_group_quant_fp8_ref(y, 128, EPS, scale_ue8m0=True)
+    bytes_ref = O.ue8m0_scale_bytes_ref(y, 128, EPS)
+    got = O.unpack_ue8m0_words(s.cpu(), G)
+    assert torch.equal(O.v2_column_major_deinterleave(got), bytes_ref)
+    if G % 4:
+        words = O.unpack_ue8m0_words(s.cpu(), (G + 3) // 4 * 4)
+        # logical row r, last packed word: bytes past G % 4 are zero wherever the row's last group was written
+        assert int(words[:, G:(G + 3) // 4 * 4].to(torch.int32).abs().sum()) == 0
+    d = (q.cpu().view(torch.uint8).to(torch.int16) - q_ref.view(torch.uint8).to(torch.int16)).abs()
+    if fuse:
+        assert int((d >= 2).sum()) == 0 and float((d == 1).sum()) / d.numel() < 0.005
+    else:
+        assert int(d.sum()) == 0
+
+
+@pytest.mark.parametrize("experts,tokens,hidden,counts", [(4, 16, 2048, [16, 0, 5, 9]), (8, 64, 2048, [64, 1, 0, 33, 64, 7, 12, 63]),
+                                                           (2, 128, 1024, [100, 128]), (3, 8, 1152, [8, 3, 0])])
+def test_v2_masked_moe_layout(experts, tokens, hidden, counts):
+    """v2 op, masked MoE layout (…_v2.cpp:464-563): input [E, T, 2*hidden], only tokens < masked_m[e] are quantised,
+    scales go to expert slab e of the 3-D packed UE8M0 column-major tensor with the same interleave over the slab's
+    T rows; everything else is left untouched.  (The reference's own masked tests are commented out,
+    tests/test_per_token_group_quant_8bit_v2.py:376-399, so this pins the kernel's addressing, restated.)"""
+    torch.manual_seed(experts * 100 + tokens)
+    G = hidden // 128
+    x = torch.randn(experts, tokens, 2 * hidden, dtype=torch.bfloat16)
+    masked_m = torch.tensor(counts, dtype=torch.int32)
+    q = torch.full((experts, tokens, hidden), 0x55, dtype=torch.uint8, device=DEV).view(torch.float8_e4m3fn)
+    s = sgl_kernel.create_per_token_group_quant_fp8_output_scale((experts, tokens, hidden), DEV, 128, True, True, True)
+    s.fill_(0x5A5A5A5A)
+    sgl_kernel.sgl_per_token_group_quant_8bit(x.to(DEV), q, s, 128, EPS, -448.0, 448.0, True, True, masked_m.to(DEV), enable_v2=True)
+    torch.cuda.synchronize()
+    qc, sc = q.cpu().view(torch.uint8), s.cpu()
+    for e in range(experts):
+        n = counts[e]
+        y = O.silu_and_mul_ref(x[e]).contiguous()
+        q_ref, _ = O.per_token_group_quant_fp8_ref(y, 128, EPS, scale_ue8m0=True)
+        bytes_ref = O.ue8m0_scale_bytes_ref(y, 128, EPS)
+        d = (qc[e, :n].to(torch.int16) - q_ref[:n].view(torch.uint8).to(torch.int16)).abs()
+        assert int((d >= 2).sum()) == 0 and (n == 0 or float((d == 1).sum()) / d.numel() < 0.005)
+        assert bool((qc[e, n:] == 0x55).all()), "codes of masked tokens were touched"
+        got = O.unpack_ue8m0_words(sc[e], (G + 3) // 4 * 4)            # [T, Gpad] logical bytes of the slab
+        expect = torch.full((tokens, (G + 3) // 4 * 4), 0x5A, dtype=torch.uint8)
+        for t in range(n):
+            for g in range(G):
+                flat = t + g * tokens
+                expect[flat // G, flat % G] = bytes_ref[t, g]
+        # tail-byte zeroing follows the slot the LAST logical group lands in (…_v2.cpp:231-248)
+        for t in range(n):
+            for g in range(G):
+                flat = t + g * tokens
+                if flat % G == G - 1 and G % 4:
+                    expect[flat // G, G:] = 0
+        assert torch.equal(got, expect), f"expert {e}"
+
+
+def test_v2_argument_checks():
+    x = torch.randn(8, 256, dtype=torch.bfloat16, device=DEV)
+    q = torch.empty(8, 256, dtype=torch.float8_e4m3fn, device=DEV)
+    s = torch.empty(8, 2, device=DEV)
+    v2 = torch.ops.sgl_kernel.sgl_per_token_group_quant_8bit_v2.default
+    with pytest.raises(RuntimeError, match="eps"):
+        v2(x, q, s, 128, 1e-6, -448.0, 448.0, False, False, None)
+    with pytest.raises(RuntimeError, match="min_8bit"):
+        v2(x, q, s, 128, EPS, -224.0, 224.0, False, False, None)
+    with pytest.raises(RuntimeError, match="output_s.dim"):
+        v2(x, q, s, 128, EPS, -448.0, 448.0, False, False, torch.zeros(1, dtype=torch.int32, device=DEV))
+    s3 = torch.empty(1, 8, 2, device=DEV)
+    with pytest.raises(RuntimeError, match="masked_m needs"):
+        v2(x.view(1, 8, 256), q.view(1, 8, 256), s3, 128, EPS, -448.0, 448.0, False, False,
+           torch.zeros(1, dtype=torch.int32, device=DEV))
+
+
 def test_division_scheme_on_device():
     """Exactness of the 3-op division against __fdiv_rn for every bf16 numerator, on the device."""
     torch.manual_seed(5)
@@ -253,7 +360,7 @@ def test_error_behaviour():
         f(x, q.view(torch.uint8), s, 128, EPS, -448.0, 448.0, False)
     with pytest.raises(RuntimeError, match="dim"):
         f(x, q, s.view(-1), 128, EPS, -448.0, 448.0, False)
-    with pytest.raises(RuntimeError, match="masked_m"):
+    with pytest.raises(RuntimeError, match="output_s.dim"):     # masked layout wants 3-D scales (…_v2.cpp:739)
         torch.ops.sgl_kernel.sgl_per_token_group_quant_8bit_v2.default(
             x, q, s, 128, EPS, -448.0, 448.0, False, False, torch.zeros(1, device=DEV, dtype=torch.int32))
 
