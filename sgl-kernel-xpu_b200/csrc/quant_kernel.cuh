@@ -165,7 +165,9 @@ struct QuantCfg {
   static_assert(GROUP % EPV == 0, "group must be a whole number of 32-byte vectors");
 };
 
-template <typename T, int GROUP, bool kInt8, int kLayout, bool kFuse>
+// kV2: the v2 op's column-major addressing and masked MoE layout (compiled out of the v1 instantiations: the extra
+// parameter reads and the predicate cost the streaming kernel 5-8 % when they were runtime switches)
+template <typename T, int GROUP, bool kInt8, int kLayout, bool kFuse, bool kV2 = false>
 __global__ void __launch_bounds__(256)
 ptgq_kernel(const T* __restrict__ x, uint8_t* __restrict__ q, void* __restrict__ s_out, const QuantParams p) {
   using C = QuantCfg<T, GROUP, kInt8, kLayout, kFuse>;
@@ -186,7 +188,7 @@ ptgq_kernel(const T* __restrict__ x, uint8_t* __restrict__ q, void* __restrict__
 #pragma unroll
     for (int u = 0; u < U; ++u) {
       const int64_t slot = chunk0 + u * C::kThreads + tid;
-      if ((full || slot < total_slots) && group_active(p, slot / LPG)) {
+      if ((full || slot < total_slots) && (!kV2 || group_active(p, slot / LPG))) {
         const int64_t gid = slot / LPG;
         const int l = int(slot % LPG);
         int64_t off;
@@ -217,7 +219,7 @@ ptgq_kernel(const T* __restrict__ x, uint8_t* __restrict__ q, void* __restrict__
     for (int u = 0; u < U; ++u) {
       const int64_t slot = chunk0 + u * C::kThreads + tid;
       const int64_t gid = slot / LPG;
-      const bool valid = (full || slot < total_slots) && group_active(p, gid);   // uniform across the group's lanes
+      const bool valid = (full || slot < total_slots) && (!kV2 || group_active(p, gid));   // uniform across the group's lanes
       const int l = int(slot % LPG);
       float2 f[VPL][EPV / 2];
       float amax = 0.0f;
@@ -261,13 +263,19 @@ ptgq_kernel(const T* __restrict__ x, uint8_t* __restrict__ q, void* __restrict__
         } else {
           const uint32_t row = fast_div(uint32_t(gid), p.div_mul, p.div_shift);
           const uint32_t col = uint32_t(gid) - row * p.groups_per_row;
-          uint32_t orow, ocol;
-          int64_t slab;
-          col_major_slot(p, row, col, orow, ocol, slab);
-          if constexpr (kLayout == SGLK_SCALE_F32_COL_MAJOR) {
-            reinterpret_cast<float*>(s_out)[slab + int64_t(ocol) * p.scale_stride + orow] = scale;
-          } else {  // 4 exponent bytes per int32 word
-            store_packed_ue8m0(s_out, p, orow, ocol, slab, uint8_t(exp2s + 127));
+          if constexpr (kV2) {
+            uint32_t orow, ocol;
+            int64_t slab;
+            col_major_slot(p, row, col, orow, ocol, slab);
+            if constexpr (kLayout == SGLK_SCALE_F32_COL_MAJOR)
+              reinterpret_cast<float*>(s_out)[slab + int64_t(ocol) * p.scale_stride + orow] = scale;
+            else
+              store_packed_ue8m0(s_out, p, orow, ocol, slab, uint8_t(exp2s + 127));
+          } else if constexpr (kLayout == SGLK_SCALE_F32_COL_MAJOR) {
+            reinterpret_cast<float*>(s_out)[int64_t(col) * p.scale_stride + row] = scale;
+          } else {  // 4 exponent bytes per int32 word; word (row, col/4) lives at (col/4)*stride + row
+            reinterpret_cast<uint8_t*>(s_out)[(int64_t(col >> 2) * p.scale_stride + row) * 4 + (col & 3)] =
+                uint8_t(exp2s + 127);
           }
         }
       }
@@ -390,27 +398,27 @@ static int launch_generic(const void* x, void* q, void* s, const QuantParams& p,
   return int(cudaGetLastError());
 }
 
-template <typename T, int GROUP, bool kInt8, int kLayout, bool kFuse>
+template <typename T, int GROUP, bool kInt8, int kLayout, bool kFuse, bool kV2 = false>
 static int launch_one(const void* x, void* q, void* s, const QuantParams& p, cudaStream_t st) {
   using C = QuantCfg<T, GROUP, kInt8, kLayout, kFuse>;
   const int64_t slots = p.num_groups * C::LPG;
   const int64_t chunks = (slots + C::SLOTS_PER_CHUNK - 1) / C::SLOTS_PER_CHUNK;
   const int64_t cap = int64_t(device_sm_count()) * 16;     // a few waves of resident CTAs, then grid-stride
   const int blocks = int(chunks < cap ? (chunks < 1 ? 1 : chunks) : cap);
-  ptgq_kernel<T, GROUP, kInt8, kLayout, kFuse><<<blocks, C::kThreads, 0, st>>>(
+  ptgq_kernel<T, GROUP, kInt8, kLayout, kFuse, kV2><<<blocks, C::kThreads, 0, st>>>(
       static_cast<const T*>(x), static_cast<uint8_t*>(q), s, p);
   return int(cudaGetLastError());
 }
 
-template <typename T, bool kInt8, int kLayout, bool kFuse>
+template <typename T, bool kInt8, int kLayout, bool kFuse, bool kV2 = false>
 static int launch_group(int64_t group, const void* x, void* q, void* s, const QuantParams& p, cudaStream_t st) {
   switch (group) {
-    case 16:  return launch_one<T, 16, kInt8, kLayout, kFuse>(x, q, s, p, st);
-    case 32:  return launch_one<T, 32, kInt8, kLayout, kFuse>(x, q, s, p, st);
-    case 64:  return launch_one<T, 64, kInt8, kLayout, kFuse>(x, q, s, p, st);
-    case 128: return launch_one<T, 128, kInt8, kLayout, kFuse>(x, q, s, p, st);
-    case 256: return launch_one<T, 256, kInt8, kLayout, kFuse>(x, q, s, p, st);
-    case 512: return launch_one<T, 512, kInt8, kLayout, kFuse>(x, q, s, p, st);
+    case 16:  return launch_one<T, 16, kInt8, kLayout, kFuse, kV2>(x, q, s, p, st);
+    case 32:  return launch_one<T, 32, kInt8, kLayout, kFuse, kV2>(x, q, s, p, st);
+    case 64:  return launch_one<T, 64, kInt8, kLayout, kFuse, kV2>(x, q, s, p, st);
+    case 128: return launch_one<T, 128, kInt8, kLayout, kFuse, kV2>(x, q, s, p, st);
+    case 256: return launch_one<T, 256, kInt8, kLayout, kFuse, kV2>(x, q, s, p, st);
+    case 512: return launch_one<T, 512, kInt8, kLayout, kFuse, kV2>(x, q, s, p, st);
     default: break;
   }
   return SGLK_E_GROUP;
@@ -426,6 +434,17 @@ static int launch_dtype(int64_t group, int out_dtype, int layout, const void* x,
     if (group != 16 && group != 32 && group != 64 && group != 128 && group != 256 && group != 512) return SGLK_E_GROUP;
     return out_dtype == SGLK_INT8 ? launch_generic<T, true>(x, q, s, p, int(group), layout, kFuse, st)
                                   : launch_generic<T, false>(x, q, s, p, int(group), layout, kFuse, st);
+  }
+  const bool v2 = p.v2_interleave != 0 || p.masked_m != nullptr;
+  if (v2) {
+    // v2 column-major addressing / masked layout: e4m3 instantiations; the rare int8 form takes the generic kernel
+    if (out_dtype == SGLK_INT8)
+      return kFuse ? SGLK_E_DTYPE : launch_generic<T, true>(x, q, s, p, int(group), layout, kFuse, st);
+    switch (layout) {
+      case SGLK_SCALE_F32_COL_MAJOR: return launch_group<T, false, SGLK_SCALE_F32_COL_MAJOR, kFuse, true>(group, x, q, s, p, st);
+      case SGLK_SCALE_UE8M0_COL_PACKED: return launch_group<T, false, SGLK_SCALE_UE8M0_COL_PACKED, kFuse, true>(group, x, q, s, p, st);
+      default: return SGLK_E_LAYOUT;
+    }
   }
   if (out_dtype == SGLK_INT8) {
     if (kFuse) return SGLK_E_DTYPE;   // the v2 fused path quantises to e4m3 only
