@@ -18,6 +18,7 @@ if os.environ.get("SCALES", "col") == "row":
 else:
     sa = (torch.randn(K // 128, M, device=dev) * 1e-3).t()
     sb = torch.randn(K // 128, -(N // -128), device=dev) * 1e-3
+REPEAT = int(os.environ.get('REPEAT', '1'))   # launches inside one timed region (reported time is the total)
 SK = os.environ.get("NOWS", "0") != "1"   # NOWS=1: no workspace (no stream-K, no scale re-layout)
 flush = torch.zeros(256 << 20, dtype=torch.uint8, device=dev).view(torch.int64)
 times = {v: [] for v in variants}
@@ -27,9 +28,12 @@ torch.cuda.synchronize()
 for r in range(rounds + 2):
     for v in variants:
         for _ in range(3):
-            flush.sum()
+            # NOFLUSH=1: keep L2 warm, but still put ~100 us of device work in front so the host-side launch cost stays hidden
+            flush.sum() if os.environ.get('NOFLUSH', '0') != '1' else torch.cuda._sleep(200000)
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            e0.record(); _ops._gemm(a, bt.t(), sa, sb, torch.bfloat16, v, 0, SK); e1.record(); e1.synchronize()
+            e0.record()
+            for _ in range(REPEAT): _ops._gemm(a, bt.t(), sa, sb, torch.bfloat16, v, 0, SK)
+            e1.record(); e1.synchronize()
             if r >= 2:
                 times[v].append(e0.elapsed_time(e1))
 lib = _lib.load()

@@ -13,3 +13,9 @@ $CMD > gpurun_out/plain_bench3.log 2>&1 && \
 ncu --set full --clock-control none --import-source on -k regex:ptgq_kernel -s 3 -c 1 -o gpurun_out/quant_$R $CMD > gpurun_out/ncu_quant.log 2>&1
 tail -2 gpurun_out/ncu_quant.log
 ls -la gpurun_out | grep $R
+# decode shape (weight streaming, stream-K): one full capture of the 128-wide kernel
+DCMD="python tools/ncu_target.py gemm 64 24576 7168"
+$DCMD > gpurun_out/plain_decode.log 2>&1 && \
+ncu --set full --clock-control none --import-source on -k regex:fp8_blockwise_gemm -s 2 -c 1 -o gpurun_out/decode_$R $DCMD > gpurun_out/ncu_decode.log 2>&1
+tail -2 gpurun_out/ncu_decode.log
+ls -la gpurun_out | grep $R

@@ -81,4 +81,5 @@ def dump_launches():
 dump_launches()
 dump_kernel("gemm")
 dump_kernel("quant")
+dump_kernel("decode")
 print(sorted(os.listdir(P)))
