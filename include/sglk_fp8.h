@@ -189,6 +189,29 @@ SGLK_API int sglk_fp8_blockwise_scaled_mm_allgather(const void* A, const void* B
                                            int64_t sb_stride_n, int out_dtype, int variant, int num_sms,
                                            void* workspace, int64_t workspace_bytes, void* stream);
 
+/*
+ * Replaces: void fp8_blockwise_scaled_grouped_mm(output, a_ptrs, ..., problem_sizes, expert_offsets, workspace)
+ *   declared /root/reference/include/sgl_kernel_ops.h:660-678, wrapped python/sgl_kernel/moe.py:236-276, semantics
+ *   pinned by tests/test_fp8_blockwise_moe.py:27-51,66-171 (the reference ships no kernel).
+ * For every expert e: C[off_e : off_e + m_e, :] = blockwise_scaled_mm(A[off_e : off_e + m_e], B[e], sa[off_e : ...], sb[e]).
+ * A  : e4m3 [total_m, K] — the experts' activations stacked, row stride lda
+ * B  : e4m3 [num_experts * N, K] — expert e's [N, K] (K-contiguous) weight at rows [e*N, (e+1)*N), row stride ldb
+ * sa : fp32 (row, kb) at row*sa_stride_m + kb*sa_stride_k (rows of the stack)
+ * sb : fp32 (e, kb, nb) at e*sb_stride_e + kb*sb_stride_k + nb*sb_stride_n
+ * C  : bf16 / f16 [total_m, N], row stride ldc
+ * expert_offsets : DEVICE int32[num_experts], first stacked row of each expert
+ * problem_sizes  : DEVICE int32[num_experts, 3] = (m_e, n, k); only m_e is read (n, k are the N, K arguments)
+ * workspace : >= sglk_grouped_mm_workspace_bytes(num_experts, total_m) bytes, 16-byte aligned; the m-tile table is
+ *             built there on the device — no host synchronisation, CUDA-graph capturable.
+ */
+SGLK_API int sglk_fp8_blockwise_scaled_grouped_mm(const void* A, const void* B, const float* sa, const float* sb, void* C,
+                                         const int32_t* expert_offsets, const int32_t* problem_sizes,
+                                         int64_t num_experts, int64_t total_m, int64_t N, int64_t K, int64_t lda,
+                                         int64_t ldb, int64_t ldc, int64_t sa_stride_m, int64_t sa_stride_k,
+                                         int64_t sb_stride_e, int64_t sb_stride_k, int64_t sb_stride_n, int out_dtype,
+                                         int num_sms, void* workspace, int64_t workspace_bytes, void* stream);
+SGLK_API int64_t sglk_grouped_mm_workspace_bytes(int64_t num_experts, int64_t total_m);
+
 /* bytes of workspace the call above can make use of (0: none): [1 MiB tile counters][stream-K partials, if the
  * scheduler would cut tiles][K-block-contiguous copies of sa / sb, for prefill-sized problems whose scales are not
  * already laid out that way] */

@@ -190,6 +190,26 @@ def baseline_scaled_mm(
     return output
 
 
+def grouped_scaled_mm_ref(a, b, scales_a, scales_b, expert_offsets, problem_sizes, out_dtype):
+    """fp8_blockwise_scaled_grouped_mm as its test defines it (tests/test_fp8_blockwise_moe.py:66-171): expert g owns
+    rows [off_g, off_g + m_g) of the stacked a / scales_a / output and the g-th [K, N] weight and [K/128, N/128] scales;
+    every expert is the plain blockwise GEMM (`baseline_scaled_mm`, :27-51 — same arithmetic as the dense oracle)."""
+    _require_cpu(a, b, scales_a, scales_b)
+    E = b.shape[0]
+    out = torch.zeros(a.shape[0], b.shape[2], dtype=out_dtype)
+    for g in range(E):
+        off, m = int(expert_offsets[g]), int(problem_sizes[g][0])
+        if m == 0:
+            continue
+        out[off:off + m] = baseline_scaled_mm(a[off:off + m], b[g], scales_a[off:off + m], scales_b[g], out_dtype)
+    return out
+
+
+def to_fp8_round(t: torch.Tensor) -> torch.Tensor:
+    """`to_fp8`, tests/test_fp8_blockwise_moe.py:20-24: clamp to the e4m3 range, round to integers, cast."""
+    return torch.round(t.clamp(min=-FP8_E4M3_MAX, max=FP8_E4M3_MAX)).to(torch.float8_e4m3fn)
+
+
 def make_gemm_inputs(M: int, N: int, K: int, seed: int = 0):
     """tests/test_fp8_blockwise_gemm.py:66-80 — the reference's synthetic GEMM inputs:
     codes uniform in +-448, scales randn*1e-3, `mat_b` = [N,K].t(), scales M-major / K-block-major."""

@@ -65,6 +65,10 @@ struct GemmParams {
   int32_t num_stages;
   int32_t* ws_counters;   // [num_tiles][kCG*8], zero on entry, reset by the reducer
   float* ws_partials;     // [2*workers][kCG*8][NC/4][32] float4
+  // grouped (MoE) mode, kGrouped instantiation only: A / C / sa are the experts' row ranges stacked, B is [E*N, K]
+  const int4* grp_tiles;          // one entry per 128-row m-tile: {first row in the stack, valid rows, expert, 0}
+  const int32_t* grp_num_m_tiles; // how many entries (written on the device by build_group_tiles_kernel)
+  int64_t grp_sb_expert_stride;   // floats between the experts' weight-scale matrices
 };
 
 constexpr int kMaxDests = 8;
@@ -169,7 +173,8 @@ __device__ __forceinline__ void tile_coords(int tile, const GemmParams& p, int& 
 // TMEM like an unscaled GEMM (one accumulator hand-off per tile) — both measure ceilings of the TMA/MMA pipeline.
 // kSplitN: each K block is issued as two N/2-wide MMA halves with their own full/empty barriers, so a half can be
 // promoted (and handed back) while the other half and the next K block are still in the tensor pipe.
-template <int BLOCK_N, int kStages, int kCG, typename OutT, bool kTmaStore, int kDiag = 0, bool kSplitN = false>
+template <int BLOCK_N, int kStages, int kCG, typename OutT, bool kTmaStore, int kDiag = 0, bool kSplitN = false,
+          bool kGrouped = false>
 __global__ void __launch_bounds__(kNumThreads, 1)
 fp8_blockwise_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
                           const __grid_constant__ CMaps tmap_c, const GemmParams p) {
@@ -180,6 +185,7 @@ fp8_blockwise_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gr
   constexpr int kAccBars = kAccStages * kHalves;
   static_assert(!kSplitN || (BLOCK_N == 256 && (kDiag == 0 || kDiag == 4)), "split-N is for the 256-wide product tiles");
   static_assert(!kTmaStore || C::kCanTmaStore, "TMA-store epilogue needs >= 64 columns per warp");
+  static_assert(!kGrouped || (kCG == 1 && !kTmaStore && kDiag == 0 && !kSplitN), "grouped mode: single-CTA tiles, predicated stores");
 
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   // 128B-swizzled TMA/UMMA tiles need 1024-byte alignment.  The budget (kSmemOverhead) has no slack for a
@@ -234,7 +240,12 @@ fp8_blockwise_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gr
   ptx::tc_fence_after();
   const uint32_t tmem_base = *reinterpret_cast<volatile uint32_t*>(smem_gen + (tmem_slot - smem_base));
 
-  const int num_tiles = p.num_m_blocks * p.num_n_blocks;     // m-blocks of 128*kCG rows
+  // m-blocks of 128*kCG rows; grouped: the m-tile table was built on the device from the expert offsets
+  const int num_m_tiles = kGrouped ? __ldg(p.grp_num_m_tiles) : p.num_m_blocks;
+  const int num_tiles = num_m_tiles * p.num_n_blocks;
+  // grouped: tile -> (m-tile, n-block) with the m-tile fastest, so CTAs running together share an expert's B panel
+  auto grouped_tile = [&](int tile, int& nb) { nb = tile / num_m_tiles; return __ldg(p.grp_tiles + (tile - nb * num_m_tiles)); };
+  (void)grouped_tile;
   const int num_workers = gridDim.x / kCG;
   const int worker = blockIdx.x / kCG;
   const int num_kb = p.num_k_blocks;
@@ -253,10 +264,17 @@ fp8_blockwise_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gr
       WorkIter it(p, worker, num_workers, num_tiles);
       int tile, kb0, kb1;
       while (it.next(tile, kb0, kb1)) {
-        int mb, nb;
-        tile_coords(tile, p, mb, nb);
-        const int m0 = mb * (BLOCK_M * kCG) + int(cta_rank) * BLOCK_M;
-        const int n0 = nb * BLOCK_N + int(cta_rank) * C::LOAD_N;
+        int mb, nb, m0, n0;
+        if constexpr (kGrouped) {
+          const int4 ti = grouped_tile(tile, nb);
+          m0 = ti.x;                                            // rows past the expert's range are loaded but never stored
+          n0 = ti.z * int(p.N) + nb * BLOCK_N;                  // B is the experts' [N, K] matrices stacked
+          mb = 0; (void)mb;
+        } else {
+          tile_coords(tile, p, mb, nb);
+          m0 = mb * (BLOCK_M * kCG) + int(cta_rank) * BLOCK_M;
+          n0 = nb * BLOCK_N + int(cta_rank) * C::LOAD_N;
+        }
         for (int kb = kb0; kb < kb1; ++kb) {
           ptx::mbar_wait(empty_bar(stage), phase ^ 1);
           const uint32_t sa_addr = smem_base + stage * stage_bytes;
@@ -404,16 +422,26 @@ fp8_blockwise_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gr
     int tile, kb0, kb1;
     bool first_segment = true;
     while (it.next(tile, kb0, kb1)) {
-      int mb, nb;
-      tile_coords(tile, p, mb, nb);
-      const int m0 = mb * (BLOCK_M * kCG) + int(cta_rank) * BLOCK_M;
+      int mb, nb, m0;
+      bool row_ok;
+      const float* sb_base = p.sb;
+      if constexpr (kGrouped) {
+        const int4 ti = grouped_tile(tile, nb);
+        m0 = ti.x;
+        row_ok = quarter * 32 + lane < ti.y;                    // rows of this expert in the tile
+        sb_base += int64_t(ti.z) * p.grp_sb_expert_stride;
+        mb = 0;
+      } else {
+        tile_coords(tile, p, mb, nb);
+        m0 = mb * (BLOCK_M * kCG) + int(cta_rank) * BLOCK_M;
+        row_ok = m0 + quarter * 32 + lane < p.M;
+      }
       const int row = m0 + quarter * 32 + lane;
       const int col0 = nb * BLOCK_N + half * NC;          // first column this warp owns
-      const bool row_ok = row < p.M;
       // scale pointers: sa walks kb for this row, sb walks kb for this warp's 128-column block
       const float* sa_ptr = p.sa + int64_t(row_ok ? row : 0) * p.sa_sm;
       const int sbc = min(col0 / 128, p.num_sb_cols - 1);
-      const float* sb_ptr = p.sb + int64_t(sbc) * p.sb_sn;
+      const float* sb_ptr = sb_base + int64_t(sbc) * p.sb_sn;
       // NC <= 128 and col0 % NC == 0, so the warp's columns never straddle a 128-wide scale block
       float accum[NC];
 #pragma unroll
@@ -786,6 +814,39 @@ __global__ void __launch_bounds__(256) relayout_scales_kernel(RelayoutJob ja, Re
   }
 }
 
+// Grouped (MoE) GEMM: the m-tile table.  Expert e owns rows [offsets[e], offsets[e] + sizes[e][0]) of the stacked A;
+// it contributes ceil(m_e / 128) entries {first row, valid rows, expert, 0}.  One block, one thread per expert,
+// an inclusive scan of the tile counts in shared memory; everything stays on the device (no host sync, capturable).
+__global__ void __launch_bounds__(1024)
+build_group_tiles_kernel(const int32_t* __restrict__ offsets, const int32_t* __restrict__ sizes, int num_experts,
+                         int4* __restrict__ table, int32_t* __restrict__ count, int max_tiles) {
+  __shared__ int scan[1024];
+  int base = 0;                                           // tiles of the experts handled in earlier rounds
+  for (int e0 = 0; e0 < num_experts; e0 += 1024) {
+    const int e = e0 + int(threadIdx.x);
+    const int m = e < num_experts ? max(sizes[e * 3], 0) : 0;
+    const int nt = (m + BLOCK_M - 1) / BLOCK_M;
+    scan[threadIdx.x] = nt;
+    __syncthreads();
+    for (int d = 1; d < 1024; d <<= 1) {
+      const int v = int(threadIdx.x) >= d ? scan[threadIdx.x - d] : 0;
+      __syncthreads();
+      scan[threadIdx.x] += v;
+      __syncthreads();
+    }
+    const int first = base + scan[threadIdx.x] - nt;
+    if (e < num_experts) {
+      const int off = offsets[e];
+      for (int t = 0; t < nt; ++t)
+        if (first + t < max_tiles)
+          table[first + t] = make_int4(off + t * BLOCK_M, min(BLOCK_M, m - t * BLOCK_M), e, 0);
+    }
+    base += scan[1023];
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) *count = min(base, max_tiles);
+}
+
 // --------------------------------------------------------------------------------------------
 // host side
 // --------------------------------------------------------------------------------------------
@@ -855,11 +916,12 @@ constexpr int kNumVariants = int(sizeof(kVariants) / sizeof(kVariants[0]));
 constexpr int kNumProductVariants = 7;   // ids 0..6; 7..12 are diagnostics; 13, 14 are product variants again
 constexpr int64_t kCounterAreaBytes = 1 << 20;   // first MiB of a stream-K workspace: tile counters (zero between launches)
 
-template <int BLOCK_N, int kStages, int kCG, typename OutT, bool kTmaStore, int kDiag = 0, bool kSplitN = false>
+template <int BLOCK_N, int kStages, int kCG, typename OutT, bool kTmaStore, int kDiag = 0, bool kSplitN = false,
+          bool kGrouped = false>
 static int launch_variant(const CUtensorMap& ta, const CUtensorMap& tb, const CMaps& tc, const GemmParams& p,
                           int workers, cudaStream_t st) {
   using C = Cfg<BLOCK_N, kCG>;
-  auto kern = fp8_blockwise_gemm_kernel<BLOCK_N, kStages, kCG, OutT, kTmaStore, kDiag, kSplitN>;
+  auto kern = fp8_blockwise_gemm_kernel<BLOCK_N, kStages, kCG, OutT, kTmaStore, kDiag, kSplitN, kGrouped>;
   constexpr int smem = kMaxDynSmem;
   (void)sizeof(C);
   static bool configured = false;   // per instantiation
@@ -1008,6 +1070,7 @@ static int gemm_entry(const void* A, const void* B, const float* sa, const float
   if (num_sms <= 0) num_sms = device_sm_count();
 
   GemmParams p;
+  p.grp_tiles = nullptr; p.grp_num_m_tiles = nullptr; p.grp_sb_expert_stride = 0;
   p.sa = sa; p.sb = sb; p.C = Cout;
   p.M = M; p.N = N; p.K = K; p.ldc = ldc;
   p.sa_sm = sa_sm; p.sa_sk = sa_sk; p.sb_sk = sb_sk; p.sb_sn = sb_sn;
@@ -1093,7 +1156,79 @@ static int gemm_entry(const void* A, const void* B, const float* sa, const float
   return launch_by_id<__half>(variant, ta, tb, tc, p, pl.workers, st);
 }
 
+// Grouped (MoE) form: experts' activations stacked along M, one [N, K] weight per expert, m-tiles from a device table.
+static int grouped_entry(const void* A, const void* B, const float* sa, const float* sb, void* Cout,
+                         const int32_t* expert_offsets, const int32_t* problem_sizes, int64_t num_experts,
+                         int64_t total_m, int64_t N, int64_t K, int64_t lda, int64_t ldb, int64_t ldc, int64_t sa_sm,
+                         int64_t sa_sk, int64_t sb_se, int64_t sb_sk, int64_t sb_sn, int out_dtype, int num_sms,
+                         void* workspace, int64_t workspace_bytes, void* stream) {
+  if (total_m < 0 || N < 0 || K < 0 || num_experts < 0) return SGLK_E_SHAPE;
+  if (out_dtype != SGLK_BF16 && out_dtype != SGLK_F16) return SGLK_E_DTYPE;
+  if (total_m == 0 || N == 0 || num_experts == 0) return SGLK_OK;
+  if (!A || !B || !sa || !sb || !Cout || !expert_offsets || !problem_sizes || !workspace) return SGLK_E_NULL;
+  if (K <= 0 || K % 16 != 0 || lda % 16 != 0 || ldb % 16 != 0 || lda < K || ldb < K || ldc < N) return SGLK_E_STRIDE;
+  if ((reinterpret_cast<uintptr_t>(A) & 15) || (reinterpret_cast<uintptr_t>(B) & 15) ||
+      (reinterpret_cast<uintptr_t>(workspace) & 15)) return SGLK_E_STRIDE;
+  if (total_m >= (int64_t(1) << 31) || num_experts * N >= (int64_t(1) << 31) || K >= (int64_t(1) << 31)) return SGLK_E_SHAPE;
+  const int64_t max_tiles = (total_m + BLOCK_M - 1) / BLOCK_M + num_experts;   // every expert can add one ragged tile
+  if (workspace_bytes < 16 + max_tiles * 16) return SGLK_E_ARG;
+  if (num_sms <= 0) num_sms = device_sm_count();
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  int32_t* count = static_cast<int32_t*>(workspace);
+  int4* table = reinterpret_cast<int4*>(static_cast<char*>(workspace) + 16);
+  build_group_tiles_kernel<<<1, 1024, 0, st>>>(expert_offsets, problem_sizes, int(num_experts), table, count, int(max_tiles));
+
+  GemmParams p;
+  memset(&p, 0, sizeof(p));
+  p.sa = sa; p.sb = sb; p.C = Cout;
+  p.M = total_m; p.N = N; p.K = K; p.ldc = ldc;
+  p.sa_sm = sa_sm; p.sa_sk = sa_sk; p.sb_sk = sb_sk; p.sb_sn = sb_sn;
+  p.num_m_blocks = int32_t(max_tiles);
+  p.num_n_blocks = int32_t((N + 127) / 128);
+  p.num_k_blocks = int32_t((K + BLOCK_K - 1) / BLOCK_K);
+  p.num_sb_cols = int32_t((N + 127) / 128);
+  p.group_m = 8;
+  p.num_dests = 1;
+  p.grp_tiles = table; p.grp_num_m_tiles = count; p.grp_sb_expert_stride = sb_se;
+  const uint32_t b_bytes = 128u * BLOCK_K;
+  p.stage_tx_bytes = BLOCK_M * BLOCK_K + b_bytes;
+  p.a_slot_bytes = BLOCK_M * BLOCK_K;
+  p.stage_bytes = p.a_slot_bytes + b_bytes;
+  p.num_stages = 6;
+  p.scale_vec = (sa_sk == 1 && sb_sk == 1 && p.num_k_blocks % 4 == 0 && sa_sm % 4 == 0 && sb_sn % 4 == 0 && sb_se % 4 == 0 &&
+                 (reinterpret_cast<uintptr_t>(sa) & 15) == 0 && (reinterpret_cast<uintptr_t>(sb) & 15) == 0) ? 1 : 0;
+  CUtensorMap ta, tb;
+  CMaps tc;
+  if (!make_tmap_2d(&ta, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, A, uint64_t(total_m), uint64_t(K), uint64_t(lda), BLOCK_M, BLOCK_K))
+    return SGLK_E_DRIVER;
+  if (!make_tmap_2d(&tb, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, B, uint64_t(num_experts * N), uint64_t(K), uint64_t(ldb), 128, BLOCK_K))
+    return SGLK_E_DRIVER;
+  for (int d = 0; d < kMaxDests; ++d) tc.m[d] = ta;   // unused by the predicated-store epilogue
+  int64_t workers = max_tiles * p.num_n_blocks;
+  if (workers > num_sms) workers = num_sms;
+  if (out_dtype == SGLK_BF16)
+    return launch_variant<128, 6, 1, __nv_bfloat16, false, 0, false, true>(ta, tb, tc, p, int(workers), st);
+  return launch_variant<128, 6, 1, __half, false, 0, false, true>(ta, tb, tc, p, int(workers), st);
+}
+
 }  // namespace sglk
+
+extern "C" int sglk_fp8_blockwise_scaled_grouped_mm(const void* A, const void* B, const float* sa, const float* sb, void* C,
+                                                    const int32_t* expert_offsets, const int32_t* problem_sizes,
+                                                    int64_t num_experts, int64_t total_m, int64_t N, int64_t K,
+                                                    int64_t lda, int64_t ldb, int64_t ldc, int64_t sa_stride_m,
+                                                    int64_t sa_stride_k, int64_t sb_stride_e, int64_t sb_stride_k,
+                                                    int64_t sb_stride_n, int out_dtype, int num_sms, void* workspace,
+                                                    int64_t workspace_bytes, void* stream) {
+  return sglk::grouped_entry(A, B, sa, sb, C, expert_offsets, problem_sizes, num_experts, total_m, N, K, lda, ldb, ldc,
+                             sa_stride_m, sa_stride_k, sb_stride_e, sb_stride_k, sb_stride_n, out_dtype, num_sms,
+                             workspace, workspace_bytes, stream);
+}
+
+extern "C" int64_t sglk_grouped_mm_workspace_bytes(int64_t num_experts, int64_t total_m) {
+  if (num_experts < 0 || total_m < 0) return 0;
+  return 16 + ((total_m + sglk::BLOCK_M - 1) / sglk::BLOCK_M + num_experts) * 16;
+}
 
 extern "C" int sglk_fp8_blockwise_scaled_mm_ex(const void* A, const void* B, const float* sa, const float* sb, void* C,
                                                int64_t M, int64_t N, int64_t K, int64_t lda, int64_t ldb, int64_t ldc,

@@ -3,7 +3,7 @@
 Drop-in for the four names the reference exports for this path
 (python/sgl_kernel/__init__.py:67,75-78); everything else in the reference is out of scope here.
 Importing the package registers torch.ops.sgl_kernel.{sgl_per_token_group_quant_8bit,
-sgl_per_token_group_quant_8bit_v2, fp8_blockwise_scaled_mm} for dispatch key CUDA.
+sgl_per_token_group_quant_8bit_v2, fp8_blockwise_scaled_mm, fp8_blockwise_scaled_grouped_mm} for dispatch key CUDA.
 """
 from .gemm import (
     fp8_blockwise_scaled_mm,
@@ -17,12 +17,14 @@ from .linear import (
     create_per_token_group_quant_fp8_output_scale,
     per_token_group_quant_fp8,
 )
+from .moe import fp8_blockwise_scaled_grouped_mm
 from .sharded import ColumnShardedFp8Linear
 
 __version__ = "0.11.0+b200"
 
 __all__ = [
     "fp8_blockwise_scaled_mm",
+    "fp8_blockwise_scaled_grouped_mm",
     "sgl_per_token_group_quant_8bit",
     "sgl_per_token_group_quant_fp8",
     "sgl_per_token_group_quant_int8",

@@ -34,10 +34,21 @@ _GEMM_SCHEMA = (
     " ScalarType out_dtype) -> Tensor"
 )
 
+# derived from the C++ declaration include/sgl_kernel_ops.h:660-678 + python/sgl_kernel/moe.py:236-276 (the reference
+# registers none); `output` is written in place, the pointer / stride / layout tensors are the CUTLASS scratch of the
+# upstream CUDA op and are accepted but not used here
+_GROUPED_SCHEMA = (
+    "fp8_blockwise_scaled_grouped_mm(Tensor(a!) output, Tensor a_ptrs, Tensor b_ptrs, Tensor out_ptrs,"
+    " Tensor a_scales_ptrs, Tensor b_scales_ptrs, Tensor a, Tensor b, Tensor scales_a, Tensor scales_b,"
+    " Tensor stride_a, Tensor stride_b, Tensor stride_c, Tensor layout_sfa, Tensor layout_sfb,"
+    " Tensor problem_sizes, Tensor expert_offsets, Tensor workspace) -> ()"
+)
+
 _library = torch.library.Library("sgl_kernel", "FRAGMENT")
 _library.define(_QUANT_SCHEMA)
 _library.define(_QUANT_V2_SCHEMA)
 _library.define(_GEMM_SCHEMA)
+_library.define(_GROUPED_SCHEMA)
 
 
 def _stream_ptr(t: torch.Tensor) -> int:
@@ -287,6 +298,51 @@ def _gemm_op(mat_a, mat_b, scales_a, scales_b, out_dtype):
     return _gemm(mat_a, mat_b, scales_a, scales_b, out_dtype)
 
 
+def _grouped_mm(output, a_ptrs, b_ptrs, out_ptrs, a_scales_ptrs, b_scales_ptrs, a, b, scales_a, scales_b,
+                stride_a, stride_b, stride_c, layout_sfa, layout_sfb, problem_sizes, expert_offsets, workspace):
+    """fp8_blockwise_scaled_grouped_mm, include/sgl_kernel_ops.h:660-678; semantics tests/test_fp8_blockwise_moe.py:66-171:
+    a [sum_m, K] e4m3 (experts stacked), b [E, K, N] e4m3 with K contiguous (the transposed view of [E, N, K]),
+    scales_a [sum_m, K/128], scales_b [E, K/128, N/128], problem_sizes int32 [E, 3], expert_offsets int32 [E]."""
+    name = "fp8_blockwise_scaled_grouped_mm"
+    _check(all(t.is_cuda for t in (output, a, b, scales_a, scales_b, problem_sizes, expert_offsets, workspace)),
+           f"{name}: tensors must be CUDA tensors")
+    _check(a.dim() == 2 and b.dim() == 3 and output.dim() == 2, "a must be 2-D, b 3-D, output 2-D")
+    _check(a.dtype == torch.float8_e4m3fn and b.dtype == torch.float8_e4m3fn, "a and b must be Float8_e4m3fn")
+    _check(scales_a.dtype == torch.float32 and scales_b.dtype == torch.float32, "scales must be Float32")
+    _check(output.dtype in _GEMM_OUT, "output must be Half or BFloat16")
+    _check(problem_sizes.dtype == torch.int32 and expert_offsets.dtype == torch.int32,
+           "problem_sizes and expert_offsets must be Int32")
+    E, K, N = b.shape
+    total_m = a.size(0)
+    _check(a.size(1) == K and output.size(0) == total_m and output.size(1) == N, "a / b / output shapes do not match")
+    _check(problem_sizes.dim() == 2 and problem_sizes.size(0) == E and problem_sizes.size(1) == 3 and
+           problem_sizes.is_contiguous(), "problem_sizes must be a contiguous [num_experts, 3] tensor")
+    _check(expert_offsets.numel() >= E and expert_offsets.stride(0) == 1, "expert_offsets must have one entry per expert")
+    _check(K == 0 or a.stride(1) == 1 or total_m == 0, "a must be a row major tensor")
+    _check(b.stride(1) == 1 and b.stride(0) == N * b.stride(2), "b must be [E, K, N] with K contiguous (column major per expert)")
+    _check(output.stride(1) == 1, "output must be row major")
+    kb, nb = -(K // -128), -(N // -128)
+    _check(scales_a.dim() == 2 and scales_a.size(0) == total_m and scales_a.size(1) == kb, "scales_a must be [sum_m, ceil(K/128)]")
+    _check(scales_b.dim() == 3 and tuple(scales_b.shape) == (E, kb, nb), "scales_b must be [E, ceil(K/128), ceil(N/128)]")
+    if total_m == 0 or N == 0 or E == 0:
+        return
+    lib = _lib.load()
+    need = lib.sglk_grouped_mm_workspace_bytes(E, total_m)
+    ws_ptr = workspace.data_ptr()
+    pad = (-ws_ptr) % 16
+    _check(workspace.is_contiguous() and workspace.numel() * workspace.element_size() >= need + pad,
+           f"{name}: workspace too small ({need + pad} bytes needed)")
+    with torch.cuda.device(a.device):
+        rc = lib.sglk_fp8_blockwise_scaled_grouped_mm(
+            a.data_ptr(), b.data_ptr(), scales_a.data_ptr(), scales_b.data_ptr(), output.data_ptr(),
+            expert_offsets.data_ptr(), problem_sizes.data_ptr(), E, total_m, N, K,
+            a.stride(0) if total_m > 1 else max(K, 16), b.stride(2) if N > 1 else max(K, 16), output.stride(0),
+            scales_a.stride(0), scales_a.stride(1), scales_b.stride(0), scales_b.stride(1), scales_b.stride(2),
+            _GEMM_OUT[output.dtype], 0, ws_ptr + pad, workspace.numel() * workspace.element_size() - pad, _stream_ptr(a))
+    _lib.check(rc, name)
+
+
+_library.impl("fp8_blockwise_scaled_grouped_mm", _grouped_mm, "CUDA")
 _library.impl("sgl_per_token_group_quant_8bit", _quant_v1, "CUDA")
 _library.impl("sgl_per_token_group_quant_8bit_v2", _quant_v2, "CUDA")
 _library.impl("fp8_blockwise_scaled_mm", _gemm_op, "CUDA")
@@ -307,6 +363,11 @@ def _gemm_fake(mat_a, mat_b, scales_a, scales_b, out_dtype):
     return torch.empty((mat_a.size(0), mat_b.size(1)), dtype=out_dtype, device=mat_a.device)
 
 
+def _grouped_fake(*args):
+    return None
+
+
+_library.impl("fp8_blockwise_scaled_grouped_mm", _grouped_fake, "Meta")
 _library.impl("sgl_per_token_group_quant_8bit", _quant_fake, "Meta")
 _library.impl("sgl_per_token_group_quant_8bit_v2", _quant_v2_fake, "Meta")
 _library.impl("fp8_blockwise_scaled_mm", _gemm_fake, "Meta")

@@ -39,6 +39,11 @@ def gemm_golden():
     return np.load(os.path.join(GOLDEN, "gemm_golden.npz"))
 
 
+@pytest.fixture(scope="session")
+def grouped_golden():
+    return np.load(os.path.join(GOLDEN, "grouped_golden.npz"))
+
+
 @pytest.fixture(autouse=True)
 def _reset_torch_state():
     # reference tests/conftest.py:16-37: default dtype/device reset + device sync around each test

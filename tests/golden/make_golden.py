@@ -174,5 +174,42 @@ def main():
     print("torch", torch.__version__)
 
 
+def main_grouped():
+    """Grouped (MoE) blockwise GEMM: the recipe of tests/test_fp8_blockwise_moe.py:66-171 (its own `to_fp8` and
+    `baseline_scaled_mm`, lifted), seeded and small; per-expert baselines are stored stacked."""
+    import random
+
+    m = lift("tests/test_fp8_blockwise_moe.py", ["cdiv", "scale_shape", "to_fp8", "baseline_scaled_mm"])
+    out = {}
+    for case, (E, n_g, k_g, odt, seed) in enumerate([(4, 256, 512, torch.bfloat16, 0), (8, 384, 256, torch.float16, 1),
+                                                     (3, 128, 1024, torch.bfloat16, 2)]):
+        random.seed(seed)
+        torch.manual_seed(seed)
+        offs, sizes, a_l, bt_l, sa_l, sbt_l, o_l = [0], [], [], [], [], [], []
+        for g in range(E):
+            m_g = 16 * random.randint(1, 20)
+            offs.append(offs[-1] + m_g)
+            sizes.append([m_g, n_g, k_g])
+            a_g = m["to_fp8"](torch.randn((m_g, k_g)))
+            b_g = m["to_fp8"](torch.randn((n_g, k_g)).t())
+            sa_g = torch.randn(m["scale_shape"](a_g.shape, (1, 128))) * 0.001
+            sb_g = torch.randn(m["scale_shape"](b_g.shape, (128, 128))) * 0.001
+            o_l.append(m["baseline_scaled_mm"](a_g, b_g, sa_g, sb_g, odt))
+            a_l.append(a_g); bt_l.append(b_g.t().contiguous()); sa_l.append(sa_g); sbt_l.append(sb_g.t().contiguous())
+        name = f"grouped{case}_E{E}_n{n_g}_k{k_g}_{'bf16' if odt == torch.bfloat16 else 'f16'}"
+        out[name + ".offsets"] = np.asarray(offs[:-1], dtype=np.int32)
+        out[name + ".sizes"] = np.asarray(sizes, dtype=np.int32)
+        out[name + ".a"] = bits(torch.cat(a_l))                    # [sum_m, K]
+        out[name + ".bt"] = bits(torch.stack(bt_l))                # [E, N, K]
+        out[name + ".sa"] = bits(torch.cat(sa_l))                  # [sum_m, K/128]
+        out[name + ".sbt"] = bits(torch.stack(sbt_l))              # [E, N/128, K/128]
+        out[name + ".o"] = bits(torch.cat(o_l))                    # [sum_m, N]
+    np.savez_compressed(os.path.join(OUT, "grouped_golden.npz"), **out)
+    print("grouped_golden.npz", os.path.getsize(os.path.join(OUT, "grouped_golden.npz")), "bytes")
+
+
 if __name__ == "__main__":
-    sys.exit(main())
+    if "--grouped" in sys.argv:      # only the grouped fixture (the other two files are left as committed)
+        sys.exit(main_grouped())
+    main()
+    sys.exit(main_grouped())

@@ -172,3 +172,30 @@ def test_v2_interleave_matches_the_reference_comment():
         assert torch.equal(O.v2_column_major_deinterleave(O.v2_column_major_interleave(r)), r)
     words = torch.tensor([[0x04030201, 0x00000605]], dtype=torch.int32)
     assert O.unpack_ue8m0_words(words, 6).tolist() == [[1, 2, 3, 4, 5, 6]]
+
+
+GROUPED = ["grouped0_E4_n256_k512_bf16", "grouped1_E8_n384_k256_f16", "grouped2_E3_n128_k1024_bf16"]
+
+
+def load_grouped(gg, name):
+    odt = torch.bfloat16 if name.endswith("bf16") else torch.float16
+    a = from_bits(gg[name + ".a"], torch.float8_e4m3fn)
+    bt = from_bits(gg[name + ".bt"], torch.float8_e4m3fn)             # [E, N, K]
+    sa = torch.from_numpy(gg[name + ".sa"].copy())
+    sbt = torch.from_numpy(gg[name + ".sbt"].copy())                  # [E, N/128, K/128]
+    offs = torch.from_numpy(gg[name + ".offsets"].copy())
+    sizes = torch.from_numpy(gg[name + ".sizes"].copy())
+    o = from_bits(gg[name + ".o"], odt)
+    return a, bt, sa, sbt, offs, sizes, o, odt
+
+
+@pytest.mark.parametrize("name", GROUPED)
+def test_grouped_oracle_matches_reference_golden(grouped_golden, name):
+    """The grouped restatement against outputs of the reference's own `baseline_scaled_mm` / `to_fp8`
+    (tests/test_fp8_blockwise_moe.py), bit for bit."""
+    a, bt, sa, sbt, offs, sizes, o, odt = load_grouped(grouped_golden, name)
+    got = O.grouped_scaled_mm_ref(a, bt.transpose(1, 2), sa, sbt.transpose(1, 2), offs, sizes, odt)
+    assert torch.equal(got.view(torch.int16), o.view(torch.int16))
+    x = torch.randn(64, 64, generator=torch.Generator().manual_seed(0)) * 300
+    assert torch.equal(O.to_fp8_round(x).view(torch.uint8),
+                       torch.round(x.clamp(-448.0, 448.0)).to(torch.float8_e4m3fn).view(torch.uint8))
