@@ -134,6 +134,19 @@ SGLK_API int sglk_per_token_group_quant_8bit_v2(const void* input, void* output_
                                        void* stream);
 
 /*
+ * Replaces: at::native::xpu::sgl_per_token_quant_fp8(input, output_q, output_s)
+ *   /root/reference/src/sycl/per_token_quant_fp8.cpp:201-306 (host), :69-199 (kernels); schema
+ *   src/torch_extension_sycl.cc:410-411; python/sgl_kernel/gemm.py:236-241.
+ * input    : [num_tokens, hidden_dim] contiguous bf16 / f16 (hidden_dim % 4 == 0, rows 8-byte aligned)
+ * output_q : [num_tokens, hidden_dim] e4m3fn codes, contiguous
+ * output_s : fp32 [num_tokens]: scale = rowmax|x| / 448
+ * Math (reference order, :105-123): inv = scale == 0 ? 0 : 1/scale; q = e4m3_rne(clamp(float(x)*inv, +-448)) —
+ * bit-exact with the reference's torch check (tests/test_per_token_quant_fp8.py:17-25).
+ */
+SGLK_API int sglk_per_token_quant_fp8(const void* input, void* output_q, void* output_s, int64_t num_tokens,
+                             int64_t hidden_dim, int in_dtype, void* stream);
+
+/*
  * Replaces: torch::Tensor fp8_blockwise_scaled_mm(mat_a, mat_b, scales_a, scales_b, out_dtype)
  *   declared /root/reference/include/sgl_kernel_ops.h:581-586, wrapped python/sgl_kernel/gemm.py:24-31,
  *   semantics pinned by tests/test_fp8_blockwise_gemm.py:23-63 (the reference ships no kernel).

@@ -85,6 +85,20 @@ def ue8m0_scale_bytes_ref(x: torch.Tensor, group_size: int, eps: float = 1e-10) 
     return (exp_s.to(torch.int32) + 127).to(torch.uint8)
 
 
+def per_token_quant_fp8_ref(x: torch.Tensor) -> Tuple[torch.Tensor, torch.Tensor]:
+    """sgl_per_token_quant_fp8: the kernel's definition (/root/reference/src/sycl/per_token_quant_fp8.cpp:105-123:
+    scale = rowmax|x| / 448, inv = scale == 0 ? 0 : 1/scale, q = e4m3(clamp(float(x) * inv, +-448))) written the way
+    the reference's torch check does it (tests/test_per_token_quant_fp8.py:17-25: multiply by scale.reciprocal(),
+    clamp, .to(float8_e4m3fn)); the zero-row guard is the kernel's (the test never draws a zero row)."""
+    _require_cpu(x)
+    assert x.dim() == 2
+    xf = x.to(torch.float32)
+    scale = xf.abs().amax(dim=1) / 448.0
+    inv = torch.where(scale == 0, torch.zeros_like(scale), scale.reciprocal()).view(-1, 1)
+    q = (xf * inv).clamp(min=-448.0, max=448.0).to(torch.float8_e4m3fn)
+    return q, scale
+
+
 def silu_and_mul_ref(x: torch.Tensor) -> torch.Tensor:
     """tests/test_per_token_group_quant_8bit_v2.py:420-431 (fused path): `silu(primary) * secondary`
     evaluated in the input dtype, i.e. silu rounded to bf16, then the product rounded to bf16,

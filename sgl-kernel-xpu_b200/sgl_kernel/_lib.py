@@ -31,6 +31,7 @@ SYMBOLS = {
         _i32, [_vp, _vp, _vp, _i64, _i64, _i64, _i32, _i32, _f32, _f32, _f32, _i32, _i32, _i64, _vp]),
     "sglk_per_token_group_quant_8bit_v2": (
         _i32, [_vp, _vp, _vp, _i64, _i64, _i64, _i64, _i32, _i32, _f32, _f32, _f32, _i32, _i32, _i64, _i64, _i32, _vp, _vp]),
+    "sglk_per_token_quant_fp8": (_i32, [_vp, _vp, _vp, _i64, _i64, _i32, _vp]),
     "sglk_fp8_blockwise_scaled_mm": (
         _i32, [_vp, _vp, _vp, _vp, _vp] + [_i64] * 10 + [_i32, _vp]),
     "sglk_fp8_blockwise_scaled_mm_ex": (

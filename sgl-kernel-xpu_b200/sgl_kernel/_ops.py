@@ -44,7 +44,11 @@ _GROUPED_SCHEMA = (
     " Tensor problem_sizes, Tensor expert_offsets, Tensor workspace) -> ()"
 )
 
+# verbatim: src/torch_extension_sycl.cc:410
+_TOKEN_QUANT_SCHEMA = "sgl_per_token_quant_fp8(Tensor input, Tensor(a!) output_q, Tensor(b!) output_s) -> ()"
+
 _library = torch.library.Library("sgl_kernel", "FRAGMENT")
+_library.define(_TOKEN_QUANT_SCHEMA)
 _library.define(_QUANT_SCHEMA)
 _library.define(_QUANT_V2_SCHEMA)
 _library.define(_GEMM_SCHEMA)
@@ -342,6 +346,29 @@ def _grouped_mm(output, a_ptrs, b_ptrs, out_ptrs, a_scales_ptrs, b_scales_ptrs, 
     _lib.check(rc, name)
 
 
+def _token_quant(input, output_q, output_s):
+    """at::native::xpu::sgl_per_token_quant_fp8, src/sycl/per_token_quant_fp8.cpp:201-306 (checks :202-222)."""
+    name = "sgl_per_token_quant_fp8"
+    _check(input.is_cuda and output_q.is_cuda and output_s.is_cuda, f"{name}: tensors must be CUDA tensors")
+    _check(input.is_contiguous() and output_q.is_contiguous() and output_s.is_contiguous(), "tensors must be contiguous")
+    _check(input.dim() == 2, "input must be 2D [num_tokens, hidden_dim]")
+    _check(input.dtype in (torch.bfloat16, torch.float16), "input must be BFloat16/Half tensor")
+    _check(output_q.dtype == torch.float8_e4m3fn, "output_q must be Float8_e4m3fn tensor")
+    _check(output_s.dtype == torch.float32, "output_s must be Float tensor")
+    tokens, hidden = input.shape
+    _check(output_q.shape == input.shape, f"output_q must have same shape as input, got {tuple(output_q.shape)}")
+    _check(output_s.numel() == tokens, f"output_s must have numel == num_tokens ({tokens}), got {output_s.numel()}")
+    _check(hidden % 4 == 0, f"hidden_dim must be divisible by 4, got {hidden}")
+    if tokens == 0 or hidden == 0:
+        return
+    lib = _lib.load()
+    with torch.cuda.device(input.device):
+        rc = lib.sglk_per_token_quant_fp8(input.data_ptr(), output_q.data_ptr(), output_s.data_ptr(), tokens, hidden,
+                                          _IN_DTYPES[input.dtype], _stream_ptr(input))
+    _lib.check(rc, name)
+
+
+_library.impl("sgl_per_token_quant_fp8", _token_quant, "CUDA")
 _library.impl("fp8_blockwise_scaled_grouped_mm", _grouped_mm, "CUDA")
 _library.impl("sgl_per_token_group_quant_8bit", _quant_v1, "CUDA")
 _library.impl("sgl_per_token_group_quant_8bit_v2", _quant_v2, "CUDA")
@@ -367,6 +394,7 @@ def _grouped_fake(*args):
     return None
 
 
+_library.impl("sgl_per_token_quant_fp8", lambda input, output_q, output_s: None, "Meta")
 _library.impl("fp8_blockwise_scaled_grouped_mm", _grouped_fake, "Meta")
 _library.impl("sgl_per_token_group_quant_8bit", _quant_fake, "Meta")
 _library.impl("sgl_per_token_group_quant_8bit_v2", _quant_v2_fake, "Meta")

@@ -44,6 +44,11 @@ def grouped_golden():
     return np.load(os.path.join(GOLDEN, "grouped_golden.npz"))
 
 
+@pytest.fixture(scope="session")
+def token_golden():
+    return np.load(os.path.join(GOLDEN, "token_golden.npz"))
+
+
 @pytest.fixture(autouse=True)
 def _reset_torch_state():
     # reference tests/conftest.py:16-37: default dtype/device reset + device sync around each test

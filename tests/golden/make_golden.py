@@ -208,8 +208,34 @@ def main_grouped():
     print("grouped_golden.npz", os.path.getsize(os.path.join(OUT, "grouped_golden.npz")), "bytes")
 
 
+def main_token():
+    """sgl_per_token_quant_fp8: the reference test's own torch check (tests/test_per_token_quant_fp8.py:17-25, lifted)
+    applied to the scales the kernel defines (rowmax|x| / 448, src/sycl/per_token_quant_fp8.cpp:105); inputs as the
+    test draws them (torch.rand, seed 42, :52-53) plus signed / zero-row cases."""
+    t = lift("tests/test_per_token_quant_fp8.py", ["torch_per_token_quant_fp8"])
+    out = {}
+    for tokens, hidden, dt, kind in [(128, 512, torch.bfloat16, "rand"), (16, 1076, torch.bfloat16, "rand"),
+                                     (8, 1368, torch.float16, "rand"), (4, 7168, torch.bfloat16, "randn"),
+                                     (64, 2048, torch.float16, "randn"), (3, 20480, torch.bfloat16, "randn")]:
+        torch.manual_seed(42)
+        x = (torch.rand if kind == "rand" else torch.randn)((tokens, hidden), dtype=dt)
+        if kind == "randn":
+            x[0, 1] = -0.0
+        scale = x.float().abs().amax(dim=1) / 448.0
+        q = t["torch_per_token_quant_fp8"](x, scale)
+        name = f"ptq_{tokens}x{hidden}_{'bf16' if dt == torch.bfloat16 else 'f16'}_{kind}"
+        out[name + ".x"] = bits(x)
+        out[name + ".s"] = bits(scale)
+        out[name + ".q"] = bits(q)
+    np.savez_compressed(os.path.join(OUT, "token_golden.npz"), **out)
+    print("token_golden.npz", os.path.getsize(os.path.join(OUT, "token_golden.npz")), "bytes")
+
+
 if __name__ == "__main__":
+    if "--token" in sys.argv:        # only the per-token fixture
+        sys.exit(main_token())
     if "--grouped" in sys.argv:      # only the grouped fixture (the other two files are left as committed)
         sys.exit(main_grouped())
     main()
-    sys.exit(main_grouped())
+    main_grouped()
+    sys.exit(main_token())

@@ -199,3 +199,26 @@ def test_grouped_oracle_matches_reference_golden(grouped_golden, name):
     x = torch.randn(64, 64, generator=torch.Generator().manual_seed(0)) * 300
     assert torch.equal(O.to_fp8_round(x).view(torch.uint8),
                        torch.round(x.clamp(-448.0, 448.0)).to(torch.float8_e4m3fn).view(torch.uint8))
+
+
+# ---- sgl_per_token_quant_fp8 (per-row scale) ----------------------------------------------------------------
+TOKEN_CASES = [("ptq_128x512_bf16_rand", torch.bfloat16), ("ptq_16x1076_bf16_rand", torch.bfloat16),
+               ("ptq_8x1368_f16_rand", torch.float16), ("ptq_4x7168_bf16_randn", torch.bfloat16),
+               ("ptq_64x2048_f16_randn", torch.float16), ("ptq_3x20480_bf16_randn", torch.bfloat16)]
+
+
+@pytest.mark.parametrize("name,sdt", TOKEN_CASES)
+def test_token_quant_oracle_matches_reference_golden(token_golden, name, sdt):
+    x = from_bits(token_golden[name + ".x"], sdt)
+    q, s = O.per_token_quant_fp8_ref(x)
+    assert torch.equal(s.view(torch.int32), torch.from_numpy(token_golden[name + ".s"]).view(torch.int32))
+    assert torch.equal(q.view(torch.uint8), torch.from_numpy(token_golden[name + ".q"]))
+
+
+def test_token_quant_oracle_zero_row_follows_the_kernel():
+    # the kernel's guard (per_token_quant_fp8.cpp:110): an all-zero row has scale 0 and codes 0, not NaN
+    x = torch.zeros(2, 64, dtype=torch.bfloat16)
+    x[1, 3] = 1.0
+    q, s = O.per_token_quant_fp8_ref(x)
+    assert s[0] == 0 and int(q[0].view(torch.uint8).max()) == 0
+    assert q[1, 3].float() == 448.0
