@@ -165,23 +165,20 @@ struct QuantCfg {
   static_assert(GROUP % EPV == 0, "group must be a whole number of 32-byte vectors");
 };
 
-// kV2: the v2 op's column-major addressing and masked MoE layout (compiled out of the v1 instantiations: the extra
-// parameter reads and the predicate cost the streaming kernel 5-8 % when they were runtime switches)
-template <typename T, int GROUP, bool kInt8, int kLayout, bool kFuse, bool kV2 = false>
-__global__ void __launch_bounds__(256)
-ptgq_kernel(const T* __restrict__ x, uint8_t* __restrict__ q, void* __restrict__ s_out, const QuantParams p) {
+// One chunk of 256*U slots.  kFull (CTA-uniform, chosen by the caller): every slot of the chunk exists, so the
+// per-slot bounds predicates compile away — the kernel is sensitive to issue pressure (tools/quant_exp.py: the trimmed
+// variant 13 gains ~3 % over the predicated body, an inexact multiply-only variant ~2 % more).
+template <typename T, int GROUP, bool kInt8, int kLayout, bool kFuse, bool kV2, bool kFull>
+__device__ __forceinline__ void ptgq_chunk(const T* __restrict__ x, uint8_t* __restrict__ q, void* __restrict__ s_out,
+                                           const QuantParams& p, const int64_t chunk0, const int64_t total_slots,
+                                           const int tid) {
   using C = QuantCfg<T, GROUP, kInt8, kLayout, kFuse>;
   constexpr int EPV = C::EPV, LPG = C::LPG, VPL = C::VPL, U = C::U;
   constexpr bool k16 = InTraits<T>::k16;
   constexpr bool kUe8m0 = kLayout >= SGLK_SCALE_UE8M0_ROW_MAJOR;
   constexpr bool kColMajor = kLayout == SGLK_SCALE_F32_COL_MAJOR || kLayout == SGLK_SCALE_UE8M0_COL_PACKED;
-
-  const int64_t total_slots = p.num_groups * LPG;   // slot = (group, lane in group); == vector index when VPL == 1
-  const int tid = threadIdx.x;
-
-  for (int64_t chunk0 = int64_t(blockIdx.x) * C::SLOTS_PER_CHUNK; chunk0 < total_slots;
-       chunk0 += int64_t(gridDim.x) * C::SLOTS_PER_CHUNK) {
-    const bool full = chunk0 + C::SLOTS_PER_CHUNK <= total_slots;    // CTA-uniform
+  constexpr bool full = kFull;
+  {
     uint32_t w[U][VPL][8];
     uint32_t g[kFuse ? U : 1][kFuse ? VPL : 1][8];
     // ---------------- issue every load of the chunk ----------------
@@ -315,7 +312,7 @@ ptgq_kernel(const T* __restrict__ x, uint8_t* __restrict__ q, void* __restrict__
             if constexpr (k16 && !kFuse) {
               // sign bits straight from the four 16-bit inputs: their high bytes are bytes 1,3 of each word
               const uint32_t hib = __byte_perm(w[u][j][2 * i], w[u][j][2 * i + 1], 0x7531);
-              mag = (mag & 0x7F7F7F7Fu) | (hib & 0x80808080u);
+              asm("lop3.b32 %0, %1, %2, %3, 0xE4;" : "=r"(mag) : "r"(hib), "r"(mag), "r"(0x80808080u));   // sign ? hib : mag
             } else if constexpr (k16) {
               const uint32_t sg = ((__float_as_uint(f[j][2 * i].x) >> 24) & 0x80u) | ((__float_as_uint(f[j][2 * i].y) >> 16) & 0x8000u) |
                                   ((__float_as_uint(f[j][2 * i + 1].x) >> 8) & 0x800000u) | (__float_as_uint(f[j][2 * i + 1].y) & 0x80000000u);
@@ -331,6 +328,23 @@ ptgq_kernel(const T* __restrict__ x, uint8_t* __restrict__ q, void* __restrict__
         }
       }
     }
+  }
+}
+
+// kV2: the v2 op's column-major addressing and masked MoE layout (compiled out of the v1 instantiations: the extra
+// parameter reads and the predicate cost the streaming kernel 5-8 % when they were runtime switches)
+template <typename T, int GROUP, bool kInt8, int kLayout, bool kFuse, bool kV2 = false>
+__global__ void __launch_bounds__(256)
+ptgq_kernel(const T* __restrict__ x, uint8_t* __restrict__ q, void* __restrict__ s_out, const QuantParams p) {
+  using C = QuantCfg<T, GROUP, kInt8, kLayout, kFuse>;
+  const int64_t total_slots = p.num_groups * C::LPG;   // slot = (group, lane in group); == vector index when VPL == 1
+  const int tid = threadIdx.x;
+  for (int64_t chunk0 = int64_t(blockIdx.x) * C::SLOTS_PER_CHUNK; chunk0 < total_slots;
+       chunk0 += int64_t(gridDim.x) * C::SLOTS_PER_CHUNK) {
+    if (chunk0 + C::SLOTS_PER_CHUNK <= total_slots)       // CTA-uniform
+      ptgq_chunk<T, GROUP, kInt8, kLayout, kFuse, kV2, true>(x, q, s_out, p, chunk0, total_slots, tid);
+    else
+      ptgq_chunk<T, GROUP, kInt8, kLayout, kFuse, kV2, false>(x, q, s_out, p, chunk0, total_slots, tid);
   }
 }
 
@@ -403,7 +417,9 @@ static int launch_one(const void* x, void* q, void* s, const QuantParams& p, cud
   using C = QuantCfg<T, GROUP, kInt8, kLayout, kFuse>;
   const int64_t slots = p.num_groups * C::LPG;
   const int64_t chunks = (slots + C::SLOTS_PER_CHUNK - 1) / C::SLOTS_PER_CHUNK;
-  const int64_t cap = int64_t(device_sm_count()) * 16;     // a few waves of resident CTAs, then grid-stride
+  // one CTA per chunk (the kernel's grid-stride loop then runs once): the block scheduler staggers and balances the
+  // CTAs better than a capped persistent grid did — 6.8 vs 6.44 TB/s at 32768 x 7168 (tools/quant_exp.py, variants 1/2)
+  const int64_t cap = (int64_t(1) << 31) - 1;
   const int blocks = int(chunks < cap ? (chunks < 1 ? 1 : chunks) : cap);
   ptgq_kernel<T, GROUP, kInt8, kLayout, kFuse, kV2><<<blocks, C::kThreads, 0, st>>>(
       static_cast<const T*>(x), static_cast<uint8_t*>(q), s, p);
