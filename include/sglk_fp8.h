@@ -180,6 +180,28 @@ SGLK_API int sglk_fp8_blockwise_scaled_mm_ex(const void* A, const void* B, const
                                     int64_t workspace_bytes, void* stream);
 
 /*
+ * GEMM with the NEXT layer's activation quantisation fused into its epilogue ("emit e4m3 + scales from
+ * the previous GEMM's epilogue"; no reference counterpart — the reference runs fp8_blockwise_scaled_mm and
+ * sgl_per_token_group_quant_8bit[_v2] as separate ops, python/sgl_kernel/gemm.py:24-31,85-126).
+ * Result: bit-identical to  C = fp8_blockwise_scaled_mm(..., round_dtype);  [C = silu(C[:, gate]) * C[:, up];]
+ *                           sgl_per_token_group_quant_8bit(C, out_q, out_s, 128, eps, -448, 448)
+ * without C ever reaching HBM: each epilogue thread owns one row x 128 columns = one whole group.
+ * silu_mul = 0: out_q [M, N] codes, out_s (row, g) for g < N/128.                        Needs N % 128 == 0.
+ * silu_mul = 1: B's rows are interleaved by 128-row blocks, gate block j at rows [256j, 256j+128), up block j at
+ *               [256j+128, 256j+256) (scales_b columns likewise); out_q [M, N/2], out_s (row, g) for g < N/256.
+ *               silu in fp32 rounded to round_dtype, product rounded to round_dtype — the v2 quant op's fused mode
+ *               (/root/reference/src/sycl/per_token_group_quant_8bit_v2.cpp:255-262).            Needs N % 256 == 0.
+ * out_q row stride ldq (bytes, multiple of 16); out_s element (row, g) at row*os_stride_m + g*os_stride_g floats.
+ * Other arguments as sglk_fp8_blockwise_scaled_mm_ex.
+ */
+SGLK_API int sglk_fp8_blockwise_scaled_mm_quant(const void* A, const void* B, const float* sa, const float* sb,
+                                       void* out_q, float* out_s, int64_t M, int64_t N, int64_t K, int64_t lda,
+                                       int64_t ldb, int64_t ldq, int64_t sa_stride_m, int64_t sa_stride_k,
+                                       int64_t sb_stride_k, int64_t sb_stride_n, int64_t os_stride_m,
+                                       int64_t os_stride_g, int round_dtype, float eps, int silu_mul, int num_sms,
+                                       void* workspace, int64_t workspace_bytes, void* stream);
+
+/*
  * Fused GEMM -> all-gather for the column-(N-)sharded linear (no reference counterpart: the reference
  * has no communication layer).  Same arithmetic as above on this rank's [K, N_local]
  * weight panel; the epilogue TMA-stores every finished 32x64 output box to C_local AND to the same

@@ -29,6 +29,7 @@
 #include "../../include/sglk_fp8.h"
 #include "common.cuh"
 #include "ptx.cuh"
+#include "quant_kernel.cuh"   // div_pair / silu_mul: the fused output quantisation shares the quant op's arithmetic
 
 namespace sglk {
 
@@ -57,6 +58,11 @@ struct GemmParams {
   int32_t stream_k;
   int32_t scale_vec;         // scales contiguous along K blocks and 16-byte aligned: vector-load path of the promotion warps
   int32_t num_dests;         // TMA-store destinations (1, or the group size for the fused all-gather)
+  // fused output quantisation (kEpi != 0): C is not written; e4m3 codes leave through the TMA-store map, one fp32
+  // scale per (row, 128-column group) goes to q_scales[row * qs_sm + group * qs_sg]
+  float* q_scales;
+  int64_t qs_sm, qs_sg;
+  float q_eps;
   long long* dbg;            // diagnostics (kDiag == 4): per-K-block clock64 stamps of CTA 0, else null
   void* mc_ptr;              // NVLS multicast address of this rank's panel (fused all-gather, multicast form) or null
   uint32_t stage_tx_bytes;   // bytes TMA delivers per stage to the (leader's) full barrier
@@ -173,8 +179,11 @@ __device__ __forceinline__ void tile_coords(int tile, const GemmParams& p, int& 
 // TMEM like an unscaled GEMM (one accumulator hand-off per tile) — both measure ceilings of the TMA/MMA pipeline.
 // kSplitN: each K block is issued as two N/2-wide MMA halves with their own full/empty barriers, so a half can be
 // promoted (and handed back) while the other half and the next K block are still in the tensor pipe.
+// kEpi: 0 = C in OutT; 1 = fused per-token-group quantisation of the OutT-rounded result (e4m3 codes + one fp32 scale per
+// 1x128 group, bit-identical to GEMM -> sgl_per_token_group_quant_8bit); 2 = the same after silu(gate)*up, the tile's
+// first 128 columns being a gate block and its last 128 the matching up block (weights interleaved by 128-row blocks).
 template <int BLOCK_N, int kStages, int kCG, typename OutT, bool kTmaStore, int kDiag = 0, bool kSplitN = false,
-          bool kGrouped = false>
+          bool kGrouped = false, int kEpi = 0>
 __global__ void __launch_bounds__(kNumThreads, 1)
 fp8_blockwise_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
                           const __grid_constant__ CMaps tmap_c, const GemmParams p) {
@@ -186,6 +195,8 @@ fp8_blockwise_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gr
   static_assert(!kSplitN || (BLOCK_N == 256 && (kDiag == 0 || kDiag == 4)), "split-N is for the 256-wide product tiles");
   static_assert(!kTmaStore || C::kCanTmaStore, "TMA-store epilogue needs >= 64 columns per warp");
   static_assert(!kGrouped || (kCG == 1 && !kTmaStore && kDiag == 0 && !kSplitN), "grouped mode: single-CTA tiles, predicated stores");
+  static_assert(kEpi == 0 || (BLOCK_N == 256 && kTmaStore && kDiag == 0 && !kSplitN && !kGrouped),
+                "fused output quantisation: 256-wide tiles (one 128-column group per epilogue warp), TMA-store epilogue");
 
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   // 128B-swizzled TMA/UMMA tiles need 1024-byte alignment.  The budget (kSmemOverhead) has no slack for a
@@ -705,6 +716,95 @@ fp8_blockwise_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gr
       first_segment = false;
       // ---------------- write the finished 32 x NC sub-tile ----------------
       if (!write_out) continue;
+      if constexpr (kEpi != 0) {
+        // ---- fused output quantisation: this thread holds one whole 1x128 group (row `row`, columns col0..col0+127) ----
+        // Bit-identical to writing C in OutT and running the quant op on it: round to OutT first, then the op's own
+        // arithmetic (amax, RN(amax/448), the exhaustively verified RN(y/s) scheme of quant_kernel.cuh, sign copied).
+#pragma unroll
+        for (int i = 0; i < NC; ++i) accum[i] = round_to<OutT>(accum[i]);
+        bool emit = col0 < p.N;                                   // warp-uniform
+        int out_col = col0;
+        if constexpr (kEpi == 2) {
+          // gate | up: the up-half warp (ew + 4, same rows) parks its OutT-rounded values in the two staging boxes of
+          // the pair; the gate-half warp folds them in as silu(g) * u and quantises.  Two named-barrier phases per
+          // tile and pair: "boxes free" (the gate warp's previous TMA store has read its box) and "up values written".
+          const uint32_t box_lo = smem_store + uint32_t(quarter) * (32 * kStoreBoxCols * 2);
+          const uint32_t box_hi = box_lo + 4u * (32 * kStoreBoxCols * 2);
+          const int bar_id = 1 + quarter;
+          if (half == 1) {
+            asm volatile("bar.sync %0, 64;" ::"r"(bar_id) : "memory");
+#pragma unroll
+            for (int j = 0; j < 16; ++j) {                       // 16 x 16 B = 128 OutT values of this lane's row
+              const float* a = accum + j * 8;
+              const uint32_t w0 = pack2<OutT>(a[0], a[1]), w1 = pack2<OutT>(a[2], a[3]);
+              const uint32_t w2 = pack2<OutT>(a[4], a[5]), w3 = pack2<OutT>(a[6], a[7]);
+              const uint32_t dst = (j < 8 ? box_lo : box_hi) + uint32_t(lane * 128 + (((j & 7) ^ (lane & 7)) << 4));
+              asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(dst), "r"(w0), "r"(w1), "r"(w2), "r"(w3) : "memory");
+            }
+            asm volatile("bar.sync %0, 64;" ::"r"(bar_id) : "memory");
+            emit = false;
+          } else {
+            if (lane == 0) ptx::tma_store_wait_read<0>();
+            __syncwarp();
+            asm volatile("bar.sync %0, 64;" ::"r"(bar_id) : "memory");
+            asm volatile("bar.sync %0, 64;" ::"r"(bar_id) : "memory");
+#pragma unroll
+            for (int j = 0; j < 16; ++j) {
+              uint32_t w[4];
+              const uint32_t src = (j < 8 ? box_lo : box_hi) + uint32_t(lane * 128 + (((j & 7) ^ (lane & 7)) << 4));
+              asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(w[0]), "=r"(w[1]), "=r"(w[2]), "=r"(w[3]) : "r"(src));
+#pragma unroll
+              for (int t = 0; t < 4; ++t) {
+                const float2 u = unpack2<OutT>(w[t]);
+                accum[j * 8 + 2 * t] = silu_mul<OutT>(accum[j * 8 + 2 * t], u.x);
+                accum[j * 8 + 2 * t + 1] = silu_mul<OutT>(accum[j * 8 + 2 * t + 1], u.y);
+              }
+            }
+            __syncwarp();                                        // every lane has read the boxes before box_lo is reused below
+            out_col = nb * (BLOCK_N / 2);
+          }
+        }
+        if (emit) {
+          float amax = 0.0f;
+#pragma unroll
+          for (int i = 0; i < NC; ++i) amax = fmaxf(amax, fabsf(accum[i]));
+          amax = fmaxf(amax, p.q_eps);
+          // RN(amax / 448) exactly as the quant op forms it (same expression, so overflowed f16 groups agree too)
+          constexpr float kRcp448 = 1.0f / 448.0f;
+          const float q0s = amax * kRcp448;
+          const float scale = __fmaf_rn(__fmaf_rn(-q0s, 448.0f, amax), kRcp448, q0s);
+          if (row_ok) p.q_scales[int64_t(row) * p.qs_sm + int64_t(out_col >> 7) * p.qs_sg] = scale;
+          const float r = __frcp_rn(scale), ns = -scale;
+          if constexpr (kEpi == 1) {
+            if (lane == 0) ptx::tma_store_wait_read<0>();        // the previous tile's store has read this warp's box
+            __syncwarp();
+          }
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {                          // 8 x 16 B = 128 codes of this lane's row
+            uint32_t w[4];
+#pragma unroll
+            for (int t = 0; t < 4; ++t) {
+              const float* a = accum + j * 16 + t * 4;
+              const float2 c0 = div_pair(make_float2(a[0], a[1]), r, ns), c1 = div_pair(make_float2(a[2], a[3]), r, ns);
+              const uint32_t lo = __nv_cvt_float2_to_fp8x2(c0, __NV_SATFINITE, __NV_E4M3);
+              const uint32_t hi = __nv_cvt_float2_to_fp8x2(c1, __NV_SATFINITE, __NV_E4M3);
+              const uint32_t mag = __byte_perm(lo, hi, 0x5410);
+              const uint32_t s01 = __byte_perm(__float_as_uint(a[0]), __float_as_uint(a[1]), 0x0073);
+              const uint32_t s23 = __byte_perm(__float_as_uint(a[2]), __float_as_uint(a[3]), 0x0073);
+              const uint32_t sgn = __byte_perm(s01, s23, 0x5410);
+              asm("lop3.b32 %0, %1, %2, %3, 0xE4;" : "=r"(w[t]) : "r"(sgn), "r"(mag), "r"(0x80808080u));   // sign ? y : code
+            }
+            const uint32_t dst = my_store + uint32_t(lane * 128 + ((j ^ (lane & 7)) << 4));
+            asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(dst), "r"(w[0]), "r"(w[1]), "r"(w[2]), "r"(w[3]) : "memory");
+          }
+          ptx::fence_proxy_async_smem();
+          __syncwarp();
+          if (lane == 0) {
+            ptx::tma_store_2d(&tmap_c.m[0], my_store, out_col, m0 + quarter * 32);   // 32 rows x 128 codes, clipped at M / N
+            ptx::tma_store_commit();
+          }
+        }
+      } else
       if constexpr (kTmaStore) {
 #pragma unroll
         for (int cb = 0; cb < NC / kStoreBoxCols; ++cb) {
@@ -917,11 +1017,11 @@ constexpr int kNumProductVariants = 7;   // ids 0..6; 7..12 are diagnostics; 13,
 constexpr int64_t kCounterAreaBytes = 1 << 20;   // first MiB of a stream-K workspace: tile counters (zero between launches)
 
 template <int BLOCK_N, int kStages, int kCG, typename OutT, bool kTmaStore, int kDiag = 0, bool kSplitN = false,
-          bool kGrouped = false>
+          bool kGrouped = false, int kEpi = 0>
 static int launch_variant(const CUtensorMap& ta, const CUtensorMap& tb, const CMaps& tc, const GemmParams& p,
                           int workers, cudaStream_t st) {
   using C = Cfg<BLOCK_N, kCG>;
-  auto kern = fp8_blockwise_gemm_kernel<BLOCK_N, kStages, kCG, OutT, kTmaStore, kDiag, kSplitN, kGrouped>;
+  auto kern = fp8_blockwise_gemm_kernel<BLOCK_N, kStages, kCG, OutT, kTmaStore, kDiag, kSplitN, kGrouped, kEpi>;
   constexpr int smem = kMaxDynSmem;
   (void)sizeof(C);
   static bool configured = false;   // per instantiation
@@ -975,6 +1075,21 @@ static int launch_by_id(int v, const CUtensorMap& ta, const CUtensorMap& tb, con
     case 22: return launch_variant<256, 6, 2, OutT, true, 10>(ta, tb, tc, p, num_sms, st);
     default: return SGLK_E_VARIANT;
   }
+}
+
+// fused output quantisation: the paired 256x256 tiles for prefill, the single-CTA 128x256 tiles below that
+template <typename OutT>
+static int launch_quant_epilogue(int v, int mode, const CUtensorMap& ta, const CUtensorMap& tb, const CMaps& tc,
+                                 const GemmParams& p, int workers, cudaStream_t st) {
+  if (v == 3) {
+    return mode == 2 ? launch_variant<256, 6, 2, OutT, true, 0, false, false, 2>(ta, tb, tc, p, workers, st)
+                     : launch_variant<256, 6, 2, OutT, true, 0, false, false, 1>(ta, tb, tc, p, workers, st);
+  }
+  if (v == 2) {
+    return mode == 2 ? launch_variant<256, 4, 1, OutT, true, 0, false, false, 2>(ta, tb, tc, p, workers, st)
+                     : launch_variant<256, 4, 1, OutT, true, 0, false, false, 1>(ta, tb, tc, p, workers, st);
+  }
+  return SGLK_E_VARIANT;
 }
 
 static bool tma_store_ok(const void* C, int64_t ldc, int out_bytes) {
@@ -1038,16 +1153,37 @@ static Plan make_plan(int64_t M, int64_t N, int64_t K, int variant, int num_sms,
   return pl;
 }
 
+// Fused output quantisation request (sglk_fp8_blockwise_scaled_mm_quant): codes [M, Nq] (Nq = N, or N/2 with
+// silu_mul), row stride ldq bytes; scales (row, group) at row * ss_m + group * ss_g floats.
+struct QuantOut {
+  void* codes;
+  int64_t ldq;
+  float* scales;
+  int64_t ss_m, ss_g;
+  float eps;
+  int silu_mul;
+};
+
 static int gemm_entry(const void* A, const void* B, const float* sa, const float* sb, void* Cout, int64_t M,
                       int64_t N, int64_t K, int64_t lda, int64_t ldb, int64_t ldc, int64_t sa_sm, int64_t sa_sk,
                       int64_t sb_sk, int64_t sb_sn, int out_dtype, int variant, int num_sms, void* workspace,
                       int64_t workspace_bytes, void* stream, void* const* extra_dests = nullptr, int num_extra = 0,
-                      void* mc_ptr = nullptr) {
+                      void* mc_ptr = nullptr, const QuantOut* qo = nullptr) {
   if (M < 0 || N < 0 || K < 0) return SGLK_E_SHAPE;
   if (out_dtype != SGLK_BF16 && out_dtype != SGLK_F16) return SGLK_E_DTYPE;
   if (M == 0 || N == 0) return SGLK_OK;
-  if (!Cout) return SGLK_E_NULL;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (qo) {
+    // whole 1x128 groups only; gate|up tiles are 256 wide; codes leave through a 128-byte-wide TMA box
+    if (!qo->codes || !qo->scales) return SGLK_E_NULL;
+    if (K == 0 || N % (qo->silu_mul ? 256 : 128) != 0) return SGLK_E_SHAPE;
+    const int64_t nq = qo->silu_mul ? N / 2 : N;
+    if (qo->ldq < nq || qo->ldq % 16 != 0 || (reinterpret_cast<uintptr_t>(qo->codes) & 15)) return SGLK_E_STRIDE;
+    if (num_extra != 0 || mc_ptr) return SGLK_E_ARG;
+    variant = M > 128 ? 3 : 2;
+    Cout = qo->codes; ldc = N;       // (placeholders for the shared checks below; C itself is never written)
+  }
+  if (!Cout) return SGLK_E_NULL;
   if (K == 0) {   // empty sum: C = 0
     if (ldc == N) return int(cudaMemsetAsync(Cout, 0, size_t(M) * N * 2, st));
     return int(cudaMemset2DAsync(Cout, size_t(ldc) * 2, 0, size_t(N) * 2, size_t(M), st));
@@ -1062,7 +1198,7 @@ static int gemm_entry(const void* A, const void* B, const float* sa, const float
   if (num_extra < 0 || num_extra > kMaxDests - 1 || (num_extra > 0 && !extra_dests)) return SGLK_E_ARG;
   for (int d = 0; d < num_extra; ++d)
     if (!extra_dests[d] || !tma_store_ok(extra_dests[d], ldc, 2)) return SGLK_E_STRIDE;
-  if (v.tma_store && !tma_store_ok(Cout, ldc, 2)) {
+  if (!qo && v.tma_store && !tma_store_ok(Cout, ldc, 2)) {
     // same tile shape, predicated-store epilogue
     variant = (v.cg == 2) ? 4 : 1;
     v = kVariants[variant];
@@ -1074,7 +1210,11 @@ static int gemm_entry(const void* A, const void* B, const float* sa, const float
   p.sa = sa; p.sb = sb; p.C = Cout;
   p.M = M; p.N = N; p.K = K; p.ldc = ldc;
   p.sa_sm = sa_sm; p.sa_sk = sa_sk; p.sb_sk = sb_sk; p.sb_sn = sb_sn;
-  Plan pl = make_plan(M, N, K, variant, num_sms, workspace != nullptr);
+  // gate|up mode pairs two epilogue warps with named barriers: both must finish the same tiles, so no stream-K there
+  const bool allow_sk = workspace != nullptr && !(qo && qo->silu_mul);
+  Plan pl = make_plan(M, N, K, variant, num_sms, allow_sk);
+  if (qo) { p.q_scales = qo->scales; p.qs_sm = qo->ss_m; p.qs_sg = qo->ss_g; p.q_eps = qo->eps; }
+  else { p.q_scales = nullptr; p.qs_sm = p.qs_sg = 0; p.q_eps = 0.0f; }
   if (pl.stream_k && (workspace_bytes < pl.counter_bytes + pl.partial_bytes || (reinterpret_cast<uintptr_t>(workspace) & 15)))
     pl = make_plan(M, N, K, variant, num_sms, false);
   p.num_m_blocks = pl.num_m_blocks;
@@ -1141,6 +1281,15 @@ static int gemm_entry(const void* A, const void* B, const float* sa, const float
   if (!make_tmap_2d(&tb, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, B, uint64_t(N), uint64_t(K), uint64_t(ldb),
                     uint32_t(v.block_n / v.cg / (split_b_boxes ? 2 : 1)), BLOCK_K))
     return SGLK_E_DRIVER;
+  if (qo) {
+    const int64_t nq = qo->silu_mul ? N / 2 : N;
+    if (!make_tmap_2d(&tc.m[0], CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, qo->codes, uint64_t(M), uint64_t(nq), uint64_t(qo->ldq), 32, 128))
+      return SGLK_E_DRIVER;
+    for (int d = 1; d < kMaxDests; ++d) tc.m[d] = tc.m[0];
+    const int mode = qo->silu_mul ? 2 : 1;
+    if (out_dtype == SGLK_BF16) return launch_quant_epilogue<__nv_bfloat16>(variant, mode, ta, tb, tc, p, pl.workers, st);
+    return launch_quant_epilogue<__half>(variant, mode, ta, tb, tc, p, pl.workers, st);
+  }
   if (v.tma_store) {
     const CUtensorMapDataType cdt = out_dtype == SGLK_BF16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT16;
     if (!make_tmap_2d(&tc.m[0], cdt, 2, Cout, uint64_t(M), uint64_t(N), uint64_t(ldc), 32, kStoreBoxCols)) return SGLK_E_DRIVER;
@@ -1250,6 +1399,17 @@ extern "C" int sglk_fp8_blockwise_scaled_mm_allgather(const void* A, const void*
   return sglk::gemm_entry(A, B, sa, sb, C_local, M, N, K, lda, ldb, ldc, sa_stride_m, sa_stride_k, sb_stride_k,
                           sb_stride_n, out_dtype, variant, num_sms, workspace, workspace_bytes, stream,
                           C_multicast ? nullptr : C_peers, C_multicast ? 0 : num_peers, C_multicast);
+}
+
+extern "C" int sglk_fp8_blockwise_scaled_mm_quant(const void* A, const void* B, const float* sa, const float* sb,
+                                                  void* out_q, float* out_s, int64_t M, int64_t N, int64_t K, int64_t lda,
+                                                  int64_t ldb, int64_t ldq, int64_t sa_stride_m, int64_t sa_stride_k,
+                                                  int64_t sb_stride_k, int64_t sb_stride_n, int64_t os_stride_m,
+                                                  int64_t os_stride_g, int round_dtype, float eps, int silu_mul,
+                                                  int num_sms, void* workspace, int64_t workspace_bytes, void* stream) {
+  sglk::QuantOut qo{out_q, ldq, out_s, os_stride_m, os_stride_g, eps, silu_mul ? 1 : 0};
+  return sglk::gemm_entry(A, B, sa, sb, nullptr, M, N, K, lda, ldb, N, sa_stride_m, sa_stride_k, sb_stride_k, sb_stride_n,
+                          round_dtype, -1, num_sms, workspace, workspace_bytes, stream, nullptr, 0, nullptr, &qo);
 }
 
 extern "C" int sglk_debug_set_stream_k_mode(int mode) {

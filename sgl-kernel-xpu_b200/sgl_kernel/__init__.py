@@ -8,6 +8,8 @@ sgl_per_token_quant_fp8} for dispatch key CUDA.
 """
 from .gemm import (
     fp8_blockwise_scaled_mm,
+    fp8_blockwise_scaled_mm_quant,
+    interleave_gate_up,
     sgl_per_token_group_quant_8bit,
     sgl_per_token_group_quant_fp8,
     sgl_per_token_group_quant_int8,
@@ -26,6 +28,8 @@ __version__ = "0.11.0+b200"
 
 __all__ = [
     "fp8_blockwise_scaled_mm",
+    "fp8_blockwise_scaled_mm_quant",
+    "interleave_gate_up",
     "fp8_blockwise_scaled_grouped_mm",
     "sgl_per_token_group_quant_8bit",
     "sgl_per_token_group_quant_fp8",

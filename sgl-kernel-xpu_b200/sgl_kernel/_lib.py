@@ -36,6 +36,8 @@ SYMBOLS = {
         _i32, [_vp, _vp, _vp, _vp, _vp] + [_i64] * 10 + [_i32, _vp]),
     "sglk_fp8_blockwise_scaled_mm_ex": (
         _i32, [_vp, _vp, _vp, _vp, _vp] + [_i64] * 10 + [_i32, _i32, _i32, _vp, _i64, _vp]),
+    "sglk_fp8_blockwise_scaled_mm_quant": (
+        _i32, [_vp, _vp, _vp, _vp, _vp, _vp] + [_i64] * 12 + [_i32, _f32, _i32, _i32, _vp, _i64, _vp]),
     "sglk_fp8_blockwise_scaled_grouped_mm": (
         _i32, [_vp, _vp, _vp, _vp, _vp, _vp, _vp] + [_i64] * 12 + [_i32, _i32, _vp, _i64, _vp]),
     "sglk_grouped_mm_workspace_bytes": (_i64, [_i64, _i64]),

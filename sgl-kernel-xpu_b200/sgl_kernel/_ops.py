@@ -47,7 +47,14 @@ _GROUPED_SCHEMA = (
 # verbatim: src/torch_extension_sycl.cc:410
 _TOKEN_QUANT_SCHEMA = "sgl_per_token_quant_fp8(Tensor input, Tensor(a!) output_q, Tensor(b!) output_s) -> ()"
 
+# B200 extension (no reference counterpart): the GEMM with the next layer's group quantisation fused into its epilogue
+_GEMM_QUANT_SCHEMA = (
+    "fp8_blockwise_scaled_mm_quant(Tensor mat_a, Tensor mat_b, Tensor scales_a, Tensor scales_b, ScalarType round_dtype,"
+    " float eps, bool fuse_silu_and_mul, bool column_major_scales) -> (Tensor, Tensor)"
+)
+
 _library = torch.library.Library("sgl_kernel", "FRAGMENT")
+_library.define(_GEMM_QUANT_SCHEMA)
 _library.define(_TOKEN_QUANT_SCHEMA)
 _library.define(_QUANT_SCHEMA)
 _library.define(_QUANT_V2_SCHEMA)
@@ -298,6 +305,53 @@ def _gemm_allgather(mat_a, mat_b, scales_a, scales_b, out_full, col_lo: int, pee
     return out_full
 
 
+def _gemm_quant(mat_a, mat_b, scales_a, scales_b, round_dtype, eps, fuse_silu_and_mul, column_major_scales):
+    """fp8_blockwise_scaled_mm followed by sgl_per_token_group_quant_8bit (group 128, e4m3; optionally silu(gate)*up in
+    between, gate/up interleaved by 128-column blocks) as ONE kernel: the bf16 intermediate never reaches HBM.
+    Returns (codes [M, Nq], scales [M, Nq/128]) — bit-identical to the two (three) separate ops."""
+    name = "fp8_blockwise_scaled_mm_quant"
+    _check(mat_a.is_cuda and mat_b.is_cuda and scales_a.is_cuda and scales_b.is_cuda, f"{name}: tensors must be CUDA tensors")
+    M, N, K = _gemm_checks(mat_a, mat_b, scales_a, scales_b, round_dtype)
+    fuse = bool(fuse_silu_and_mul)
+    _check(K > 0, f"{name}: K must be positive")
+    _check(N % (256 if fuse else 128) == 0, f"{name}: N must be a multiple of {256 if fuse else 128}")
+    nq = N // 2 if fuse else N
+    groups = nq // 128
+    q = torch.empty((M, nq), dtype=torch.float8_e4m3fn, device=mat_a.device)
+    if column_major_scales:
+        s = torch.empty((groups, M), dtype=torch.float32, device=mat_a.device).t()
+    else:
+        s = torch.empty((M, groups), dtype=torch.float32, device=mat_a.device)
+    if M == 0 or N == 0:
+        return q, s
+    lda = mat_a.stride(0) if M > 1 else max(K, 16)
+    ldb = mat_b.stride(1) if N > 1 else max(K, 16)
+    _check(lda % 16 == 0 and ldb % 16 == 0 and mat_a.data_ptr() % 16 == 0 and mat_b.data_ptr() % 16 == 0,
+           "mat_a / mat_b rows must be 16-byte aligned")
+    lib = _lib.load()
+    with torch.cuda.device(mat_a.device):
+        stream = _stream_ptr(mat_a)
+        ws_ptr, ws_bytes = None, 0
+        need = lib.sglk_gemm_workspace_bytes(M, N, K, 3 if M > 128 else 2, 0)
+        if need > 0:
+            ws = _get_workspace(mat_a.device, stream, need)
+            ws_ptr, ws_bytes = ws.data_ptr(), ws.numel()
+        rc = lib.sglk_fp8_blockwise_scaled_mm_quant(
+            mat_a.data_ptr(), mat_b.data_ptr(), scales_a.data_ptr(), scales_b.data_ptr(), q.data_ptr(), s.data_ptr(),
+            M, N, K, lda, ldb, q.stride(0), scales_a.stride(0), scales_a.stride(1), scales_b.stride(0), scales_b.stride(1),
+            s.stride(0), s.stride(1), _GEMM_OUT[round_dtype], float(eps), int(fuse), 0, ws_ptr, ws_bytes, stream)
+    _lib.check(rc, name)
+    return q, s
+
+
+def _gemm_quant_fake(mat_a, mat_b, scales_a, scales_b, round_dtype, eps, fuse_silu_and_mul, column_major_scales):
+    nq = mat_b.size(1) // (2 if fuse_silu_and_mul else 1)
+    q = torch.empty((mat_a.size(0), nq), dtype=torch.float8_e4m3fn, device=mat_a.device)
+    if column_major_scales:
+        return q, torch.empty((nq // 128, mat_a.size(0)), dtype=torch.float32, device=mat_a.device).t()
+    return q, torch.empty((mat_a.size(0), nq // 128), dtype=torch.float32, device=mat_a.device)
+
+
 def _gemm_op(mat_a, mat_b, scales_a, scales_b, out_dtype):
     return _gemm(mat_a, mat_b, scales_a, scales_b, out_dtype)
 
@@ -373,6 +427,8 @@ _library.impl("fp8_blockwise_scaled_grouped_mm", _grouped_mm, "CUDA")
 _library.impl("sgl_per_token_group_quant_8bit", _quant_v1, "CUDA")
 _library.impl("sgl_per_token_group_quant_8bit_v2", _quant_v2, "CUDA")
 _library.impl("fp8_blockwise_scaled_mm", _gemm_op, "CUDA")
+_library.impl("fp8_blockwise_scaled_mm_quant", _gemm_quant, "CUDA")
+_library.impl("fp8_blockwise_scaled_mm_quant", _gemm_quant_fake, "Meta")
 
 
 # Fake (meta) kernels so the ops trace under torch.compile / FakeTensor, as the reference README asks of

@@ -61,3 +61,32 @@ def sgl_per_token_quant_fp8(
 ) -> None:
     # python/sgl_kernel/gemm.py:236-241
     torch.ops.sgl_kernel.sgl_per_token_quant_fp8.default(input, output_q, output_s)
+
+
+def fp8_blockwise_scaled_mm_quant(
+    mat_a: torch.Tensor,
+    mat_b: torch.Tensor,
+    scales_a: torch.Tensor,
+    scales_b: torch.Tensor,
+    round_dtype: torch.dtype = torch.bfloat16,
+    eps: float = 1e-10,
+    fuse_silu_and_mul: bool = False,
+    column_major_scales: bool = False,
+):
+    """B200 extension: fp8_blockwise_scaled_mm whose epilogue emits the NEXT layer's e4m3 activations and 1x128 scales
+    (optionally after silu(gate) * up, gate/up interleaved by 128-column blocks — see `interleave_gate_up`).  Bit-identical
+    to fp8_blockwise_scaled_mm -> [silu_and_mul ->] sgl_per_token_group_quant_8bit, without the bf16 round trip."""
+    return torch.ops.sgl_kernel.fp8_blockwise_scaled_mm_quant.default(
+        mat_a, mat_b, scales_a, scales_b, round_dtype, eps, fuse_silu_and_mul, column_major_scales
+    )
+
+
+def interleave_gate_up(w_q: torch.Tensor, w_s: torch.Tensor):
+    """[gate; up] stacked weight ([2I, K] codes, [2I/128, K/128] scales) -> 128-row blocks interleaved
+    (gate block 0, up block 0, gate block 1, ...), the layout `fuse_silu_and_mul=True` expects."""
+    two_i, k = w_q.shape
+    assert two_i % 256 == 0 and w_s.shape[0] == two_i // 128
+    nb = two_i // 256
+    wq = w_q.view(2, nb, 128, k).transpose(0, 1).reshape(two_i, k).contiguous()
+    ws = w_s.view(2, nb, w_s.shape[1]).transpose(0, 1).reshape(two_i // 128, w_s.shape[1]).contiguous()
+    return wq, ws
