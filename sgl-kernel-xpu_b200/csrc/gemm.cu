@@ -183,11 +183,16 @@ __device__ __forceinline__ void tile_coords(int tile, const GemmParams& p, int& 
 // 1x128 group, bit-identical to GEMM -> sgl_per_token_group_quant_8bit); 2 = the same after silu(gate)*up, the tile's
 // first 128 columns being a gate block and its last 128 the matching up block (weights interleaved by 128-row blocks).
 template <int BLOCK_N, int kStages, int kCG, typename OutT, bool kTmaStore, int kDiag = 0, bool kSplitN = false,
-          bool kGrouped = false, int kEpi = 0>
+          bool kGrouped = false, int kEpi = 0, bool kMcB = false, int kPipe = 0>
 __global__ void __launch_bounds__(kNumThreads, 1)
 fp8_blockwise_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
                           const __grid_constant__ CMaps tmap_c, const GemmParams p) {
   using C = Cfg<BLOCK_N, kCG>;
+  // kMcB: a 2-CTA cluster of INDEPENDENT cta_group::1 tiles (same n-block, adjacent m-blocks).  Each CTA loads its own
+  // A rows and HALF of the shared B tile, multicast into both CTAs' smem — the L2 traffic of the paired 256x256 tile,
+  // but every accumulator hand-off (tcgen05.commit -> promotion warps -> issuer) stays inside one CTA.
+  constexpr int kCl = kMcB ? 2 : kCG;                  // CTAs per cluster = per 256-row (kCl == 2) tile slot
+  static_assert(!kMcB || (kCG == 1 && !kSplitN && !kGrouped && kDiag == 0), "multicast-B mode: cta_group::1 MMAs");
   constexpr int NC = C::NC;
   constexpr int kAccStages = C::kAccStages;
   constexpr int kHalves = kSplitN ? 2 : 1;             // accumulator hand-off granularity: whole stage or column half
@@ -222,7 +227,7 @@ fp8_blockwise_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gr
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
-  const uint32_t cta_rank = (kCG == 2) ? ptx::cluster_ctarank() : 0u;
+  const uint32_t cta_rank = (kCl == 2) ? ptx::cluster_ctarank() : 0u;
   const bool is_leader = cta_rank == 0;
 
   if (warp == 0 && lane == 0) {
@@ -234,7 +239,7 @@ fp8_blockwise_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gr
   if (warp == 1 && lane == 0) {
     for (int s = 0; s < nstages; ++s) {
       ptx::mbar_init(full_bar(s), 1);                    // one arrive.expect_tx by the (leader's) producer
-      ptx::mbar_init(empty_bar(s), 1);                   // one tcgen05.commit
+      ptx::mbar_init(empty_bar(s), kMcB ? 2 : 1);        // one tcgen05.commit (multicast-B: this CTA's and the peer's)
     }
     for (int s = 0; s < kAccBars; ++s) {
       ptx::mbar_init(tfull_bar(s), 1);                             // one tcgen05.commit
@@ -247,7 +252,7 @@ fp8_blockwise_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gr
     ptx::tmem_relinquish<kCG>();
   }
   ptx::tc_fence_before();
-  if (kCG == 2) ptx::cluster_sync(); else __syncthreads();
+  if (kCl == 2) ptx::cluster_sync(); else __syncthreads();
   ptx::tc_fence_after();
   const uint32_t tmem_base = *reinterpret_cast<volatile uint32_t*>(smem_gen + (tmem_slot - smem_base));
 
@@ -257,8 +262,8 @@ fp8_blockwise_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gr
   // grouped: tile -> (m-tile, n-block) with the m-tile fastest, so CTAs running together share an expert's B panel
   auto grouped_tile = [&](int tile, int& nb) { nb = tile / num_m_tiles; return __ldg(p.grp_tiles + (tile - nb * num_m_tiles)); };
   (void)grouped_tile;
-  const int num_workers = gridDim.x / kCG;
-  const int worker = blockIdx.x / kCG;
+  const int num_workers = gridDim.x / kCl;
+  const int worker = blockIdx.x / kCl;
   const int num_kb = p.num_k_blocks;
 
   // Register budget: 384 threads x 168 at launch; the 4 control warps give theirs back so the
@@ -283,15 +288,21 @@ fp8_blockwise_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gr
           mb = 0; (void)mb;
         } else {
           tile_coords(tile, p, mb, nb);
-          m0 = mb * (BLOCK_M * kCG) + int(cta_rank) * BLOCK_M;
-          n0 = nb * BLOCK_N + int(cta_rank) * C::LOAD_N;
+          m0 = mb * (BLOCK_M * kCl) + int(cta_rank) * BLOCK_M;
+          n0 = nb * BLOCK_N + int(cta_rank) * (kMcB ? BLOCK_N / 2 : C::LOAD_N);
         }
         for (int kb = kb0; kb < kb1; ++kb) {
           ptx::mbar_wait(empty_bar(stage), phase ^ 1);
           const uint32_t sa_addr = smem_base + stage * stage_bytes;
           const uint32_t sb_addr = sa_addr + p.a_slot_bytes;
           if (ptx::elect_one()) {
-            if constexpr (kCG == 1) {
+            if constexpr (kMcB) {
+              // own A rows; this CTA's half of the B tile goes to BOTH CTAs (each barrier expects A + all of B)
+              ptx::mbar_arrive_expect_tx(full_bar(stage), p.stage_tx_bytes);
+              ptx::tma_load_2d(&tmap_a, full_bar(stage), sa_addr, kb * BLOCK_K, m0, pol_a);
+              ptx::tma_load_2d_mcast(&tmap_b, full_bar(stage), sb_addr + cta_rank * uint32_t((BLOCK_N / 2) * BLOCK_K),
+                                     kb * BLOCK_K, n0, uint16_t(3), pol_b);
+            } else if constexpr (kCG == 1) {
               ptx::mbar_arrive_expect_tx(full_bar(stage), p.stage_tx_bytes);
               ptx::tma_load_2d(&tmap_a, full_bar(stage), sa_addr, kb * BLOCK_K, m0, pol_a);
               ptx::tma_load_2d(&tmap_b, full_bar(stage), sb_addr, kb * BLOCK_K, n0, pol_b);
@@ -322,7 +333,7 @@ fp8_blockwise_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gr
     // The whole warp walks the loop convergently and one elected lane issues: descriptors, barrier
     // addresses and TMEM addresses then live in uniform registers (a lane-0-only branch made ptxas wrap
     // every tcgen05.mma in an ELECT/R2UR loop and the issuing thread became the bottleneck — profile r1b).
-    if (is_leader) {
+    if (is_leader || kMcB) {
       constexpr uint32_t idesc = make_idesc(BLOCK_M * kCG, BLOCK_N);
       const uint32_t tmem_base_u = __shfl_sync(0xFFFFFFFFu, tmem_base, 0);
       const uint64_t desc_hi = make_smem_desc(0);
@@ -388,7 +399,9 @@ fp8_blockwise_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gr
               ptx::mma_f8f6f4<kCG>(d_tmem, da + uint64_t(k * (UMMA_K >> 4)), db + uint64_t(k * (UMMA_K >> 4)), idesc,
                                    (k > 0 || (kDiag == 2 && kb > kb0)) ? 1u : 0u);
             }
-            ptx::tc_commit<kCG>(empty_bar(stage));               // smem stage reusable once these MMAs have read it
+            // smem stage reusable once these MMAs have read it (multicast-B: the peer's producer writes here too)
+            if constexpr (kMcB) ptx::tc_commit_mcast1(empty_bar(stage), uint16_t(3));
+            else ptx::tc_commit<kCG>(empty_bar(stage));
             if (!last_of_tile) ptx::tc_commit<kCG>(tfull_bar(acc));   // partial for this K block complete
           }
           __syncwarp();
@@ -444,7 +457,7 @@ fp8_blockwise_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gr
         mb = 0;
       } else {
         tile_coords(tile, p, mb, nb);
-        m0 = mb * (BLOCK_M * kCG) + int(cta_rank) * BLOCK_M;
+        m0 = mb * (BLOCK_M * kCl) + int(cta_rank) * BLOCK_M;
         row_ok = m0 + quarter * 32 + lane < p.M;
       }
       const int row = m0 + quarter * 32 + lane;
@@ -552,7 +565,44 @@ fp8_blockwise_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gr
         float4 a_nx, b_nx;                               // vector path: the next group's raw scales
         const float4* sa4n = nullptr;
         const float4* sb4n = nullptr;
+        // kPipe == 1: chunk loads go out in PAIRS (both staging buffers), so a K block costs two tcgen05.ld round trips
+        // instead of four and only two chunks of FMAs (not three) stand between the block's commit and the hand-back
+        // of its accumulator stage.  Entry state: chunks 0 and 1 of this block are already in flight.
+        auto fma_chunk = [&](int c, const uint32_t (&buf)[32], float s) {
+#pragma unroll
+          for (int i = 0; i < 32; i += 2) ptx::fma2(accum[c * 32 + i], accum[c * 32 + i + 1], buf[i], buf[i + 1], s);
+        };
+        auto promote2 = [&](const float s, const bool more, const bool fetch = false) {
+          static_assert(kPipe == 0 || NCH == 4, "paired chunk loads: 128 columns per epilogue warp");
+          ptx::tmem_ld_wait(v[0]);
+          ptx::tmem_ld_wait(v[1]);
+          fma_chunk(0, v[0], s);
+          ptx::tmem_ld_32x32(taddr + 64u, v[0]);
+          fma_chunk(1, v[1], s);
+          ptx::tmem_ld_32x32(taddr + 96u, v[1]);
+          ptx::tmem_ld_wait(v[0]);
+          ptx::tmem_ld_wait(v[1]);
+          release_stage();
+          bool ready = false;
+          if (more) {
+            taddr = stage_addr();
+            ready = ptx::mbar_try_wait(tfull_bar(acc * kHalves + hb), acc_phase);
+          }
+          if (fetch) {
+            a_nx = __ldg(sa4n);
+            b_nx = __ldg(sb4n);
+          }
+          fma_chunk(2, v[0], s);
+          if (more) {
+            if (!ready) ptx::mbar_wait(tfull_bar(acc * kHalves + hb), acc_phase);
+            ptx::tc_fence_after();
+            ptx::tmem_ld_32x32(taddr, v[0]);
+          }
+          fma_chunk(3, v[1], s);
+          if (more) ptx::tmem_ld_32x32(taddr + 32u, v[1]);
+        };
         auto promote = [&](const float s, const bool more, const bool fetch = false) {
+          if constexpr (kPipe == 1) { promote2(s, more, fetch); return; }
           const bool stamp = (kDiag == 4 || kDiag >= 6) && blockIdx.x == 0 && ew == 0 && lane == 0 && dbg_kb < 64 && tile == worker;
 #pragma unroll
           for (int c = 0; c < NCH; ++c) {
@@ -624,6 +674,7 @@ fp8_blockwise_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gr
           ptx::tc_fence_after();
           taddr = stage_addr();
           ptx::tmem_ld_32x32(taddr, v[0]);
+          if constexpr (kPipe == 1) ptx::tmem_ld_32x32(taddr + 32u, v[1]);
           if constexpr (kDiag == 7 || kDiag == 8) {     // diagnostic: FMAs on two chunks fetched once, no tcgen05.ld in the loop
             ptx::tmem_ld_32x32(taddr + 32u, v[1]);
             ptx::tmem_ld_wait(v[0]);
@@ -646,6 +697,7 @@ fp8_blockwise_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gr
           ptx::tc_fence_after();
           taddr = stage_addr();
           ptx::tmem_ld_32x32(taddr, v[0]);
+          if constexpr (kPipe == 1) ptx::tmem_ld_32x32(taddr + 32u, v[1]);
           for (int kb = kb0; kb < kb1; ++kb) promote(staged_scale(), kb + 1 < kb1);
           ptx::cp_async_wait<0>();
         }
@@ -680,7 +732,7 @@ fp8_blockwise_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gr
         auto slot_of = [&](int c) { return 2 * c + ((int(range_begin(c) / num_kb) == tile) ? 0 : 1); };
         constexpr int kWarpFloats = NC * 32;                         // one warp's 32 x NC partial
         auto part_ptr = [&](int c) {
-          return p.ws_partials + (int64_t(slot_of(c)) * (kCG * kNumEpiWarps) + int(cta_rank) * kNumEpiWarps + ew) * kWarpFloats;
+          return p.ws_partials + (int64_t(slot_of(c)) * (kCl * kNumEpiWarps) + int(cta_rank) * kNumEpiWarps + ew) * kWarpFloats;
         };
         (void)first_segment;
         float4* mine = reinterpret_cast<float4*>(part_ptr(worker));
@@ -691,7 +743,7 @@ fp8_blockwise_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gr
         }
         __threadfence();
         __syncwarp();
-        int32_t* cnt = p.ws_counters + int64_t(tile) * (kCG * kNumEpiWarps) + int(cta_rank) * kNumEpiWarps + ew;
+        int32_t* cnt = p.ws_counters + int64_t(tile) * (kCl * kNumEpiWarps) + int(cta_rank) * kNumEpiWarps + ew;
         int arrived = 0;
         if (lane == 0) arrived = atomicAdd(cnt, 1);
         arrived = __shfl_sync(0xFFFFFFFFu, arrived, 0);
@@ -886,7 +938,7 @@ fp8_blockwise_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gr
 
   // =========================== teardown ===========================
   ptx::tc_fence_before();
-  if (kCG == 2) ptx::cluster_sync(); else __syncthreads();
+  if (kCl == 2) ptx::cluster_sync(); else __syncthreads();
   if (warp == 2) ptx::tmem_dealloc<kCG>(tmem_base, C::TMEM_COLS);
 }
 
@@ -983,8 +1035,9 @@ static bool make_tmap_2d(CUtensorMap* m, CUtensorMapDataType dt, int elem_bytes,
 
 struct Variant {
   const char* name;
-  int block_n, stages, cg;
+  int block_n, stages, cg;   // cg: CTAs that share one 128*cg-row tile slot (cluster size)
   bool tma_store;
+  bool mcb = false;          // cg == 2 as a cluster of two independent cta_group::1 tiles with multicast B
 };
 // index == variant id of the C ABI
 static const Variant kVariants[] = {
@@ -1011,17 +1064,22 @@ static const Variant kVariants[] = {
     {"diag_n256_s6_cta2_fma_only_not_on_mma_scheduler_timestamps", 256, 6, 2, true},
     {"diag_n256_s6_cta2_handoff_then_fma_timestamps", 256, 6, 2, true},
     {"diag_n256_s6_cta2_serialised_timestamps", 256, 6, 2, true},
+    {"n256_s4_cl2_mcb_tma", 256, 4, 2, true, true},      // product variant: 2-CTA cluster, cta_group::1 tiles, multicast B
+    {"n256_s6_cta2_tma_pairld", 256, 6, 2, true},         // paired tiles, chunk loads issued in pairs
+    {"n256_s6_cta2_tma_splitn_pairld", 256, 6, 2, true},
+    {"n256_s4_cl2_mcb_tma_pairld", 256, 4, 2, true, true},
 };
+constexpr int kFirstStampVariant = 15, kLastStampVariant = 22;
 constexpr int kNumVariants = int(sizeof(kVariants) / sizeof(kVariants[0]));
 constexpr int kNumProductVariants = 7;   // ids 0..6; 7..12 are diagnostics; 13, 14 are product variants again
 constexpr int64_t kCounterAreaBytes = 1 << 20;   // first MiB of a stream-K workspace: tile counters (zero between launches)
 
 template <int BLOCK_N, int kStages, int kCG, typename OutT, bool kTmaStore, int kDiag = 0, bool kSplitN = false,
-          bool kGrouped = false, int kEpi = 0>
+          bool kGrouped = false, int kEpi = 0, bool kMcB = false, int kPipe = 0>
 static int launch_variant(const CUtensorMap& ta, const CUtensorMap& tb, const CMaps& tc, const GemmParams& p,
                           int workers, cudaStream_t st) {
   using C = Cfg<BLOCK_N, kCG>;
-  auto kern = fp8_blockwise_gemm_kernel<BLOCK_N, kStages, kCG, OutT, kTmaStore, kDiag, kSplitN, kGrouped, kEpi>;
+  auto kern = fp8_blockwise_gemm_kernel<BLOCK_N, kStages, kCG, OutT, kTmaStore, kDiag, kSplitN, kGrouped, kEpi, kMcB, kPipe>;
   constexpr int smem = kMaxDynSmem;
   (void)sizeof(C);
   static bool configured = false;   // per instantiation
@@ -1032,13 +1090,14 @@ static int launch_variant(const CUtensorMap& ta, const CUtensorMap& tb, const CM
   }
   cudaLaunchConfig_t cfg;
   memset(&cfg, 0, sizeof(cfg));
-  cfg.gridDim = dim3(unsigned(workers * kCG));
+  constexpr int kCl = kMcB ? 2 : kCG;
+  cfg.gridDim = dim3(unsigned(workers * kCl));
   cfg.blockDim = dim3(kNumThreads);
   cfg.dynamicSmemBytes = smem;
   cfg.stream = st;
   cudaLaunchAttribute attr[1];
   attr[0].id = cudaLaunchAttributeClusterDimension;
-  attr[0].val.clusterDim.x = kCG;
+  attr[0].val.clusterDim.x = kCl;
   attr[0].val.clusterDim.y = 1;
   attr[0].val.clusterDim.z = 1;
   cfg.attrs = attr;
@@ -1073,6 +1132,10 @@ static int launch_by_id(int v, const CUtensorMap& ta, const CUtensorMap& tb, con
     case 20: return launch_variant<256, 6, 2, OutT, true, 8>(ta, tb, tc, p, num_sms, st);
     case 21: return launch_variant<256, 6, 2, OutT, true, 9>(ta, tb, tc, p, num_sms, st);
     case 22: return launch_variant<256, 6, 2, OutT, true, 10>(ta, tb, tc, p, num_sms, st);
+    case 23: return launch_variant<256, 4, 1, OutT, true, 0, false, false, 0, true>(ta, tb, tc, p, num_sms, st);
+    case 24: return launch_variant<256, 6, 2, OutT, true, 0, false, false, 0, false, 1>(ta, tb, tc, p, num_sms, st);
+    case 25: return launch_variant<256, 6, 2, OutT, true, 0, true, false, 0, false, 1>(ta, tb, tc, p, num_sms, st);
+    case 26: return launch_variant<256, 4, 1, OutT, true, 0, false, false, 0, true, 1>(ta, tb, tc, p, num_sms, st);
     default: return SGLK_E_VARIANT;
   }
 }
@@ -1098,7 +1161,10 @@ static bool tma_store_ok(const void* C, int64_t ldc, int out_bytes) {
 
 static int pick_variant(int64_t M, int64_t N, int64_t K) {
   (void)K;
-  if (M > 128 && N >= 256) return 3;   // paired 256x256 tiles (one pair covers 256 rows)
+  // paired 256x256 tiles (one pair covers 256 rows), each K block issued as two 128-column MMA halves with their own
+  // hand-off barriers: a half's stage has three half-MMAs (768 clk) of slack before it is needed again instead of one
+  // whole MMA (512) — +5-10 % over the unsplit pair tile at every prefill shape measured (tools/session18.sh)
+  if (M > 128 && N >= 256) return 13;
   // M <= 128 (decode): one m-block; 128-wide tiles, balanced over the SMs by stream-K
   return 0;
 }
@@ -1230,7 +1296,7 @@ static int gemm_entry(const void* A, const void* B, const float* sa, const float
                             (reinterpret_cast<uintptr_t>(sa) & 15) == 0 && (reinterpret_cast<uintptr_t>(sb) & 15) == 0;
     const int64_t base = pl.stream_k ? pl.counter_bytes + pl.partial_bytes : kCounterAreaBytes;
     if (!vec_layout && pl.scale_bytes > 0 && workspace && workspace_bytes >= base + pl.scale_bytes &&
-        (reinterpret_cast<uintptr_t>(workspace) & 15) == 0 && variant < 15) {
+        (reinterpret_cast<uintptr_t>(workspace) & 15) == 0 && (variant < kFirstStampVariant || variant > kLastStampVariant)) {
       const int G = pl.num_k_blocks, NB = p.num_sb_cols;
       float* sa_t = reinterpret_cast<float*>(static_cast<char*>(workspace) + base);
       float* sb_t = sa_t + (int64_t(M) * G * 4 + 255) / 256 * 64;
@@ -1245,7 +1311,7 @@ static int gemm_entry(const void* A, const void* B, const float* sa, const float
     }
   }
   p.dbg = nullptr;
-  if (variant >= 15) {   // timestamps diagnostic: the stamps go to the start of the partials area of the workspace
+  if (variant >= kFirstStampVariant && variant <= kLastStampVariant) {   // timestamps diagnostic: the stamps go to the start of the partials area of the workspace
     if (!workspace || workspace_bytes < kCounterAreaBytes + 64 * 8 * 8) return SGLK_E_ARG;
     p.dbg = reinterpret_cast<long long*>(static_cast<char*>(workspace) + kCounterAreaBytes);
   }
@@ -1254,8 +1320,10 @@ static int gemm_entry(const void* A, const void* B, const float* sa, const float
   // ~20 clk per row (measured: M=1 ran 2x slower than M=128), so the A box is cut to round_up(M, 8) rows;
   // the MMA still reads 128 rows of smem, the stale ones only feed accumulator lanes that are never stored.
   const uint32_t a_rows = (v.cg == 1 && M < BLOCK_M) ? uint32_t((M + 7) / 8 * 8) : uint32_t(BLOCK_M);
-  const uint32_t b_bytes = uint32_t(v.block_n / v.cg) * BLOCK_K;
-  p.stage_tx_bytes = uint32_t(v.cg) * (a_rows * BLOCK_K + b_bytes);
+  // bytes of B in one CTA's stage / bytes its full barrier sees per stage (pair: both CTAs' loads on the leader's barrier;
+  // multicast-B: own A + own half of B + the peer's half)
+  const uint32_t b_bytes = uint32_t(v.mcb ? v.block_n : v.block_n / v.cg) * BLOCK_K;
+  p.stage_tx_bytes = v.mcb ? (a_rows * BLOCK_K + b_bytes) : uint32_t(v.cg) * (a_rows * BLOCK_K + b_bytes);
   p.a_slot_bytes = (a_rows * BLOCK_K + 1023u) & ~1023u;
   p.stage_bytes = p.a_slot_bytes + b_bytes;
   {
@@ -1277,7 +1345,7 @@ static int gemm_entry(const void* A, const void* B, const float* sa, const float
   if (mc_ptr && (!v.tma_store || (reinterpret_cast<uintptr_t>(mc_ptr) & 15) || N % 8 != 0 || ldc % 8 != 0)) return SGLK_E_STRIDE;
   if (!make_tmap_2d(&ta, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, A, uint64_t(M), uint64_t(K), uint64_t(lda), a_rows, BLOCK_K))
     return SGLK_E_DRIVER;
-  const bool split_b_boxes = (variant == 13 || variant == 16);   // pair + split-N: two 64-row boxes per CTA per stage
+  const bool split_b_boxes = (variant == 13 || variant == 16 || variant == 25);   // pair + split-N: two 64-row boxes per CTA per stage
   if (!make_tmap_2d(&tb, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, B, uint64_t(N), uint64_t(K), uint64_t(ldb),
                     uint32_t(v.block_n / v.cg / (split_b_boxes ? 2 : 1)), BLOCK_K))
     return SGLK_E_DRIVER;

@@ -119,6 +119,16 @@ __device__ __forceinline__ void tma_load_2d_pair(const CUtensorMap* m, uint32_t 
       ::"r"(dst), "l"(reinterpret_cast<uint64_t>(m)), "r"(bar), "r"(c0), "r"(c1), "l"(policy)
       : "memory");
 }
+// multicast variant: the tile lands at the same CTA-relative smem offset in every CTA of `cta_mask`, and each of
+// those CTAs' mbarrier (same CTA-relative offset) is credited with the bytes
+__device__ __forceinline__ void tma_load_2d_mcast(const CUtensorMap* m, uint32_t bar, uint32_t dst, int32_t c0, int32_t c1,
+                                                  uint16_t cta_mask, uint64_t policy) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes.multicast::cluster.L2::cache_hint"
+      " [%0], [%1, {%3, %4}], [%2], %5, %6;"
+      ::"r"(dst), "l"(reinterpret_cast<uint64_t>(m)), "r"(bar), "r"(c0), "r"(c1), "h"(cta_mask), "l"(policy)
+      : "memory");
+}
 __device__ __forceinline__ void tma_store_2d(const CUtensorMap* m, uint32_t src, int32_t c0, int32_t c1) {
   asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];"
                ::"l"(reinterpret_cast<uint64_t>(m)), "r"(src), "r"(c0), "r"(c1)
@@ -210,6 +220,12 @@ __device__ __forceinline__ void tc_commit(uint32_t bar) {
         ::"r"(bar), "h"(uint16_t(3))
         : "memory");
   }
+}
+
+// cta_group::1 commit whose arrive is multicast to the same barrier offset in every CTA of `cta_mask`
+__device__ __forceinline__ void tc_commit_mcast1(uint32_t bar, uint16_t cta_mask) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
+               ::"r"(bar), "h"(cta_mask) : "memory");
 }
 
 // 32 lanes x 32 consecutive 32-bit columns -> 32 registers per thread (thread i <- lane base+i)
