@@ -1,5 +1,5 @@
 #!/usr/bin/env python
-"""Tiny launcher for ncu captures: `ncu_target.py quant [M]` or `ncu_target.py gemm M N K [variant]`."""
+"""Tiny launcher for ncu captures: `ncu_target.py quant [M]`, `ncu_target.py tokenquant [M]` or `ncu_target.py gemm M N K [variant]`."""
 import os
 import sys
 
@@ -20,6 +20,13 @@ if what == "quant":
     s = sgl_kernel.create_per_token_group_quant_fp8_output_scale((m, 7168), dev, 128, col, col, False)
     for _ in range(3):
         sgl_kernel.sgl_per_token_group_quant_8bit(x, q, s, 128, 1e-10, -448.0, 448.0, enable_v2=False)
+elif what == "tokenquant":
+    m = int(sys.argv[2]) if len(sys.argv) > 2 else 32768
+    x = torch.randn(m, 7168, dtype=torch.bfloat16, device=dev)
+    q = torch.empty(m, 7168, dtype=torch.float8_e4m3fn, device=dev)
+    s = torch.zeros(m, device=dev)
+    for _ in range(3):
+        sgl_kernel.sgl_per_token_quant_fp8(x, q, s)
 else:
     M, N, K = (int(v) for v in sys.argv[2:5])
     v = int(sys.argv[5]) if len(sys.argv) > 5 else -1

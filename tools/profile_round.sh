@@ -19,3 +19,9 @@ $DCMD > gpurun_out/plain_decode.log 2>&1 && \
 ncu --set full --clock-control none --import-source on -k regex:fp8_blockwise_gemm -s 2 -c 1 -o gpurun_out/decode_$R $DCMD > gpurun_out/ncu_decode.log 2>&1
 tail -2 gpurun_out/ncu_decode.log
 ls -la gpurun_out | grep $R
+# per-token quant (sgl_per_token_quant_fp8): one full capture
+TCMD="python tools/ncu_target.py tokenquant 32768"
+$TCMD > gpurun_out/plain_tokenquant.log 2>&1 && \
+ncu --set full --clock-control none --import-source on -k regex:ptq_kernel -s 2 -c 1 -o gpurun_out/tokenquant_$R $TCMD > gpurun_out/ncu_tokenquant.log 2>&1
+tail -2 gpurun_out/ncu_tokenquant.log
+ls -la gpurun_out | grep $R

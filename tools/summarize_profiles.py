@@ -82,4 +82,5 @@ dump_launches()
 dump_kernel("gemm")
 dump_kernel("quant")
 dump_kernel("decode")
+dump_kernel("tokenquant")
 print(sorted(os.listdir(P)))
