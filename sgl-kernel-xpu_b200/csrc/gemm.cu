@@ -200,7 +200,7 @@ fp8_blockwise_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gr
   static_assert(!kSplitN || (BLOCK_N == 256 && (kDiag == 0 || kDiag == 4)), "split-N is for the 256-wide product tiles");
   static_assert(!kTmaStore || C::kCanTmaStore, "TMA-store epilogue needs >= 64 columns per warp");
   static_assert(!kGrouped || (kCG == 1 && !kTmaStore && kDiag == 0 && !kSplitN), "grouped mode: single-CTA tiles, predicated stores");
-  static_assert(kEpi == 0 || (BLOCK_N == 256 && kTmaStore && kDiag == 0 && !kSplitN && !kGrouped),
+  static_assert(kEpi == 0 || (BLOCK_N == 256 && kTmaStore && kDiag == 0 && !kGrouped),
                 "fused output quantisation: 256-wide tiles (one 128-column group per epilogue warp), TMA-store epilogue");
 
   extern __shared__ __align__(1024) uint8_t smem_raw[];
@@ -1144,9 +1144,9 @@ static int launch_by_id(int v, const CUtensorMap& ta, const CUtensorMap& tb, con
 template <typename OutT>
 static int launch_quant_epilogue(int v, int mode, const CUtensorMap& ta, const CUtensorMap& tb, const CMaps& tc,
                                  const GemmParams& p, int workers, cudaStream_t st) {
-  if (v == 3) {
-    return mode == 2 ? launch_variant<256, 6, 2, OutT, true, 0, false, false, 2>(ta, tb, tc, p, workers, st)
-                     : launch_variant<256, 6, 2, OutT, true, 0, false, false, 1>(ta, tb, tc, p, workers, st);
+  if (v == 13) {   // split-N pair tiles, like the plain GEMM's prefill default
+    return mode == 2 ? launch_variant<256, 6, 2, OutT, true, 0, true, false, 2>(ta, tb, tc, p, workers, st)
+                     : launch_variant<256, 6, 2, OutT, true, 0, true, false, 1>(ta, tb, tc, p, workers, st);
   }
   if (v == 2) {
     return mode == 2 ? launch_variant<256, 4, 1, OutT, true, 0, false, false, 2>(ta, tb, tc, p, workers, st)
@@ -1246,7 +1246,7 @@ static int gemm_entry(const void* A, const void* B, const float* sa, const float
     const int64_t nq = qo->silu_mul ? N / 2 : N;
     if (qo->ldq < nq || qo->ldq % 16 != 0 || (reinterpret_cast<uintptr_t>(qo->codes) & 15)) return SGLK_E_STRIDE;
     if (num_extra != 0 || mc_ptr) return SGLK_E_ARG;
-    variant = M > 128 ? 3 : 2;
+    variant = M > 128 ? 13 : 2;
     Cout = qo->codes; ldc = N;       // (placeholders for the shared checks below; C itself is never written)
   }
   if (!Cout) return SGLK_E_NULL;

@@ -332,7 +332,7 @@ def _gemm_quant(mat_a, mat_b, scales_a, scales_b, round_dtype, eps, fuse_silu_an
     with torch.cuda.device(mat_a.device):
         stream = _stream_ptr(mat_a)
         ws_ptr, ws_bytes = None, 0
-        need = lib.sglk_gemm_workspace_bytes(M, N, K, 3 if M > 128 else 2, 0)
+        need = lib.sglk_gemm_workspace_bytes(M, N, K, 13 if M > 128 else 2, 0)
         if need > 0:
             ws = _get_workspace(mat_a.device, stream, need)
             ws_ptr, ws_bytes = ws.data_ptr(), ws.numel()
