@@ -262,6 +262,11 @@ SGLK_API int sglk_gemm_pick_variant(int64_t M, int64_t N, int64_t K);
  * shape allows it (tests exercise the fixup on small shapes); -1: never.  Process-wide; returns the previous mode. */
 SGLK_API int sglk_debug_set_stream_k_mode(int mode);
 
+/* Tuning hook: m-blocks per rasterisation group of the dense GEMM (tiles of one group are walked n-major, so a group's
+ * A panels stay in L2 while B streams once per group).  0 (default): the built-in choice.  Results do not depend on
+ * it.  Process-wide; returns the previous value. */
+SGLK_API int sglk_debug_set_group_m(int group_m);
+
 /* Device self-check of the quant kernel's division scheme against __fdiv_rn over every 16-bit
  * numerator (numerator_dtype = SGLK_BF16 or SGLK_F16) for `num_scales` scales; adds the number of
  * differing e4m3 codes to *mismatches (device ptr). */

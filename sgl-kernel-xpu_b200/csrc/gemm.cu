@@ -1164,6 +1164,9 @@ static int pick_variant(int64_t M, int64_t N, int64_t K) {
   // paired 256x256 tiles (one pair covers 256 rows), each K block issued as two 128-column MMA halves with their own
   // hand-off barriers: a half's stage has three half-MMAs (768 clk) of slack before it is needed again instead of one
   // whole MMA (512) — +5-10 % over the unsplit pair tile at every prefill shape measured (tools/session18.sh)
+  // ... except a handful of wide tiles on a narrow weight (N=2112, 129 <= M <= 256: 9 pair tiles for 74 pairs):
+  // 128-wide single-CTA tiles give stream-K twice the units to balance (21.5 vs 26.7 us, tools/session23.sh)
+  if (M > 128 && M <= 256 && N < 4096) return 0;
   if (M > 128 && N >= 256) return 13;
   // M <= 128 (decode): one m-block; 128-wide tiles, balanced over the SMs by stream-K
   return 0;
@@ -1184,6 +1187,7 @@ struct Plan {
 // 1.3 waves of 128-wide tiles, N=2112: 17 tiles for 148 SMs); short-K prefill shapes (4096x7168x2048: 75.8 us
 // stream-K vs 67.6 us whole tiles) do not and stay on whole tiles.
 static int g_stream_k_mode = 0;   // sglk_debug_set_stream_k_mode: 0 cost model, 1 whenever possible, -1 never
+static int g_group_m = 0;         // sglk_debug_set_group_m: 0 = heuristic (pick_group_m), else m-blocks per raster group
 static Plan make_plan(int64_t M, int64_t N, int64_t K, int variant, int num_sms, bool have_ws) {
   Plan pl;
   pl.variant = variant;
@@ -1287,7 +1291,15 @@ static int gemm_entry(const void* A, const void* B, const float* sa, const float
   p.num_n_blocks = pl.num_n_blocks;
   p.num_k_blocks = pl.num_k_blocks;
   p.num_sb_cols = int32_t((N + 127) / 128);
-  p.group_m = 8;
+  // Rasterisation group: its A panels (group_m * tile_m * K bytes) must stay in L2 while B streams past once per group.
+  // ncu at 16384x18432x7168 (tools/session22.sh): DRAM reads 5.60 / 3.74 / 1.65 / 1.03 / 1.70 / 4.42 GB for groups of
+  // 2 / 4 / 8 / 16 / 32 / 64 m-blocks (algorithmic 0.25 GB) at equal speed within noise — ~32 MB of A is what one L2
+  // partition keeps; beyond that the panels evict each other.
+  {
+    int64_t gm = (int64_t(32) << 20) / (int64_t(BLOCK_M) * v.cg * K);
+    gm = gm < 4 ? 4 : (gm > 16 ? 16 : gm);
+    p.group_m = g_group_m > 0 ? g_group_m : int32_t(gm);
+  }
   p.stream_k = pl.stream_k;
   p.ws_counters = pl.stream_k ? static_cast<int32_t*>(workspace) : nullptr;
   p.ws_partials = pl.stream_k ? reinterpret_cast<float*>(static_cast<char*>(workspace) + pl.counter_bytes) : nullptr;
@@ -1483,6 +1495,12 @@ extern "C" int sglk_fp8_blockwise_scaled_mm_quant(const void* A, const void* B, 
 extern "C" int sglk_debug_set_stream_k_mode(int mode) {
   const int prev = sglk::g_stream_k_mode;
   sglk::g_stream_k_mode = mode > 0 ? 1 : (mode < 0 ? -1 : 0);
+  return prev;
+}
+
+extern "C" int sglk_debug_set_group_m(int group_m) {
+  const int prev = sglk::g_group_m;
+  sglk::g_group_m = group_m > 0 ? group_m : 0;
   return prev;
 }
 

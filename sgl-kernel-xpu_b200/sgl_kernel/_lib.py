@@ -49,6 +49,7 @@ SYMBOLS = {
     "sglk_gemm_pick_variant": (_i32, [_i64, _i64, _i64]),
     "sglk_debug_check_division": (_i32, [_vp, _i64, _i32, _vp, _vp]),
     "sglk_debug_set_stream_k_mode": (_i32, [_i32]),
+    "sglk_debug_set_group_m": (_i32, [_i32]),
 }
 
 _lib = None
