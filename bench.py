@@ -300,7 +300,10 @@ def main():
         x_host = torch.empty(M, K, dtype=torch.bfloat16).pin_memory()
         x_host.copy_(x)
         out_hosts = [torch.empty(M, n_loc, dtype=torch.bfloat16).pin_memory() for _ in range(2)]
-        runner = sgl_kernel.HostStreamedFp8Linear(layer, M)     # public host-buffer API: H2D / quant+GEMM / D2H overlapped
+        # public host-buffer API: H2D / quant+GEMM / D2H overlapped; N>1: every rank uploads M/g rows, quantises them and
+        # all-gathers codes + scales over NVLink instead of pushing g copies of x through the host's PCIe root
+        runner = (sgl_kernel.HostStreamedShardedFp8Linear(sharded, M) if world > 1
+                  else sgl_kernel.HostStreamedFp8Linear(layer, M))
         e2e_steps = max(4, min(args.steps, 12))
         for i in range(2):
             runner.submit(x_host, out_hosts[i & 1])
@@ -319,11 +322,15 @@ def main():
         e2e_ok = bool(torch.equal(out_hosts[(e2e_steps - 1) & 1][:64].to(dev), out[:64]))
         e2e = {"value": 2.0 * M * N * K / (float(te.item()) * 1e-3) / 1e12, "unit": "TFLOPS",
                "ms_per_step": float(te.item()), "steps": e2e_steps,
-               "h2d_bytes_per_step": int(x_host.numel() * 2 * world), "d2h_bytes_per_step": int(M * N * 2),
+               "h2d_bytes_per_step": int(x_host.numel() * 2), "d2h_bytes_per_step": int(M * N * 2),
                "matches_device_result": e2e_ok,
-               "note": "sgl_kernel.HostStreamedFp8Linear: pinned host x -> HBM, quant + GEMM ops, result panel -> pinned host, "
-                       "every step; the three phases of consecutive steps overlap on three streams; wall clock over "
-                       "all steps incl. final sync; bytes are whole-job (all ranks)"}
+               "note": ("sgl_kernel.HostStreamedFp8Linear: pinned host x -> HBM, quant + GEMM ops, result panel -> pinned host, "
+                        "every step; the three phases of consecutive steps overlap on three streams; wall clock over "
+                        "all steps incl. final sync; bytes are whole-job (all ranks)") if world == 1 else
+                       ("sgl_kernel.HostStreamedShardedFp8Linear: every rank uploads M/g rows of the pinned host x, quantises "
+                        "them, NCCL all-gathers codes + scales over NVLink, GEMMs its N/g panel and downloads it to pinned "
+                        "host memory, every step; phases of consecutive steps overlap on three streams; wall clock over all "
+                        "steps incl. final sync, max over ranks; bytes are whole-job (all ranks)")}
 
     if rank != 0:
         if world > 1:

@@ -22,7 +22,7 @@ from .linear import (
     per_token_group_quant_fp8,
 )
 from .moe import fp8_blockwise_scaled_grouped_mm
-from .sharded import ColumnShardedFp8Linear
+from .sharded import ColumnShardedFp8Linear, HostStreamedShardedFp8Linear
 
 __version__ = "0.11.0+b200"
 
@@ -40,4 +40,5 @@ __all__ = [
     "Fp8BlockLinear",
     "HostStreamedFp8Linear",
     "ColumnShardedFp8Linear",
+    "HostStreamedShardedFp8Linear",
 ]

@@ -105,3 +105,92 @@ class ColumnShardedFp8Linear:
         return self.gather(y) if gather_output else y
 
     __call__ = forward
+
+
+def row_chunk(m: int, world: int) -> int:
+    """Rows per rank when [M, K] activations are split for upload: equal chunks (all_gather_into_tensor needs
+    them equal), the last ranks' chunks may be partly or wholly beyond M."""
+    return -(m // -world) if m > 0 else 0
+
+
+def gather_row_chunks(buf: torch.Tensor, chunk_rows: int, rank: int, group=None) -> None:
+    """In-place all-gather of a row-chunked buffer: `buf` is [world*chunk_rows, ...] contiguous, this rank has
+    filled rows [rank*chunk_rows, (rank+1)*chunk_rows); afterwards every rank holds every chunk.  Bytes are
+    moved as uint8, so any dtype (e4m3 codes, fp32 scales) goes through NCCL/gloo unchanged."""
+    flat = buf.view(torch.uint8).reshape(-1)
+    per = flat.numel() // (buf.shape[0] // chunk_rows) if chunk_rows else 0
+    if per == 0:
+        return
+    dist.all_gather_into_tensor(flat, flat[rank * per : (rank + 1) * per], group=group)
+
+
+class HostStreamedShardedFp8Linear:
+    """Host-buffer entry point of the N-sharded layer: x_host [M, K] (pinned, the same batch on every rank) ->
+    this rank's [M, N/g] output panel in pinned host memory.
+
+    Uploading the whole batch on every rank would push g copies of x through the host's PCIe root and memory
+    (measured at 8 GPUs: 16 ms/step against 11.5 ms on one GPU).  Instead each rank uploads only rows
+    [r*ceil(M/g), (r+1)*ceil(M/g)), quantises them with the group-quant op straight into its slice of the full
+    [M, K] code / [M, K/128] scale buffers, and one in-place all-gather of codes and one of scales over NVLink
+    (1.03 bytes per element instead of 2 over PCIe) completes them on every rank; the local GEMM then produces
+    the rank's panel, which leaves over the rank's own PCIe link.  Quantisation is row-local, so the gathered
+    codes and scales are bit-identical to quantising the full batch on every rank.  Three streams and two
+    buffer sets overlap upload / compute+gather / download of consecutive batches as in HostStreamedFp8Linear."""
+
+    def __init__(self, sharded: ColumnShardedFp8Linear, max_tokens: int):
+        layer = sharded.local
+        dev = layer.weight_q.device
+        self.sh, self.layer = sharded, layer
+        self.world, self.rank, self.group = sharded.world, sharded.rank, sharded.group
+        k = layer.in_features
+        self.max_chunk = row_chunk(max_tokens, self.world)
+        rows = self.max_chunk * self.world
+        self.s_in, self.s_cmp, self.s_out = (torch.cuda.Stream(dev) for _ in range(3))
+        self.x_dev = [torch.empty((self.max_chunk, k), dtype=torch.bfloat16, device=dev) for _ in range(2)]
+        self.xq = [torch.empty((rows, k), dtype=torch.float8_e4m3fn, device=dev) for _ in range(2)]
+        self.xs = [torch.empty((rows, k // 128), dtype=torch.float32, device=dev) for _ in range(2)]
+        self.ev_in = [torch.cuda.Event() for _ in range(2)]
+        self.ev_cmp = [torch.cuda.Event() for _ in range(2)]
+        self.ev_out = [torch.cuda.Event() for _ in range(2)]
+        self.count = 0
+
+    def submit(self, x_host: torch.Tensor, y_host: torch.Tensor) -> None:
+        """Enqueue one batch (collective: every rank calls it with the same batch, in the same order)."""
+        from .gemm import sgl_per_token_group_quant_8bit
+
+        assert x_host.is_pinned() and y_host.is_pinned(), "host buffers must be pinned"
+        b = self.count & 1
+        m, k = x_host.shape
+        chunk = row_chunk(m, self.world)
+        assert chunk <= self.max_chunk
+        lo = min(self.rank * chunk, m)
+        hi = min(lo + chunk, m)
+        xq = self.xq[b][: chunk * self.world]
+        xs = self.xs[b][: chunk * self.world]
+        with torch.cuda.stream(self.s_in):
+            self.s_in.wait_event(self.ev_cmp[b])          # x_dev[b] no longer read by the quant of batch i-2
+            if hi > lo:
+                self.x_dev[b][: hi - lo].copy_(x_host[lo:hi], non_blocking=True)
+            self.ev_in[b].record(self.s_in)
+        with torch.cuda.stream(self.s_cmp):
+            self.s_cmp.wait_event(self.ev_in[b])
+            self.s_cmp.wait_event(self.ev_out[b])
+            if hi > lo:
+                sgl_per_token_group_quant_8bit(self.x_dev[b][: hi - lo], xq[lo:hi], xs[lo:hi], 128, 1e-10, -448.0, 448.0,
+                                               enable_v2=False)
+            if self.world > 1:
+                gather_row_chunks(xq, chunk, self.rank, self.group)
+                gather_row_chunks(xs, chunk, self.rank, self.group)
+            y = self.layer.forward_quantized(xq[:m], xs[:m])
+            self.ev_cmp[b].record(self.s_cmp)
+        with torch.cuda.stream(self.s_out):
+            self.s_out.wait_event(self.ev_cmp[b])
+            y.record_stream(self.s_out)
+            y_host.copy_(y, non_blocking=True)
+            self.ev_out[b].record(self.s_out)
+        self.count += 1
+
+    def synchronize(self) -> None:
+        self.s_out.synchronize()
+        self.s_cmp.synchronize()
+        self.s_in.synchronize()

@@ -290,3 +290,24 @@ def test_cuda_graph_capture():
     g.replay()
     torch.cuda.synchronize()
     check(out.cpu(), O.baseline_scaled_mm(a, b, sa, sb, torch.bfloat16))
+
+
+@pytest.mark.parametrize("M", [300, 1])
+def test_host_streamed_pipelines_match_device_result(M):
+    """The host-buffer entry points (bench.py's `e2e`): pinned x -> pinned y through the overlapped pipelines equals the
+    plain device-side layer call bit for bit, for several consecutive batches (buffer reuse), single rank."""
+    from sgl_kernel.sharded import ColumnShardedFp8Linear, HostStreamedShardedFp8Linear
+
+    x, wq_t, ws_t = O.make_linear_inputs(M, 512, 1024, seed=5)
+    layer = sgl_kernel.Fp8BlockLinear(wq_t.t().contiguous().to(DEV), ws_t.t().contiguous().to(DEV))
+    runners = [sgl_kernel.HostStreamedFp8Linear(layer, 512),
+               HostStreamedShardedFp8Linear(ColumnShardedFp8Linear(layer, 512), 512)]
+    xs = [(x.float() * (i + 1)).to(torch.bfloat16).pin_memory() for i in range(3)]
+    want = [layer(xh.to(DEV)).cpu() for xh in xs]
+    for runner in runners:
+        ys = [torch.empty(M, 512, dtype=torch.bfloat16).pin_memory() for _ in xs]
+        for xh, yh in zip(xs, ys):
+            runner.submit(xh, yh)
+        runner.synchronize()
+        for yh, w in zip(ys, want):
+            assert torch.equal(yh, w)

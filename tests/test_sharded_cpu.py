@@ -73,3 +73,48 @@ def test_column_sharded_linear_gloo(world, n):
         ret = mgr.dict()
         mp.spawn(_worker, args=(world, port, n, ret), nprocs=world, join=True)
         assert dict(ret) == {r: True for r in range(world)}
+
+
+# ---- row-chunked upload path of HostStreamedShardedFp8Linear: quantise own rows, gather codes + scales ----
+from sgl_kernel.sharded import gather_row_chunks, row_chunk  # noqa: E402
+
+
+@pytest.mark.parametrize("m,world", [(16384, 8), (6, 2), (7, 3), (1, 4), (0, 2)])
+def test_row_chunk_covers_m(m, world):
+    c = row_chunk(m, world)
+    assert c * world >= m and (m == 0 or (c - 1) * world < m)
+    covered = sum(max(0, min((r + 1) * c, m) - min(r * c, m)) for r in range(world))
+    assert covered == m
+
+
+def _row_worker(rank, world, port, m, ret):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        torch.manual_seed(3)
+        K = 256
+        x = torch.randn(m, K).to(torch.bfloat16)                  # the same batch on every rank
+        q_full, s_full = O.per_token_group_quant_fp8_ref(x, 128)
+        c = row_chunk(m, world)
+        xq = torch.zeros(c * world, K, dtype=torch.float8_e4m3fn)
+        xs = torch.zeros(c * world, K // 128, dtype=torch.float32)
+        lo, hi = min(rank * c, m), min(rank * c + c, m)
+        if hi > lo:
+            q, s = O.per_token_group_quant_fp8_ref(x[lo:hi], 128)
+            xq[lo:hi] = q
+            xs[lo:hi] = s
+        gather_row_chunks(xq, c, rank)
+        gather_row_chunks(xs, c, rank)
+        ok = torch.equal(xq[:m].view(torch.uint8), q_full.view(torch.uint8)) and torch.equal(xs[:m], s_full)
+        ret[rank] = bool(ok)
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world,m", [(2, 6), (3, 7), (2, 1)])
+def test_row_chunk_gather_equals_full_quant_gloo(world, m):
+    port = _free_port()
+    with mp.Manager() as mgr:
+        ret = mgr.dict()
+        mp.spawn(_row_worker, args=(world, port, m, ret), nprocs=world, join=True)
+        assert dict(ret) == {r: True for r in range(world)}
