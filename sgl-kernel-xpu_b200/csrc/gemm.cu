@@ -734,32 +734,70 @@ fp8_blockwise_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gr
         auto part_ptr = [&](int c) {
           return p.ws_partials + (int64_t(slot_of(c)) * (kCl * kNumEpiWarps) + int(cta_rank) * kNumEpiWarps + ew) * kWarpFloats;
         };
-        (void)first_segment;
         float4* mine = reinterpret_cast<float4*>(part_ptr(worker));
-        if (row_ok) {
-#pragma unroll
-          for (int j = 0; j < NC / 4; ++j)
-            __stcg(mine + j * 32 + lane, make_float4(accum[4 * j], accum[4 * j + 1], accum[4 * j + 2], accum[4 * j + 3]));
-        }
-        __threadfence();
-        __syncwarp();
         int32_t* cnt = p.ws_counters + int64_t(tile) * (kCl * kNumEpiWarps) + int(cta_rank) * kNumEpiWarps + ew;
-        int arrived = 0;
-        if (lane == 0) arrived = atomicAdd(cnt, 1);
-        arrived = __shfl_sync(0xFFFFFFFFu, arrived, 0);
-        write_out = arrived == c_last - c_first;                     // everyone else's partial is already visible
+        const int n_others = c_last - c_first;
+        // Narrow sub-tiles (NC <= 64: the decode tiles) first PEEK at the counter: the worker that holds a tile's first
+        // K blocks reaches it at the very end of its range, when everybody else has long arrived — it then knows it is
+        // the finisher, skips the store + fence + atomic round trips of its own partial (they sit fully exposed at the
+        // end of the kernel) and folds its registers in at its place in the CTA order.
+        constexpr bool kPeek = NC <= 64;
+        bool finisher = false;
+        // Only where it can succeed: the segment is the head of a tile (kb0 == 0) and not the worker's first piece of work,
+        // so the tile's other contributors started on it a whole range ago (N=24576: -2..-6 % GPU-side).  Workers whose one
+        // segment lies inside a single tile (N=2112: four contributors running concurrently) would only pay for the peek.
+        if (kPeek && !first_segment && kb0 == 0) {
+          int seen = 0;
+          if (lane == 0) seen = *reinterpret_cast<volatile int32_t*>(cnt);
+          finisher = __shfl_sync(0xFFFFFFFFu, seen, 0) == n_others;
+        }
+        if (!finisher) {
+          if (row_ok) {
+#pragma unroll
+            for (int j = 0; j < NC / 4; ++j)
+              __stcg(mine + j * 32 + lane, make_float4(accum[4 * j], accum[4 * j + 1], accum[4 * j + 2], accum[4 * j + 3]));
+          }
+          __threadfence();
+          __syncwarp();
+          int arrived = 0;
+          if (lane == 0) arrived = atomicAdd(cnt, 1);
+          arrived = __shfl_sync(0xFFFFFFFFu, arrived, 0);
+          finisher = arrived == n_others;                            // everyone else's partial is already visible
+        }
+        write_out = finisher;
         if (write_out) {
           __threadfence();
           if (lane == 0) *cnt = 0;                                   // leave the counters zeroed for the next launch
+          if constexpr (kPeek) {
+            float tot[NC];
 #pragma unroll
-          for (int i = 0; i < NC; ++i) accum[i] = 0.0f;
-          for (int c = c_first; c <= c_last; ++c) {                  // fixed order: bit-reproducible
-            const float4* src = reinterpret_cast<const float4*>(part_ptr(c));
-            if (row_ok) {
+            for (int i = 0; i < NC; ++i) tot[i] = 0.0f;
+            for (int c = c_first; c <= c_last; ++c) {                // fixed order: bit-reproducible
+              if (c == worker) {                                     // own partial: from registers (what a store + re-load would give)
 #pragma unroll
-              for (int j = 0; j < NC / 4; ++j) {
-                const float4 t = __ldcg(src + j * 32 + lane);
-                accum[4 * j] += t.x; accum[4 * j + 1] += t.y; accum[4 * j + 2] += t.z; accum[4 * j + 3] += t.w;
+                for (int i = 0; i < NC; ++i) tot[i] += accum[i];
+              } else if (row_ok) {
+                const float4* src = reinterpret_cast<const float4*>(part_ptr(c));
+#pragma unroll
+                for (int j = 0; j < NC / 4; ++j) {
+                  const float4 t = __ldcg(src + j * 32 + lane);
+                  tot[4 * j] += t.x; tot[4 * j + 1] += t.y; tot[4 * j + 2] += t.z; tot[4 * j + 3] += t.w;
+                }
+              }
+            }
+#pragma unroll
+            for (int i = 0; i < NC; ++i) accum[i] = tot[i];
+          } else {
+#pragma unroll
+            for (int i = 0; i < NC; ++i) accum[i] = 0.0f;
+            for (int c = c_first; c <= c_last; ++c) {                // fixed order: bit-reproducible
+              const float4* src = reinterpret_cast<const float4*>(part_ptr(c));
+              if (row_ok) {
+#pragma unroll
+                for (int j = 0; j < NC / 4; ++j) {
+                  const float4 t = __ldcg(src + j * 32 + lane);
+                  accum[4 * j] += t.x; accum[4 * j + 1] += t.y; accum[4 * j + 2] += t.z; accum[4 * j + 3] += t.w;
+                }
               }
             }
           }
