@@ -737,21 +737,20 @@ fp8_blockwise_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gr
         float4* mine = reinterpret_cast<float4*>(part_ptr(worker));
         int32_t* cnt = p.ws_counters + int64_t(tile) * (kCl * kNumEpiWarps) + int(cta_rank) * kNumEpiWarps + ew;
         const int n_others = c_last - c_first;
-        // Narrow sub-tiles (NC <= 64: the decode tiles) first PEEK at the counter: the worker that holds a tile's first
-        // K blocks reaches it at the very end of its range, when everybody else has long arrived — it then knows it is
-        // the finisher, skips the store + fence + atomic round trips of its own partial (they sit fully exposed at the
-        // end of the kernel) and folds its registers in at its place in the CTA order.
-        constexpr bool kPeek = NC <= 64;
-        bool finisher = false;
-        // Only where it can succeed: the segment is the head of a tile (kb0 == 0) and not the worker's first piece of work,
-        // so the tile's other contributors started on it a whole range ago (N=24576: -2..-6 % GPU-side).  Workers whose one
-        // segment lies inside a single tile (N=2112: four contributors running concurrently) would only pay for the peek.
-        if (kPeek && !first_segment && kb0 == 0) {
+        // PEEK at the counter first where that can succeed: the worker that holds a tile's first K blocks (kb0 == 0) reaches
+        // it at the very end of its range, when everybody else has long arrived — it then knows it is the finisher, skips
+        // the store + fence + atomic round trips of its own partial (they sit fully exposed at the end of the kernel) and,
+        // being the first contributor in CTA order, simply adds the others to its registers in order (same bits as
+        // 0 + own + others).  Not for a worker's first piece of work: contributors that start together (N=2112: four per
+        // tile, one segment each) would only pay for the peek.  N=24576 decode: -2..-8 % GPU-side (tools/session30.sh).
+        bool peeked = false;
+        if (!first_segment && kb0 == 0) {
           int seen = 0;
           if (lane == 0) seen = *reinterpret_cast<volatile int32_t*>(cnt);
-          finisher = __shfl_sync(0xFFFFFFFFu, seen, 0) == n_others;
+          peeked = __shfl_sync(0xFFFFFFFFu, seen, 0) == n_others;
         }
-        if (!finisher) {
+        bool finisher = peeked;
+        if (!peeked) {
           if (row_ok) {
 #pragma unroll
             for (int j = 0; j < NC / 4; ++j)
@@ -768,36 +767,17 @@ fp8_blockwise_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gr
         if (write_out) {
           __threadfence();
           if (lane == 0) *cnt = 0;                                   // leave the counters zeroed for the next launch
-          if constexpr (kPeek) {
-            float tot[NC];
+          // fixed order (bit-reproducible): 0 + partial(c_first) + partial(c_first + 1) + ...; after a successful peek
+          // this worker IS c_first and its partial is still in registers
 #pragma unroll
-            for (int i = 0; i < NC; ++i) tot[i] = 0.0f;
-            for (int c = c_first; c <= c_last; ++c) {                // fixed order: bit-reproducible
-              if (c == worker) {                                     // own partial: from registers (what a store + re-load would give)
+          for (int i = 0; i < NC; ++i) accum[i] = peeked ? 0.0f + accum[i] : 0.0f;
+          for (int c = peeked ? c_first + 1 : c_first; c <= c_last; ++c) {
+            const float4* src = reinterpret_cast<const float4*>(part_ptr(c));
+            if (row_ok) {
 #pragma unroll
-                for (int i = 0; i < NC; ++i) tot[i] += accum[i];
-              } else if (row_ok) {
-                const float4* src = reinterpret_cast<const float4*>(part_ptr(c));
-#pragma unroll
-                for (int j = 0; j < NC / 4; ++j) {
-                  const float4 t = __ldcg(src + j * 32 + lane);
-                  tot[4 * j] += t.x; tot[4 * j + 1] += t.y; tot[4 * j + 2] += t.z; tot[4 * j + 3] += t.w;
-                }
-              }
-            }
-#pragma unroll
-            for (int i = 0; i < NC; ++i) accum[i] = tot[i];
-          } else {
-#pragma unroll
-            for (int i = 0; i < NC; ++i) accum[i] = 0.0f;
-            for (int c = c_first; c <= c_last; ++c) {                // fixed order: bit-reproducible
-              const float4* src = reinterpret_cast<const float4*>(part_ptr(c));
-              if (row_ok) {
-#pragma unroll
-                for (int j = 0; j < NC / 4; ++j) {
-                  const float4 t = __ldcg(src + j * 32 + lane);
-                  accum[4 * j] += t.x; accum[4 * j + 1] += t.y; accum[4 * j + 2] += t.z; accum[4 * j + 3] += t.w;
-                }
+              for (int j = 0; j < NC / 4; ++j) {
+                const float4 t = __ldcg(src + j * 32 + lane);
+                accum[4 * j] += t.x; accum[4 * j + 1] += t.y; accum[4 * j + 2] += t.z; accum[4 * j + 3] += t.w;
               }
             }
           }
