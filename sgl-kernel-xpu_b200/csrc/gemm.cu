@@ -573,7 +573,8 @@ fp8_blockwise_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gr
           for (int i = 0; i < 32; i += 2) ptx::fma2(accum[c * 32 + i], accum[c * 32 + i + 1], buf[i], buf[i + 1], s);
         };
         auto promote2 = [&](const float s, const bool more, const bool fetch = false) {
-          static_assert(kPipe == 0 || NCH == 4, "paired chunk loads: 128 columns per epilogue warp");
+          static_assert(kPipe != 1 || NCH == 4, "paired chunk loads: 128 columns per epilogue warp");
+          static_assert(kPipe != 2 || NCH == 2, "whole-share staging: 64 columns per epilogue warp");
           ptx::tmem_ld_wait(v[0]);
           ptx::tmem_ld_wait(v[1]);
           fma_chunk(0, v[0], s);
@@ -601,8 +602,34 @@ fp8_blockwise_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gr
           fma_chunk(3, v[1], s);
           if (more) ptx::tmem_ld_32x32(taddr + 32u, v[1]);
         };
+        // kPipe == 2 (128-wide tiles: 64 columns per epilogue warp = both staging buffers): the WHOLE share of the K block
+        // is parked in registers, the accumulator stage goes back to the MMA issuer at once and all FMAs come after —
+        // the order the diagnostics say costs nothing (hand-back first, FMAs after).  Entry state: both chunks in flight.
+        auto promote3 = [&](const float s, const bool more, const bool fetch = false) {
+          ptx::tmem_ld_wait(v[0]);
+          ptx::tmem_ld_wait(v[1]);
+          release_stage();
+          bool ready = false;
+          if (more) {
+            taddr = stage_addr();
+            ready = ptx::mbar_try_wait(tfull_bar(acc * kHalves + hb), acc_phase);
+          }
+          if (fetch) {
+            a_nx = __ldg(sa4n);
+            b_nx = __ldg(sb4n);
+          }
+          fma_chunk(0, v[0], s);
+          if (more) {
+            if (!ready) ptx::mbar_wait(tfull_bar(acc * kHalves + hb), acc_phase);
+            ptx::tc_fence_after();
+            ptx::tmem_ld_32x32(taddr, v[0]);
+          }
+          fma_chunk(1, v[1], s);
+          if (more) ptx::tmem_ld_32x32(taddr + 32u, v[1]);
+        };
         auto promote = [&](const float s, const bool more, const bool fetch = false) {
           if constexpr (kPipe == 1) { promote2(s, more, fetch); return; }
+          if constexpr (kPipe == 2) { promote3(s, more, fetch); return; }
           const bool stamp = (kDiag == 4 || kDiag >= 6) && blockIdx.x == 0 && ew == 0 && lane == 0 && dbg_kb < 64 && tile == worker;
 #pragma unroll
           for (int c = 0; c < NCH; ++c) {
@@ -674,7 +701,7 @@ fp8_blockwise_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gr
           ptx::tc_fence_after();
           taddr = stage_addr();
           ptx::tmem_ld_32x32(taddr, v[0]);
-          if constexpr (kPipe == 1) ptx::tmem_ld_32x32(taddr + 32u, v[1]);
+          if constexpr (kPipe >= 1) ptx::tmem_ld_32x32(taddr + 32u, v[1]);
           if constexpr (kDiag == 7 || kDiag == 8) {     // diagnostic: FMAs on two chunks fetched once, no tcgen05.ld in the loop
             ptx::tmem_ld_32x32(taddr + 32u, v[1]);
             ptx::tmem_ld_wait(v[0]);
@@ -697,7 +724,7 @@ fp8_blockwise_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gr
           ptx::tc_fence_after();
           taddr = stage_addr();
           ptx::tmem_ld_32x32(taddr, v[0]);
-          if constexpr (kPipe == 1) ptx::tmem_ld_32x32(taddr + 32u, v[1]);
+          if constexpr (kPipe >= 1) ptx::tmem_ld_32x32(taddr + 32u, v[1]);
           for (int kb = kb0; kb < kb1; ++kb) promote(staged_scale(), kb + 1 < kb1);
           ptx::cp_async_wait<0>();
         }
@@ -1086,6 +1113,7 @@ static const Variant kVariants[] = {
     {"n256_s6_cta2_tma_pairld", 256, 6, 2, true},         // paired tiles, chunk loads issued in pairs
     {"n256_s6_cta2_tma_splitn_pairld", 256, 6, 2, true},
     {"n256_s4_cl2_mcb_tma_pairld", 256, 4, 2, true, true},
+    {"n128_s8_cta2_tma_earlyrel", 128, 8, 2, true},       // 256x128 pair tiles, whole K-block share staged, hand-back before the FMAs
 };
 constexpr int kFirstStampVariant = 15, kLastStampVariant = 22;
 constexpr int kNumVariants = int(sizeof(kVariants) / sizeof(kVariants[0]));
@@ -1154,6 +1182,7 @@ static int launch_by_id(int v, const CUtensorMap& ta, const CUtensorMap& tb, con
     case 24: return launch_variant<256, 6, 2, OutT, true, 0, false, false, 0, false, 1>(ta, tb, tc, p, num_sms, st);
     case 25: return launch_variant<256, 6, 2, OutT, true, 0, true, false, 0, false, 1>(ta, tb, tc, p, num_sms, st);
     case 26: return launch_variant<256, 4, 1, OutT, true, 0, false, false, 0, true, 1>(ta, tb, tc, p, num_sms, st);
+    case 27: return launch_variant<128, 8, 2, OutT, true, 0, false, false, 0, false, 2>(ta, tb, tc, p, num_sms, st);
     default: return SGLK_E_VARIANT;
   }
 }

@@ -20,10 +20,11 @@ else:
     sb = torch.randn(K // 128, -(N // -128), device=dev) * 1e-3
 REPEAT = int(os.environ.get('REPEAT', '1'))   # launches inside one timed region (reported time is the total)
 SK = os.environ.get("NOWS", "0") != "1"   # NOWS=1: no workspace (no stream-K, no scale re-layout)
+NUM_SMS = int(os.environ.get('NUM_SMS', '0'))   # restrict the persistent grid (per-SM efficiency without L2 / power limits)
 flush = torch.zeros(256 << 20, dtype=torch.uint8, device=dev).view(torch.int64)
 times = {v: [] for v in variants}
 for v in variants:
-    _ops._gemm(a, bt.t(), sa, sb, torch.bfloat16, v, 0, SK)
+    _ops._gemm(a, bt.t(), sa, sb, torch.bfloat16, v, NUM_SMS, SK)
 torch.cuda.synchronize()
 for r in range(rounds + 2):
     for v in variants:
@@ -32,7 +33,7 @@ for r in range(rounds + 2):
             flush.sum() if os.environ.get('NOFLUSH', '0') != '1' else torch.cuda._sleep(200000)
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             e0.record()
-            for _ in range(REPEAT): _ops._gemm(a, bt.t(), sa, sb, torch.bfloat16, v, 0, SK)
+            for _ in range(REPEAT): _ops._gemm(a, bt.t(), sa, sb, torch.bfloat16, v, NUM_SMS, SK)
             e1.record(); e1.synchronize()
             if r >= 2:
                 times[v].append(e0.elapsed_time(e1))
