@@ -55,7 +55,7 @@ SHAPES = [(1, 128, 512), (5, 512, 1024), (127, 256, 512), (128, 128, 7168), (129
           (512, 2112, 1024), (1024, 1024, 512), (64, 4096, 128)]
 
 
-@pytest.mark.parametrize("variant", list(range(7)) + [13, 14, 23, 24, 25, 26, 27])
+@pytest.mark.parametrize("variant", list(range(7)) + [13, 14, 23, 24, 25, 26, 27, 29])
 @pytest.mark.parametrize("M,N,K", SHAPES)
 def test_every_variant(variant, M, N, K):
     if variant >= n_variants():
@@ -196,7 +196,7 @@ STREAMK = [(1, 2112, 7168), (16, 24576, 7168), (64, 2112, 7168), (130, 4096, 204
 
 
 @pytest.mark.parametrize("M,N,K", STREAMK)
-@pytest.mark.parametrize("variant", [-1, 0, 2, 3, 5, 6, 13, 14, 23, 25, 27])
+@pytest.mark.parametrize("variant", [-1, 0, 2, 3, 5, 6, 13, 14, 23, 25, 27, 29])
 def test_stream_k_matches_whole_tiles_and_oracle(M, N, K, variant, force_stream_k):
     """Stream-K scheduling (tiles cut across CTAs, summed through the workspace by the last arriver)
     gives the oracle's answer, is bit-reproducible, and leaves its counters zeroed for the next launch."""
