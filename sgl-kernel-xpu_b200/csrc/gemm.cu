@@ -17,6 +17,7 @@
 //     own 128 rows of A and half of the B tile; the leader CTA issues the MMAs for both.
 //   * C leaves through per-warp swizzled smem boxes and TMA stores (coalesced, clipped at M/N
 //     edges by the tensor map); a plain predicated store path covers unaligned ldc.
+#include <cstdlib>
 #include <cuda.h>
 #include <cuda_bf16.h>
 #include <cuda_fp16.h>
@@ -1216,7 +1217,13 @@ static bool tma_store_ok(const void* C, int64_t ldc, int out_bytes) {
   return (reinterpret_cast<uintptr_t>(C) & 15) == 0 && (ldc * out_bytes) % 16 == 0;
 }
 
-static int g_prefill_variant = 13;   // 13 validated by the whole GPU suite; 29 (two staging boxes) measured +1-3 %, see tools/session38.sh
+// 13 validated by the whole GPU suite; 29 (two staging boxes) measured +1-3 %, see tools/session38.sh.  The environment
+// variable SGLK_PREFILL_VARIANT=13|29 (read once) selects between them for validation runs.
+static int init_prefill_variant() {
+  const char* e = getenv("SGLK_PREFILL_VARIANT");
+  return (e && e[0] == '2' && e[1] == '9' && e[2] == 0) ? 29 : 13;
+}
+static int g_prefill_variant = init_prefill_variant();
 static int pick_variant(int64_t M, int64_t N, int64_t K) {
   (void)K;
   // paired 256x256 tiles (one pair covers 256 rows), each K block issued as two 128-column MMA halves with their own
