@@ -1217,11 +1217,12 @@ static bool tma_store_ok(const void* C, int64_t ldc, int out_bytes) {
   return (reinterpret_cast<uintptr_t>(C) & 15) == 0 && (ldc * out_bytes) % 16 == 0;
 }
 
-// 13 validated by the whole GPU suite; 29 (two staging boxes) measured +1-3 %, see tools/session38.sh.  The environment
-// variable SGLK_PREFILL_VARIANT=13|29 (read once) selects between them for validation runs.
+// 29 (split-N pair tiles, two staging boxes per epilogue warp, 5-stage ring): +1-3 % over 13 at every prefill shape
+// (tools/session38.sh), whole GPU suite green on it (tools/session39.sh: 632 passed).  SGLK_PREFILL_VARIANT=13 (read
+// once) selects the single-box 6-stage form for A/B runs.
 static int init_prefill_variant() {
   const char* e = getenv("SGLK_PREFILL_VARIANT");
-  return (e && e[0] == '2' && e[1] == '9' && e[2] == 0) ? 29 : 13;
+  return (e && e[0] == '1' && e[1] == '3' && e[2] == 0) ? 13 : 29;
 }
 static int g_prefill_variant = init_prefill_variant();
 static int pick_variant(int64_t M, int64_t N, int64_t K) {
