@@ -29,7 +29,8 @@ WORKLOAD = "dsv3_dense_mlp_prefill_M16384_N18432_K7168_group128"
 METRIC = "FP8 blockwise GEMM TFLOPS (% dense-FP8 peak); group-quant GB/s (% HBM)"
 # dram__bytes_read.sum + dram__bytes_write.sum per launch from the `ncu --set full` captures of this command
 # (profiles/r01d_gemm_ncu_metrics.csv, profiles/r01d_quant_ncu_metrics.csv); algorithmic: 853 MB / 356 MB
-# (GEMM: 2.41 GB before the rasterisation group went from 8 to 16 m-blocks, profiles/r01b_*)
+# (GEMM: 2.41 GB before the rasterisation group went from 8 to 16 m-blocks, profiles/r01b_*; the r01d capture is of
+# variant 13 — the default since, 29, has the same tiles, ring contents and rasterisation, only a second staging box)
 GEMM_DRAM_TRAFFIC_BYTES = 1_164_657_000 + 590_170_112
 QUANT_DRAM_TRAFFIC_BYTES = 234_919_936 + 66_678_272
 FP8_NOMINAL_TFLOPS = 4500.0
