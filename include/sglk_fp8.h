@@ -30,7 +30,7 @@
 extern "C" {
 #endif
 
-#define SGLK_ABI_VERSION 1
+#define SGLK_ABI_VERSION 2
 
 #if defined(__GNUC__)
 #define SGLK_API __attribute__((visibility("default")))
@@ -165,10 +165,22 @@ SGLK_API int sglk_fp8_blockwise_scaled_mm(const void* A, const void* B, const fl
                                  int64_t sb_stride_k, int64_t sb_stride_n, int out_dtype,
                                  void* stream);
 
+/* flags of the _ex / _quant entry points and of sglk_gemm_workspace_bytes (0 = defaults).  They change scheduling only,
+ * never which result is computed; there is no process-wide state in the library. */
+enum {
+  SGLK_GEMM_STREAMK_AUTO = 0,   /* cost model decides whether tiles are cut across CTAs (needs a workspace)          */
+  SGLK_GEMM_STREAMK_FORCE = 1,  /* cut whenever the shape allows it (tests exercise the fix-up on small shapes)      */
+  SGLK_GEMM_STREAMK_NEVER = 2,  /* whole tiles only                                                                 */
+  SGLK_GEMM_GROUP_M_SHIFT = 8,  /* bits 8..15: m-blocks per rasterisation group of the prefill kernel, 0 = built-in */
+  SGLK_GEMM_SPLIT_SHIFT = 16    /* bits 16..23: decode kernel, workers per tile when there are fewer tiles than SMs, 0 = built-in */
+};
+
 /* Same, with an explicit kernel variant (tile shape / CTA pairing) for tests and tuning, and an
  * optional device workspace that enables stream-K scheduling (decode shapes, ragged last waves):
- * variant = -1 selects the heuristic used by sglk_fp8_blockwise_scaled_mm;
- * num_sms <= 0 uses every SM of the current device;
+ * variant = -1 selects the heuristic used by sglk_fp8_blockwise_scaled_mm; ids for which
+ * sglk_gemm_variant_is_product() is 0 are laboratory variants that exist only in the diagnostics
+ * build (libsglk_diag.so, -DSGLK_DIAG) — the product library answers SGLK_E_VARIANT for them;
+ * num_sms <= 0 uses every SM of the current device; flags: SGLK_GEMM_* above;
  * workspace: >= sglk_gemm_workspace_bytes(...) bytes, 16-byte aligned, whose first MiB (the tile
  * counters) is ZERO on entry — the kernel leaves it zero, so one zero-initialised buffer can be
  * reused by consecutive launches (of any shape) on the same stream.  NULL disables stream-K. */
@@ -176,7 +188,7 @@ SGLK_API int sglk_fp8_blockwise_scaled_mm_ex(const void* A, const void* B, const
                                     void* C, int64_t M, int64_t N, int64_t K, int64_t lda,
                                     int64_t ldb, int64_t ldc, int64_t sa_stride_m,
                                     int64_t sa_stride_k, int64_t sb_stride_k, int64_t sb_stride_n,
-                                    int out_dtype, int variant, int num_sms, void* workspace,
+                                    int out_dtype, int variant, int num_sms, int flags, void* workspace,
                                     int64_t workspace_bytes, void* stream);
 
 /*
@@ -199,7 +211,7 @@ SGLK_API int sglk_fp8_blockwise_scaled_mm_quant(const void* A, const void* B, co
                                        int64_t ldb, int64_t ldq, int64_t sa_stride_m, int64_t sa_stride_k,
                                        int64_t sb_stride_k, int64_t sb_stride_n, int64_t os_stride_m,
                                        int64_t os_stride_g, int round_dtype, float eps, int silu_mul, int num_sms,
-                                       void* workspace, int64_t workspace_bytes, void* stream);
+                                       int flags, void* workspace, int64_t workspace_bytes, void* stream);
 
 /*
  * Fused GEMM -> all-gather for the column-(N-)sharded linear (no reference counterpart: the reference
@@ -250,28 +262,21 @@ SGLK_API int64_t sglk_grouped_mm_workspace_bytes(int64_t num_experts, int64_t to
 /* bytes of workspace the call above can make use of (0: none): [1 MiB tile counters][stream-K partials, if the
  * scheduler would cut tiles][K-block-contiguous copies of sa / sb, for prefill-sized problems whose scales are not
  * already laid out that way] */
-SGLK_API int64_t sglk_gemm_workspace_bytes(int64_t M, int64_t N, int64_t K, int variant, int num_sms);
+SGLK_API int64_t sglk_gemm_workspace_bytes(int64_t M, int64_t N, int64_t K, int variant, int num_sms, int flags);
 
-/* number of GEMM variants compiled in, and a printable name for each ("" if out of range) */
+/* number of GEMM variant ids, a printable name for each ("" if out of range), and whether the id is a product
+ * variant (1) or a laboratory one that only the diagnostics build can launch (0) */
 SGLK_API int sglk_gemm_num_variants(void);
 SGLK_API const char* sglk_gemm_variant_name(int variant);
-/* the variant the heuristic would pick for a problem */
+SGLK_API int sglk_gemm_variant_is_product(int variant);
+/* the variant the heuristic would pick for a problem with a plain [M, N] output */
 SGLK_API int sglk_gemm_pick_variant(int64_t M, int64_t N, int64_t K);
-
-/* Test hook: how the GEMM decides on stream-K when it has a workspace.  0 (default): cost model; 1: whenever the
- * shape allows it (tests exercise the fixup on small shapes); -1: never.  Process-wide; returns the previous mode. */
-SGLK_API int sglk_debug_set_stream_k_mode(int mode);
-
-/* Tuning hook: m-blocks per rasterisation group of the dense GEMM (tiles of one group are walked n-major, so a group's
- * A panels stay in L2 while B streams once per group).  0 (default): the built-in choice.  Results do not depend on
- * it.  Process-wide; returns the previous value. */
-SGLK_API int sglk_debug_set_group_m(int group_m);
 
 /* Device self-check of the quant kernel's division scheme against __fdiv_rn over every 16-bit
  * numerator (numerator_dtype = SGLK_BF16 or SGLK_F16) for `num_scales` scales; adds the number of
  * differing e4m3 codes to *mismatches (device ptr). */
-SGLK_API int sglk_debug_check_division(const float* scales, int64_t num_scales, int numerator_dtype,
-                              unsigned long long* mismatches, void* stream);
+SGLK_API int sglk_selftest_division(const float* scales, int64_t num_scales, int numerator_dtype,
+                           unsigned long long* mismatches, void* stream);
 
 #ifdef __cplusplus
 }

@@ -17,7 +17,6 @@
 //     own 128 rows of A and half of the B tile; the leader CTA issues the MMAs for both.
 //   * C leaves through per-warp swizzled smem boxes and TMA stores (coalesced, clipped at M/N
 //     edges by the tensor map); a plain predicated store path covers unaligned ldc.
-#include <cstdlib>
 #include <cuda.h>
 #include <cuda_bf16.h>
 #include <cuda_fp16.h>
@@ -25,23 +24,18 @@
 #include <stdint.h>
 #include <string.h>
 
+#include <atomic>
 #include <mutex>
 
-#include "../../include/sglk_fp8.h"
-#include "common.cuh"
-#include "ptx.cuh"
+#include "gemm_common.cuh"
 #include "quant_kernel.cuh"   // div_pair / silu_mul: the fused output quantisation shares the quant op's arithmetic
 
 namespace sglk {
 
-constexpr int BLOCK_M = 128;   // rows per CTA (TMEM lanes)
-constexpr int BLOCK_K = 128;   // one scale block; 128 B of e4m3 = one 128B-swizzle atom row
-constexpr int UMMA_K = 32;     // K per tcgen05.mma for 8-bit operands
 constexpr int kNumEpiWarps = 8;
 constexpr int kNumThreads = 128 + kNumEpiWarps * 32;   // 4 control warps + 8 epilogue warps
 constexpr int kStoreBoxCols = 64;                      // bf16 columns per TMA store box (128 B)
 constexpr int kMaxStages = 16;                         // barrier slots reserved for the smem ring
-constexpr int kMaxDynSmem = 232448;                    // 227 KB
 constexpr int kSmemOverhead = 1024 + 2048;             // barriers + sb slots (1 KB), per-thread sa slots (2 KB); base is 1024-aligned
 
 struct GemmParams {
@@ -134,35 +128,6 @@ struct Cfg {
   static constexpr bool kCanTmaStore = (NC % kStoreBoxCols) == 0;
   static_assert((TMEM_COLS & (TMEM_COLS - 1)) == 0 && TMEM_COLS >= 32 && TMEM_COLS <= 512, "TMEM columns");
 };
-
-// K-major, 128-byte-swizzled operand tile: 8-row x 128-B atoms, 1024 B apart (SBO); LBO unused.
-__device__ __forceinline__ uint64_t make_smem_desc(uint32_t smem_addr) {
-  uint64_t d = 0;
-  d |= uint64_t((smem_addr & 0x3FFFFu) >> 4);        // start address      bits [0,14)
-  d |= uint64_t(0) << 16;                            // leading byte offset bits [16,30) (ignored)
-  d |= uint64_t(1024 >> 4) << 32;                    // stride byte offset  bits [32,46)
-  d |= uint64_t(1) << 46;                            // descriptor version (sm_100)
-  d |= uint64_t(2) << 61;                            // SWIZZLE_128B
-  return d;
-}
-// kind::f8f6f4, A = B = e4m3, D = f32, both K-major, dense
-__host__ __device__ constexpr uint32_t make_idesc(int umma_m, int umma_n) {
-  return (1u << 4)                        // D format f32
-       | (0u << 7) | (0u << 10)           // A, B format e4m3
-       | (0u << 15) | (0u << 16)          // A, B K-major
-       | (uint32_t(umma_n >> 3) << 17)
-       | (uint32_t(umma_m >> 4) << 24);
-}
-
-template <typename OutT> __device__ __forceinline__ uint32_t pack2(float a, float b);
-template <> __device__ __forceinline__ uint32_t pack2<__nv_bfloat16>(float a, float b) {
-  const __nv_bfloat162 v = __floats2bfloat162_rn(a, b);
-  return *reinterpret_cast<const uint32_t*>(&v);
-}
-template <> __device__ __forceinline__ uint32_t pack2<__half>(float a, float b) {
-  const __half2 v = __floats2half2_rn(a, b);
-  return *reinterpret_cast<const uint32_t*>(&v);
-}
 
 // tile index -> (m_block, n_block): groups of `group_m` m-blocks are walked n-major so that the
 // CTAs resident at one time share a few B panels and `group_m` A panels in L2.
@@ -787,10 +752,14 @@ fp8_blockwise_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gr
             for (int j = 0; j < NC / 4; ++j)
               __stcg(mine + j * 32 + lane, make_float4(accum[4 * j], accum[4 * j + 1], accum[4 * j + 2], accum[4 * j + 3]));
           }
-          __threadfence();
+          // release pattern: every lane's partial is ordered before lane 0 by the warp barrier, lane 0's (cumulative)
+          // fence orders them before its counter increment
           __syncwarp();
           int arrived = 0;
-          if (lane == 0) arrived = atomicAdd(cnt, 1);
+          if (lane == 0) {
+            __threadfence();
+            arrived = atomicAdd(cnt, 1);
+          }
           arrived = __shfl_sync(0xFFFFFFFFu, arrived, 0);
           finisher = arrived == n_others;                            // everyone else's partial is already visible
         }
@@ -1054,80 +1023,51 @@ build_group_tiles_kernel(const int32_t* __restrict__ offsets, const int32_t* __r
 // --------------------------------------------------------------------------------------------
 // host side
 // --------------------------------------------------------------------------------------------
-typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
-                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
-                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
-
-static EncodeTiledFn get_encode_fn() {
-  static EncodeTiledFn fn = nullptr;
-  static std::once_flag once;
-  std::call_once(once, [] {
-    void* sym = nullptr;
-    cudaDriverEntryPointQueryResult qres;
-    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &sym, cudaEnableDefault, &qres) == cudaSuccess &&
-        qres == cudaDriverEntryPointSuccess)
-      fn = reinterpret_cast<EncodeTiledFn>(sym);
-  });
-  return fn;
-}
-
-// 2-D row-major tensor [rows, cols] with `ld` elements between rows; box = [box_rows, box_cols]
-static bool make_tmap_2d(CUtensorMap* m, CUtensorMapDataType dt, int elem_bytes, const void* ptr, uint64_t rows,
-                         uint64_t cols, uint64_t ld, uint32_t box_rows, uint32_t box_cols) {
-  EncodeTiledFn enc = get_encode_fn();
-  if (!enc) return false;
-  const cuuint64_t dims[2] = {cols, rows};
-  const cuuint64_t strides[1] = {ld * uint64_t(elem_bytes)};
-  const cuuint32_t box[2] = {box_cols, box_rows};
-  const cuuint32_t estr[2] = {1, 1};
-  return enc(m, dt, 2, const_cast<void*>(ptr), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
-             CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
-             CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
-}
-
 struct Variant {
   const char* name;
   int block_n, stages, cg;   // cg: CTAs that share one 128*cg-row tile slot (cluster size)
   bool tma_store;
-  bool mcb = false;          // cg == 2 as a cluster of two independent cta_group::1 tiles with multicast B
+  bool mcb;                  // cg == 2 as a cluster of two independent cta_group::1 tiles with multicast B
+  bool product;              // false: laboratory variant, compiled only with -DSGLK_DIAG (libsglk_diag.so, tools/ only)
 };
-// index == variant id of the C ABI
+// index == variant id of the C ABI.  Ids are stable; the product library rejects the laboratory ones (SGLK_E_VARIANT).
 static const Variant kVariants[] = {
-    {"n128_s6_cta1_tma", 128, 6, 1, true},
-    {"n128_s6_cta1_direct", 128, 6, 1, false},
-    {"n256_s4_cta1_tma", 256, 4, 1, true},
-    {"n256_s6_cta2_tma", 256, 6, 2, true},
-    {"n256_s6_cta2_direct", 256, 6, 2, false},
-    {"n128_s8_cta2_tma", 128, 8, 2, true},
-    {"n64_s8_cta1_direct", 64, 8, 1, false},
-    {"diag_n256_s6_cta2_nopromote", 256, 6, 2, false},   // NOT product paths: diagnostics with wrong results
-    {"diag_n256_s6_cta2_plain_gemm", 256, 6, 2, true},
-    {"diag_n256_s7_cta2_plain_gemm", 256, 7, 2, false},
-    {"diag_n256_s4_cta2_plain_gemm", 256, 4, 2, false},
-    {"diag_n256_s7_cta2_nopromote", 256, 7, 2, false},
-    {"diag_n256_s6_cta2_plain_gemm_splitN", 256, 6, 2, true},
-    {"n256_s6_cta2_tma_splitn", 256, 6, 2, true},
-    {"n256_s4_cta1_tma_splitn", 256, 4, 1, true},
-    {"diag_n256_s6_cta2_timestamps", 256, 6, 2, true},
-    {"diag_n256_s6_cta2_splitn_timestamps", 256, 6, 2, true},
-    {"diag_n256_s6_cta2_nopromote_timestamps", 256, 6, 2, true},
-    {"diag_n256_s6_cta2_ldtm_only_timestamps", 256, 6, 2, true},
-    {"diag_n256_s6_cta2_fma_only_timestamps", 256, 6, 2, true},
-    {"diag_n256_s6_cta2_fma_only_not_on_mma_scheduler_timestamps", 256, 6, 2, true},
-    {"diag_n256_s6_cta2_handoff_then_fma_timestamps", 256, 6, 2, true},
-    {"diag_n256_s6_cta2_serialised_timestamps", 256, 6, 2, true},
-    {"n256_s4_cl2_mcb_tma", 256, 4, 2, true, true},      // product variant: 2-CTA cluster, cta_group::1 tiles, multicast B
-    {"n256_s6_cta2_tma_pairld", 256, 6, 2, true},         // paired tiles, chunk loads issued in pairs
-    {"n256_s6_cta2_tma_splitn_pairld", 256, 6, 2, true},
-    {"n256_s4_cl2_mcb_tma_pairld", 256, 4, 2, true, true},
-    {"n128_s8_cta2_tma_earlyrel", 128, 8, 2, true},       // 256x128 pair tiles, whole K-block share staged, hand-back before the FMAs
-    {"diag_n128_s8_cta2_nopromote", 128, 8, 2, true},     // NOT a product path (wrong results): per-block hand-off, no promotion
-    {"n256_s5_cta2_tma_splitn_2box", 256, 5, 2, true},     // split-N pair tiles, two staging boxes per epilogue warp (5-stage ring)
+    {"n128_s6_cta1_tma", 128, 6, 1, true, false, true},
+    {"n128_s6_cta1_direct", 128, 6, 1, false, false, true},
+    {"n256_s4_cta1_tma", 256, 4, 1, true, false, true},
+    {"n256_s6_cta2_tma", 256, 6, 2, true, false, true},
+    {"n256_s6_cta2_direct", 256, 6, 2, false, false, true},
+    {"n128_s8_cta2_tma", 128, 8, 2, true, false, true},
+    {"n64_s8_cta1_direct", 64, 8, 1, false, false, true},
+    {"diag_n256_s6_cta2_nopromote", 256, 6, 2, false, false, false},   // diag_*: wrong results by design (pipeline ceilings)
+    {"diag_n256_s6_cta2_plain_gemm", 256, 6, 2, true, false, false},
+    {"diag_n256_s7_cta2_plain_gemm", 256, 7, 2, false, false, false},
+    {"diag_n256_s4_cta2_plain_gemm", 256, 4, 2, false, false, false},
+    {"diag_n256_s7_cta2_nopromote", 256, 7, 2, false, false, false},
+    {"diag_n256_s6_cta2_plain_gemm_splitN", 256, 6, 2, true, false, false},
+    {"n256_s6_cta2_tma_splitn", 256, 6, 2, true, false, true},
+    {"n256_s4_cta1_tma_splitn", 256, 4, 1, true, false, true},
+    {"diag_n256_s6_cta2_timestamps", 256, 6, 2, true, false, false},
+    {"diag_n256_s6_cta2_splitn_timestamps", 256, 6, 2, true, false, false},
+    {"diag_n256_s6_cta2_nopromote_timestamps", 256, 6, 2, true, false, false},
+    {"diag_n256_s6_cta2_ldtm_only_timestamps", 256, 6, 2, true, false, false},
+    {"diag_n256_s6_cta2_fma_only_timestamps", 256, 6, 2, true, false, false},
+    {"diag_n256_s6_cta2_fma_only_not_on_mma_scheduler_timestamps", 256, 6, 2, true, false, false},
+    {"diag_n256_s6_cta2_handoff_then_fma_timestamps", 256, 6, 2, true, false, false},
+    {"diag_n256_s6_cta2_serialised_timestamps", 256, 6, 2, true, false, false},
+    {"n256_s4_cl2_mcb_tma", 256, 4, 2, true, true, true},          // 2-CTA cluster, cta_group::1 tiles, multicast B
+    {"lab_n256_s6_cta2_tma_pairld", 256, 6, 2, true, false, false},         // correct, measured no better: laboratory only
+    {"lab_n256_s6_cta2_tma_splitn_pairld", 256, 6, 2, true, false, false},
+    {"lab_n256_s4_cl2_mcb_tma_pairld", 256, 4, 2, true, true, false},
+    {"lab_n128_s8_cta2_tma_earlyrel", 128, 8, 2, true, false, false},
+    {"diag_n128_s8_cta2_nopromote", 128, 8, 2, true, false, false},
+    {"n256_s5_cta2_tma_splitn_2box", 256, 5, 2, true, false, true},  // split-N pair tiles, two staging boxes per epilogue warp
+    {"swapab_cta1", 128, 0, 1, false, false, true},                  // decode (gemm_decode.cu): weights are the MMA M side
+    {"swapab_cta2", 128, 0, 2, false, false, true},                  // decode, CTA pair: 256 weight rows, tokens split over the pair
 };
+constexpr int kDecodeVariant1 = 30, kDecodeVariant2 = 31;
 constexpr int kFirstStampVariant = 15, kLastStampVariant = 22;
 constexpr int kNumVariants = int(sizeof(kVariants) / sizeof(kVariants[0]));
-constexpr int kNumProductVariants = 7;   // ids 0..6; 7..12 are diagnostics; 13, 14 are product variants again
-constexpr int64_t kCounterAreaBytes = 1 << 20;   // first MiB of a stream-K workspace: tile counters (zero between launches)
 
 template <int BLOCK_N, int kStages, int kCG, typename OutT, bool kTmaStore, int kDiag = 0, bool kSplitN = false,
           bool kGrouped = false, int kEpi = 0, bool kMcB = false, int kPipe = 0>
@@ -1137,12 +1077,8 @@ static int launch_variant(const CUtensorMap& ta, const CUtensorMap& tb, const CM
   auto kern = fp8_blockwise_gemm_kernel<BLOCK_N, kStages, kCG, OutT, kTmaStore, kDiag, kSplitN, kGrouped, kEpi, kMcB, kPipe>;
   constexpr int smem = kMaxDynSmem;
   (void)sizeof(C);
-  static bool configured = false;   // per instantiation
-  if (!configured) {
-    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
-    if (e != cudaSuccess) return int(e);
-    configured = true;
-  }
+  static std::atomic<uint64_t> configured{0};   // per instantiation, one bit per device ordinal
+  if (int e = ensure_max_dyn_smem(kern, configured, smem)) return e;
   cudaLaunchConfig_t cfg;
   memset(&cfg, 0, sizeof(cfg));
   constexpr int kCl = kMcB ? 2 : kCG;
@@ -1171,14 +1107,17 @@ static int launch_by_id(int v, const CUtensorMap& ta, const CUtensorMap& tb, con
     case 4: return launch_variant<256, 6, 2, OutT, false>(ta, tb, tc, p, num_sms, st);
     case 5: return launch_variant<128, 8, 2, OutT, true>(ta, tb, tc, p, num_sms, st);
     case 6: return launch_variant<64, 8, 1, OutT, false>(ta, tb, tc, p, num_sms, st);
+    case 13: return launch_variant<256, 6, 2, OutT, true, 0, true>(ta, tb, tc, p, num_sms, st);
+    case 14: return launch_variant<256, 4, 1, OutT, true, 0, true>(ta, tb, tc, p, num_sms, st);
+    case 23: return launch_variant<256, 4, 1, OutT, true, 0, false, false, 0, true>(ta, tb, tc, p, num_sms, st);
+    case 29: return launch_variant<256, 5, 2, OutT, true, 0, true, false, 0, false, 3>(ta, tb, tc, p, num_sms, st);
+#ifdef SGLK_DIAG   // laboratory build only (libsglk_diag.so): pipeline-ceiling diagnostics with WRONG results, timeline stamps, retired experiments
     case 7: return launch_variant<256, 6, 2, OutT, false, 1>(ta, tb, tc, p, num_sms, st);
     case 8: return launch_variant<256, 6, 2, OutT, true, 2>(ta, tb, tc, p, num_sms, st);
     case 9: return launch_variant<256, 7, 2, OutT, false, 2>(ta, tb, tc, p, num_sms, st);
     case 10: return launch_variant<256, 4, 2, OutT, false, 2>(ta, tb, tc, p, num_sms, st);
     case 11: return launch_variant<256, 7, 2, OutT, false, 1>(ta, tb, tc, p, num_sms, st);
     case 12: return launch_variant<256, 6, 2, OutT, true, 3>(ta, tb, tc, p, num_sms, st);
-    case 13: return launch_variant<256, 6, 2, OutT, true, 0, true>(ta, tb, tc, p, num_sms, st);
-    case 14: return launch_variant<256, 4, 1, OutT, true, 0, true>(ta, tb, tc, p, num_sms, st);
     case 15: return launch_variant<256, 6, 2, OutT, true, 4>(ta, tb, tc, p, num_sms, st);
     case 16: return launch_variant<256, 6, 2, OutT, true, 4, true>(ta, tb, tc, p, num_sms, st);
     case 17: return launch_variant<256, 6, 2, OutT, true, 5>(ta, tb, tc, p, num_sms, st);
@@ -1187,15 +1126,23 @@ static int launch_by_id(int v, const CUtensorMap& ta, const CUtensorMap& tb, con
     case 20: return launch_variant<256, 6, 2, OutT, true, 8>(ta, tb, tc, p, num_sms, st);
     case 21: return launch_variant<256, 6, 2, OutT, true, 9>(ta, tb, tc, p, num_sms, st);
     case 22: return launch_variant<256, 6, 2, OutT, true, 10>(ta, tb, tc, p, num_sms, st);
-    case 23: return launch_variant<256, 4, 1, OutT, true, 0, false, false, 0, true>(ta, tb, tc, p, num_sms, st);
     case 24: return launch_variant<256, 6, 2, OutT, true, 0, false, false, 0, false, 1>(ta, tb, tc, p, num_sms, st);
     case 25: return launch_variant<256, 6, 2, OutT, true, 0, true, false, 0, false, 1>(ta, tb, tc, p, num_sms, st);
     case 26: return launch_variant<256, 4, 1, OutT, true, 0, false, false, 0, true, 1>(ta, tb, tc, p, num_sms, st);
     case 27: return launch_variant<128, 8, 2, OutT, true, 0, false, false, 0, false, 2>(ta, tb, tc, p, num_sms, st);
     case 28: return launch_variant<128, 8, 2, OutT, true, 1>(ta, tb, tc, p, num_sms, st);
-    case 29: return launch_variant<256, 5, 2, OutT, true, 0, true, false, 0, false, 3>(ta, tb, tc, p, num_sms, st);
+#endif
     default: return SGLK_E_VARIANT;
   }
+}
+
+static bool variant_available(int v) {
+  if (v < 0 || v >= kNumVariants) return false;
+#ifdef SGLK_DIAG
+  return true;
+#else
+  return kVariants[v].product;
+#endif
 }
 
 // fused output quantisation: the paired 256x256 tiles for prefill, the single-CTA 128x256 tiles below that
@@ -1217,25 +1164,24 @@ static bool tma_store_ok(const void* C, int64_t ldc, int out_bytes) {
   return (reinterpret_cast<uintptr_t>(C) & 15) == 0 && (ldc * out_bytes) % 16 == 0;
 }
 
-// 29 (split-N pair tiles, two staging boxes per epilogue warp, 5-stage ring): +1-3 % over 13 at every prefill shape
-// (tools/session38.sh), whole GPU suite green on it (tools/session39.sh: 632 passed).  SGLK_PREFILL_VARIANT=13 (read
-// once) selects the single-box 6-stage form for A/B runs.
-static int init_prefill_variant() {
-  const char* e = getenv("SGLK_PREFILL_VARIANT");
-  return (e && e[0] == '1' && e[1] == '3' && e[2] == 0) ? 13 : 29;
-}
-static int g_prefill_variant = init_prefill_variant();
-static int pick_variant(int64_t M, int64_t N, int64_t K) {
-  (void)K;
+// Prefill default: 29 (split-N pair tiles, two staging boxes per epilogue warp, 5-stage ring) — +1-3 % over 13 at every
+// prefill shape, whole GPU suite green on it.  Decode (M <= 256, plain [M, N] output): the swap-AB kernel of
+// gemm_decode.cu, single CTAs for a few tokens, CTA pairs (tokens split over the pair: half the L2 -> smem traffic of the
+// activation tile) from 33 tokens up.
+static int pick_variant(int64_t M, int64_t N, int64_t K, bool plain_output) {
+  // swap-AB decode kernel (gemm_decode.cu): weight rows on the MMA's M axis, <= 32 tokens on its N axis.  Measured in a
+  // CUDA graph on B200 (tools/decode_bench.py, N=24576 K=7168): 35.8 / 36.1 / 38.8 us at M = 1 / 16 / 32 against 41.0
+  // for the 128-row tile kernel below; from 64 tokens on the token-major kernel wins again (41.5 vs 44.6 us), so the
+  // cut is at 32.  (no plain output: fused all-gather / fused quantisation epilogues live in the prefill kernel)
+  if (plain_output && M <= 32 && decode_supported(M, N, K)) return kDecodeVariant2;
+  // a handful of wide tiles on a narrow weight (N=2112, 129 <= M <= 256: 9 pair tiles for 74 pairs): 128-wide single-CTA
+  // tiles give stream-K twice the units to balance
+  if (M > 128 && M <= 256 && N < 4096) return 0;
   // paired 256x256 tiles (one pair covers 256 rows), each K block issued as two 128-column MMA halves with their own
   // hand-off barriers: a half's stage has three half-MMAs (768 clk) of slack before it is needed again instead of one
-  // whole MMA (512) — +5-10 % over the unsplit pair tile at every prefill shape measured (tools/session18.sh)
-  // ... except a handful of wide tiles on a narrow weight (N=2112, 129 <= M <= 256: 9 pair tiles for 74 pairs):
-  // 128-wide single-CTA tiles give stream-K twice the units to balance (21.5 vs 26.7 us, tools/session23.sh)
-  if (M > 128 && M <= 256 && N < 4096) return 0;
-  // (29 = the same tiles with two staging boxes per epilogue warp and a 5-stage ring: +1-3 % over 13, tools/session38.sh)
-  if (M > 128 && N >= 256) return g_prefill_variant;
-  // M <= 128 (decode): one m-block; 128-wide tiles, balanced over the SMs by stream-K
+  // whole MMA (512) — +5-10 % over the unsplit pair tile at every prefill shape measured
+  if (M > 128 && N >= 256) return 29;
+  // M <= 128 without the decode kernel: one m-block; 128-wide tiles, balanced over the SMs by stream-K
   return 0;
 }
 
@@ -1253,9 +1199,9 @@ struct Plan {
 // fp32 partial per CTA), i.e. ~30 K blocks; it scales with the partial size.  Decode shapes win clearly (N=24576:
 // 1.3 waves of 128-wide tiles, N=2112: 17 tiles for 148 SMs); short-K prefill shapes (4096x7168x2048: 75.8 us
 // stream-K vs 67.6 us whole tiles) do not and stay on whole tiles.
-static int g_stream_k_mode = 0;   // sglk_debug_set_stream_k_mode: 0 cost model, 1 whenever possible, -1 never
-static int g_group_m = 0;         // sglk_debug_set_group_m: 0 = heuristic (pick_group_m), else m-blocks per raster group
-static Plan make_plan(int64_t M, int64_t N, int64_t K, int variant, int num_sms, bool have_ws) {
+// flags (SGLK_GEMM_* of the C ABI): stream-K decision (cost model / whenever possible / never), raster group override
+static Plan make_plan(int64_t M, int64_t N, int64_t K, int variant, int num_sms, bool have_ws, int flags) {
+  const int sk_mode = (flags & SGLK_GEMM_STREAMK_FORCE) ? 1 : ((flags & SGLK_GEMM_STREAMK_NEVER) ? -1 : 0);
   Plan pl;
   pl.variant = variant;
   const Variant v = kVariants[variant];
@@ -1270,8 +1216,8 @@ static Plan make_plan(int64_t M, int64_t N, int64_t K, int variant, int num_sms,
   const int64_t units = tiles * pl.num_k_blocks;
   const int64_t sk_workers = tiles * 4 < w0 ? tiles * 4 : w0;
   const int64_t sk_cost = (units + sk_workers - 1) / sk_workers + 30 * v.block_n / 256;
-  const bool possible = have_ws && (variant < kNumProductVariants || variant >= 13) && pl.num_k_blocks >= 2 && eff < 0.9 && units >= w0;
-  pl.stream_k = (possible && g_stream_k_mode >= 0 && (g_stream_k_mode > 0 || sk_cost < waves * pl.num_k_blocks)) ? 1 : 0;
+  const bool possible = have_ws && (kVariants[variant].product || variant >= 13) && pl.num_k_blocks >= 2 && eff < 0.9 && units >= w0;
+  pl.stream_k = (possible && sk_mode >= 0 && (sk_mode > 0 || sk_cost < waves * pl.num_k_blocks)) ? 1 : 0;
   pl.workers = int(pl.stream_k ? w0 : (tiles < w0 ? tiles : w0));
   // few, large tiles (N=2112: 17): more than ~4 contributors per tile makes the last arriver's sequential
   // re-read of the partials longer than the K blocks it saves (measured: 68 workers 13.6 us, 148 workers 18.9 us)
@@ -1303,7 +1249,7 @@ struct QuantOut {
 
 static int gemm_entry(const void* A, const void* B, const float* sa, const float* sb, void* Cout, int64_t M,
                       int64_t N, int64_t K, int64_t lda, int64_t ldb, int64_t ldc, int64_t sa_sm, int64_t sa_sk,
-                      int64_t sb_sk, int64_t sb_sn, int out_dtype, int variant, int num_sms, void* workspace,
+                      int64_t sb_sk, int64_t sb_sn, int out_dtype, int variant, int num_sms, int flags, void* workspace,
                       int64_t workspace_bytes, void* stream, void* const* extra_dests = nullptr, int num_extra = 0,
                       void* mc_ptr = nullptr, const QuantOut* qo = nullptr) {
   if (M < 0 || N < 0 || K < 0) return SGLK_E_SHAPE;
@@ -1329,8 +1275,14 @@ static int gemm_entry(const void* A, const void* B, const float* sa, const float
   if (K % 16 != 0 || lda % 16 != 0 || ldb % 16 != 0 || lda < K || ldb < K || ldc < N) return SGLK_E_STRIDE;
   if ((reinterpret_cast<uintptr_t>(A) & 15) || (reinterpret_cast<uintptr_t>(B) & 15)) return SGLK_E_STRIDE;
   if (M >= (int64_t(1) << 31) || N >= (int64_t(1) << 31) || K >= (int64_t(1) << 31)) return SGLK_E_SHAPE;
-  if (variant < 0) variant = pick_variant(M, N, K);
-  if (variant >= kNumVariants) return SGLK_E_VARIANT;
+  const bool plain_output = !qo && num_extra == 0 && !mc_ptr;
+  if (variant < 0) variant = pick_variant(M, N, K, plain_output);
+  if (!variant_available(variant)) return SGLK_E_VARIANT;
+  if (variant == kDecodeVariant1 || variant == kDecodeVariant2) {
+    if (!plain_output || !decode_supported(M, N, K)) return SGLK_E_VARIANT;
+    return decode_entry(A, B, sa, sb, Cout, M, N, K, lda, ldb, ldc, sa_sm, sa_sk, sb_sk, sb_sn, out_dtype,
+                        variant == kDecodeVariant2 ? 2 : 1, num_sms, flags, workspace, workspace_bytes, st);
+  }
   Variant v = kVariants[variant];
   if (num_extra < 0 || num_extra > kMaxDests - 1 || (num_extra > 0 && !extra_dests)) return SGLK_E_ARG;
   for (int d = 0; d < num_extra; ++d)
@@ -1349,11 +1301,11 @@ static int gemm_entry(const void* A, const void* B, const float* sa, const float
   p.sa_sm = sa_sm; p.sa_sk = sa_sk; p.sb_sk = sb_sk; p.sb_sn = sb_sn;
   // gate|up mode pairs two epilogue warps with named barriers: both must finish the same tiles, so no stream-K there
   const bool allow_sk = workspace != nullptr && !(qo && qo->silu_mul);
-  Plan pl = make_plan(M, N, K, variant, num_sms, allow_sk);
+  Plan pl = make_plan(M, N, K, variant, num_sms, allow_sk, flags);
   if (qo) { p.q_scales = qo->scales; p.qs_sm = qo->ss_m; p.qs_sg = qo->ss_g; p.q_eps = qo->eps; }
   else { p.q_scales = nullptr; p.qs_sm = p.qs_sg = 0; p.q_eps = 0.0f; }
   if (pl.stream_k && (workspace_bytes < pl.counter_bytes + pl.partial_bytes || (reinterpret_cast<uintptr_t>(workspace) & 15)))
-    pl = make_plan(M, N, K, variant, num_sms, false);
+    pl = make_plan(M, N, K, variant, num_sms, false, flags);
   p.num_m_blocks = pl.num_m_blocks;
   p.num_n_blocks = pl.num_n_blocks;
   p.num_k_blocks = pl.num_k_blocks;
@@ -1365,7 +1317,8 @@ static int gemm_entry(const void* A, const void* B, const float* sa, const float
   {
     int64_t gm = (int64_t(32) << 20) / (int64_t(BLOCK_M) * v.cg * K);
     gm = gm < 4 ? 4 : (gm > 16 ? 16 : gm);
-    p.group_m = g_group_m > 0 ? g_group_m : int32_t(gm);
+    const int gm_override = (flags >> SGLK_GEMM_GROUP_M_SHIFT) & 0xFF;
+    p.group_m = gm_override > 0 ? gm_override : int32_t(gm);
   }
   p.stream_k = pl.stream_k;
   p.ws_counters = pl.stream_k ? static_cast<int32_t*>(workspace) : nullptr;
@@ -1529,10 +1482,10 @@ extern "C" int64_t sglk_grouped_mm_workspace_bytes(int64_t num_experts, int64_t 
 extern "C" int sglk_fp8_blockwise_scaled_mm_ex(const void* A, const void* B, const float* sa, const float* sb, void* C,
                                                int64_t M, int64_t N, int64_t K, int64_t lda, int64_t ldb, int64_t ldc,
                                                int64_t sa_stride_m, int64_t sa_stride_k, int64_t sb_stride_k,
-                                               int64_t sb_stride_n, int out_dtype, int variant, int num_sms,
+                                               int64_t sb_stride_n, int out_dtype, int variant, int num_sms, int flags,
                                                void* workspace, int64_t workspace_bytes, void* stream) {
   return sglk::gemm_entry(A, B, sa, sb, C, M, N, K, lda, ldb, ldc, sa_stride_m, sa_stride_k, sb_stride_k,
-                          sb_stride_n, out_dtype, variant, num_sms, workspace, workspace_bytes, stream);
+                          sb_stride_n, out_dtype, variant, num_sms, flags, workspace, workspace_bytes, stream);
 }
 
 extern "C" int sglk_fp8_blockwise_scaled_mm_allgather(const void* A, const void* B, const float* sa, const float* sb,
@@ -1544,7 +1497,7 @@ extern "C" int sglk_fp8_blockwise_scaled_mm_allgather(const void* A, const void*
                                                       void* workspace, int64_t workspace_bytes, void* stream) {
   if (variant < 0) variant = (M > 128 && N >= 256) ? 3 : 0;   // TMA-store variants only
   return sglk::gemm_entry(A, B, sa, sb, C_local, M, N, K, lda, ldb, ldc, sa_stride_m, sa_stride_k, sb_stride_k,
-                          sb_stride_n, out_dtype, variant, num_sms, workspace, workspace_bytes, stream,
+                          sb_stride_n, out_dtype, variant, num_sms, 0, workspace, workspace_bytes, stream,
                           C_multicast ? nullptr : C_peers, C_multicast ? 0 : num_peers, C_multicast);
 }
 
@@ -1553,30 +1506,21 @@ extern "C" int sglk_fp8_blockwise_scaled_mm_quant(const void* A, const void* B, 
                                                   int64_t ldb, int64_t ldq, int64_t sa_stride_m, int64_t sa_stride_k,
                                                   int64_t sb_stride_k, int64_t sb_stride_n, int64_t os_stride_m,
                                                   int64_t os_stride_g, int round_dtype, float eps, int silu_mul,
-                                                  int num_sms, void* workspace, int64_t workspace_bytes, void* stream) {
+                                                  int num_sms, int flags, void* workspace, int64_t workspace_bytes,
+                                                  void* stream) {
   sglk::QuantOut qo{out_q, ldq, out_s, os_stride_m, os_stride_g, eps, silu_mul ? 1 : 0};
   return sglk::gemm_entry(A, B, sa, sb, nullptr, M, N, K, lda, ldb, N, sa_stride_m, sa_stride_k, sb_stride_k, sb_stride_n,
-                          round_dtype, -1, num_sms, workspace, workspace_bytes, stream, nullptr, 0, nullptr, &qo);
+                          round_dtype, -1, num_sms, flags, workspace, workspace_bytes, stream, nullptr, 0, nullptr, &qo);
 }
 
-extern "C" int sglk_debug_set_stream_k_mode(int mode) {
-  const int prev = sglk::g_stream_k_mode;
-  sglk::g_stream_k_mode = mode > 0 ? 1 : (mode < 0 ? -1 : 0);
-  return prev;
-}
-
-extern "C" int sglk_debug_set_group_m(int group_m) {
-  const int prev = sglk::g_group_m;
-  sglk::g_group_m = group_m > 0 ? group_m : 0;
-  return prev;
-}
-
-extern "C" int64_t sglk_gemm_workspace_bytes(int64_t M, int64_t N, int64_t K, int variant, int num_sms) {
+extern "C" int64_t sglk_gemm_workspace_bytes(int64_t M, int64_t N, int64_t K, int variant, int num_sms, int flags) {
   if (M <= 0 || N <= 0 || K <= 0) return 0;
-  if (variant < 0) variant = sglk::pick_variant(M, N, K);
-  if (variant >= sglk::kNumVariants) return 0;
+  if (variant < 0) variant = sglk::pick_variant(M, N, K, true);
+  if (!sglk::variant_available(variant)) return 0;
   if (num_sms <= 0) num_sms = sglk::device_sm_count();
-  const sglk::Plan pl = sglk::make_plan(M, N, K, variant, num_sms, true);
+  if (variant == sglk::kDecodeVariant1 || variant == sglk::kDecodeVariant2)
+    return sglk::decode_workspace_bytes(M, N, K, variant == sglk::kDecodeVariant2 ? 2 : 1, num_sms, flags);
+  const sglk::Plan pl = sglk::make_plan(M, N, K, variant, num_sms, true, flags);
   const int64_t base = pl.stream_k ? pl.counter_bytes + pl.partial_bytes : (pl.scale_bytes ? sglk::kCounterAreaBytes : 0);
   return base + pl.scale_bytes;
 }
@@ -1586,11 +1530,14 @@ extern "C" int sglk_fp8_blockwise_scaled_mm(const void* A, const void* B, const 
                                             int64_t sa_stride_m, int64_t sa_stride_k, int64_t sb_stride_k,
                                             int64_t sb_stride_n, int out_dtype, void* stream) {
   return sglk::gemm_entry(A, B, sa, sb, C, M, N, K, lda, ldb, ldc, sa_stride_m, sa_stride_k, sb_stride_k,
-                          sb_stride_n, out_dtype, -1, 0, nullptr, 0, stream);
+                          sb_stride_n, out_dtype, -1, 0, 0, nullptr, 0, stream);
 }
 
 extern "C" int sglk_gemm_num_variants(void) { return sglk::kNumVariants; }
 extern "C" const char* sglk_gemm_variant_name(int v) {
   return (v >= 0 && v < sglk::kNumVariants) ? sglk::kVariants[v].name : "";
 }
-extern "C" int sglk_gemm_pick_variant(int64_t M, int64_t N, int64_t K) { return sglk::pick_variant(M, N, K); }
+extern "C" int sglk_gemm_variant_is_product(int v) {
+  return (v >= 0 && v < sglk::kNumVariants && sglk::kVariants[v].product) ? 1 : 0;
+}
+extern "C" int sglk_gemm_pick_variant(int64_t M, int64_t N, int64_t K) { return sglk::pick_variant(M, N, K, true); }

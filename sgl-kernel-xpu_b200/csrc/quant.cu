@@ -132,7 +132,7 @@ extern "C" int sglk_per_token_group_quant_8bit_v2(const void* input, void* outpu
                               tokens_per_expert, scale_expert_stride, masked_m);
 }
 
-extern "C" int sglk_debug_check_division(const float* scales, int64_t num_scales, int numerator_dtype,
+extern "C" int sglk_selftest_division(const float* scales, int64_t num_scales, int numerator_dtype,
                                          unsigned long long* mismatches, void* stream) {
   if (!scales || !mismatches || num_scales <= 0 || (numerator_dtype != SGLK_BF16 && numerator_dtype != SGLK_F16))
     return SGLK_E_ARG;

@@ -17,7 +17,7 @@
 //     fp32x2 ops  q0 = x*r;  e = fma(q0,-s,x);  q = fma(e,r,q0)  (Markstein correction).  Equality of
 //     the e4m3 code with RN(x/s) is verified exhaustively for every (x, amax) pair of bf16 and of f16
 //     on the CPU (oracle_check_division_scheme) and sampled on the device
-//     (sglk_debug_check_division); f32 inputs keep div.rn;
+//     (sglk_selftest_division); f32 inputs keep div.rn;
 //   * the code's sign bit is taken from x itself (x/s has the sign of x; this also makes -0.0 -> 0x80
 //     exact, which the fma chain alone would lose) with one PRMT + one LOP3 per four codes;
 //   * e4m3 rounding is the hardware cvt.rn.satfinite.e4m3x2.f32.

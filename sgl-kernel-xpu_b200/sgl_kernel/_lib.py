@@ -17,7 +17,8 @@ LIB_PATH = os.environ.get(
 # dtype / layout codes of include/sglk_fp8.h
 BF16, F16, F32, E4M3, INT8 = 0, 1, 2, 3, 4
 SCALE_F32_ROW_MAJOR, SCALE_F32_COL_MAJOR, SCALE_UE8M0_ROW_MAJOR, SCALE_UE8M0_COL_PACKED = 0, 1, 2, 3
-ABI_VERSION = 1
+ABI_VERSION = 2
+STREAMK_AUTO, STREAMK_FORCE, STREAMK_NEVER, GROUP_M_SHIFT, SPLIT_SHIFT = 0, 1, 2, 8, 16
 
 _i64, _i32, _f32, _vp = ctypes.c_int64, ctypes.c_int, ctypes.c_float, ctypes.c_void_p
 
@@ -35,21 +36,20 @@ SYMBOLS = {
     "sglk_fp8_blockwise_scaled_mm": (
         _i32, [_vp, _vp, _vp, _vp, _vp] + [_i64] * 10 + [_i32, _vp]),
     "sglk_fp8_blockwise_scaled_mm_ex": (
-        _i32, [_vp, _vp, _vp, _vp, _vp] + [_i64] * 10 + [_i32, _i32, _i32, _vp, _i64, _vp]),
+        _i32, [_vp, _vp, _vp, _vp, _vp] + [_i64] * 10 + [_i32, _i32, _i32, _i32, _vp, _i64, _vp]),
     "sglk_fp8_blockwise_scaled_mm_quant": (
-        _i32, [_vp, _vp, _vp, _vp, _vp, _vp] + [_i64] * 12 + [_i32, _f32, _i32, _i32, _vp, _i64, _vp]),
+        _i32, [_vp, _vp, _vp, _vp, _vp, _vp] + [_i64] * 12 + [_i32, _f32, _i32, _i32, _i32, _vp, _i64, _vp]),
     "sglk_fp8_blockwise_scaled_grouped_mm": (
         _i32, [_vp, _vp, _vp, _vp, _vp, _vp, _vp] + [_i64] * 12 + [_i32, _i32, _vp, _i64, _vp]),
     "sglk_grouped_mm_workspace_bytes": (_i64, [_i64, _i64]),
-    "sglk_gemm_workspace_bytes": (_i64, [_i64, _i64, _i64, _i32, _i32]),
+    "sglk_gemm_workspace_bytes": (_i64, [_i64, _i64, _i64, _i32, _i32, _i32]),
     "sglk_fp8_blockwise_scaled_mm_allgather": (
         _i32, [_vp, _vp, _vp, _vp, _vp, ctypes.POINTER(_vp), _i32, _vp] + [_i64] * 10 + [_i32, _i32, _i32, _vp, _i64, _vp]),
     "sglk_gemm_num_variants": (_i32, []),
     "sglk_gemm_variant_name": (ctypes.c_char_p, [_i32]),
+    "sglk_gemm_variant_is_product": (_i32, [_i32]),
     "sglk_gemm_pick_variant": (_i32, [_i64, _i64, _i64]),
-    "sglk_debug_check_division": (_i32, [_vp, _i64, _i32, _vp, _vp]),
-    "sglk_debug_set_stream_k_mode": (_i32, [_i32]),
-    "sglk_debug_set_group_m": (_i32, [_i32]),
+    "sglk_selftest_division": (_i32, [_vp, _i64, _i32, _vp, _vp]),
 }
 
 _lib = None

@@ -10,6 +10,7 @@ and the *current* CUDA stream.  No host sync, no allocation in quant, caching-al
 """
 from __future__ import annotations
 
+import threading
 from typing import Optional
 
 import torch
@@ -228,19 +229,65 @@ def _gemm_checks(mat_a, mat_b, scales_a, scales_b, out_dtype):
 # leaves the counter region zeroed, so the buffer is reused by consecutive launches on its stream
 # (the same per-process cache idea as the reference's `_get_cache_buf`, python/sgl_kernel/gemm.py:80).
 _workspaces = {}
+_workspaces_lock = threading.Lock()
 
 
-def _get_workspace(device: torch.device, stream_ptr: int, nbytes: int) -> torch.Tensor:
+def _get_workspace(device: torch.device, stream_ptr: int, nbytes: int) -> Optional[torch.Tensor]:
+    """The cached workspace of (device, stream), or None when one would have to be created inside a CUDA-graph
+    capture: its zero-fill would only be recorded, not executed, and an eager launch before the first replay would
+    then meet garbage tile counters.  The op falls back to whole-tile scheduling for that call (same results);
+    warm the op up once outside the capture to get stream-K inside graphs."""
     key = (device.index, stream_ptr)
-    ws = _workspaces.get(key)
-    if ws is None or ws.numel() < nbytes:
-        ws = torch.zeros(max(nbytes, 1 << 20), dtype=torch.uint8, device=device)
-        _workspaces[key] = ws
-    return ws
+    with _workspaces_lock:
+        ws = _workspaces.get(key)
+        if ws is None or ws.numel() < nbytes:
+            if torch.cuda.is_current_stream_capturing():
+                return None
+            ws = torch.zeros(max(nbytes, 1 << 20), dtype=torch.uint8, device=device)
+            _workspaces[key] = ws
+        return ws
 
 
-def _gemm(mat_a, mat_b, scales_a, scales_b, out_dtype, variant: int = -1, num_sms: int = 0, stream_k: bool = True):
-    """fp8_blockwise_scaled_mm, include/sgl_kernel_ops.h:581-586 (allocates and returns C)."""
+def _invalidate_workspace(device: torch.device, stream_ptr: int) -> None:
+    """After a failed launch the tile counters may be non-zero: drop the buffer, the next call gets a fresh zeroed one."""
+    with _workspaces_lock:
+        _workspaces.pop((device.index, stream_ptr), None)
+
+
+# Scheduling override for tests and tuning tools (thread-local, Python-side only — the C library keeps no state):
+# "auto" = the cost model, "force" = stream-K whenever the shape allows it, "never" = whole tiles.
+_sched = threading.local()
+
+
+class stream_k_mode:
+    def __init__(self, mode: str):
+        assert mode in ("auto", "force", "never")
+        self.mode = mode
+
+    def __enter__(self):
+        self.prev = getattr(_sched, "mode", "auto")
+        _sched.mode = self.mode
+        return self
+
+    def __exit__(self, *exc):
+        _sched.mode = self.prev
+        return False
+
+
+def _sched_flags(stream_k=True, group_m: int = 0, split: int = 0) -> int:
+    mode = getattr(_sched, "mode", "auto")
+    if stream_k == "force":
+        mode = "force"
+    elif stream_k is False or stream_k == "never":
+        mode = "never"
+    flags = {"auto": _lib.STREAMK_AUTO, "force": _lib.STREAMK_FORCE, "never": _lib.STREAMK_NEVER}[mode]
+    return flags | ((int(group_m) & 0xFF) << _lib.GROUP_M_SHIFT) | ((int(split) & 0xFF) << _lib.SPLIT_SHIFT)
+
+
+def _gemm(mat_a, mat_b, scales_a, scales_b, out_dtype, variant: int = -1, num_sms: int = 0, stream_k=True, group_m: int = 0,
+          split: int = 0):
+    """fp8_blockwise_scaled_mm, include/sgl_kernel_ops.h:581-586 (allocates and returns C).
+    stream_k: True (cost model), "force", or False ("never": whole tiles, no workspace)."""
     _check(mat_a.is_cuda and mat_b.is_cuda and scales_a.is_cuda and scales_b.is_cuda,
            "fp8_blockwise_scaled_mm: tensors must be CUDA tensors")
     M, N, K = _gemm_checks(mat_a, mat_b, scales_a, scales_b, out_dtype)
@@ -252,18 +299,21 @@ def _gemm(mat_a, mat_b, scales_a, scales_b, out_dtype, variant: int = -1, num_sm
     _check(lda % 16 == 0 and ldb % 16 == 0 and mat_a.data_ptr() % 16 == 0 and mat_b.data_ptr() % 16 == 0,
            "mat_a / mat_b rows must be 16-byte aligned")
     lib = _lib.load()
+    flags = _sched_flags(stream_k, group_m, split)
     with torch.cuda.device(mat_a.device):
         stream = _stream_ptr(mat_a)
         ws_ptr, ws_bytes = None, 0
-        if stream_k:
-            need = lib.sglk_gemm_workspace_bytes(M, N, K, variant, num_sms)
-            if need > 0:
-                ws = _get_workspace(mat_a.device, stream, need)
+        if stream_k is not False:   # False: no workspace at all (whole tiles, scales read in whatever layout they have)
+            need = lib.sglk_gemm_workspace_bytes(M, N, K, variant, num_sms, flags)
+            ws = _get_workspace(mat_a.device, stream, need) if need > 0 else None
+            if ws is not None:
                 ws_ptr, ws_bytes = ws.data_ptr(), ws.numel()
         rc = lib.sglk_fp8_blockwise_scaled_mm_ex(
             mat_a.data_ptr(), mat_b.data_ptr(), scales_a.data_ptr(), scales_b.data_ptr(), out.data_ptr(),
             M, N, K, lda, ldb, out.stride(0), scales_a.stride(0), scales_a.stride(1), scales_b.stride(0),
-            scales_b.stride(1), _GEMM_OUT[out_dtype], variant, num_sms, ws_ptr, ws_bytes, stream)
+            scales_b.stride(1), _GEMM_OUT[out_dtype], variant, num_sms, flags, ws_ptr, ws_bytes, stream)
+        if rc != 0 and ws_ptr is not None:
+            _invalidate_workspace(mat_a.device, stream)
     _lib.check(rc, "fp8_blockwise_scaled_mm")
     return out
 
@@ -288,9 +338,10 @@ def _gemm_allgather(mat_a, mat_b, scales_a, scales_b, out_full, col_lo: int, pee
     with torch.cuda.device(mat_a.device):
         stream = _stream_ptr(mat_a)
         ws_ptr, ws_bytes = None, 0
-        need = lib.sglk_gemm_workspace_bytes(M, N, K, variant, num_sms)
-        if need > 0:
-            ws = _get_workspace(mat_a.device, stream, need)
+        ag_variant = variant if variant >= 0 else (3 if (M > 128 and N >= 256) else 0)   # the entry point's own default
+        need = lib.sglk_gemm_workspace_bytes(M, N, K, ag_variant, num_sms, 0)
+        ws = _get_workspace(mat_a.device, stream, need) if need > 0 else None
+        if ws is not None:
             ws_ptr, ws_bytes = ws.data_ptr(), ws.numel()
         import ctypes
 
@@ -332,14 +383,15 @@ def _gemm_quant(mat_a, mat_b, scales_a, scales_b, round_dtype, eps, fuse_silu_an
     with torch.cuda.device(mat_a.device):
         stream = _stream_ptr(mat_a)
         ws_ptr, ws_bytes = None, 0
-        need = lib.sglk_gemm_workspace_bytes(M, N, K, 13 if M > 128 else 2, 0)
-        if need > 0:
-            ws = _get_workspace(mat_a.device, stream, need)
+        flags = _sched_flags()
+        need = lib.sglk_gemm_workspace_bytes(M, N, K, 13 if M > 128 else 2, 0, flags)
+        ws = _get_workspace(mat_a.device, stream, need) if need > 0 else None
+        if ws is not None:
             ws_ptr, ws_bytes = ws.data_ptr(), ws.numel()
         rc = lib.sglk_fp8_blockwise_scaled_mm_quant(
             mat_a.data_ptr(), mat_b.data_ptr(), scales_a.data_ptr(), scales_b.data_ptr(), q.data_ptr(), s.data_ptr(),
             M, N, K, lda, ldb, q.stride(0), scales_a.stride(0), scales_a.stride(1), scales_b.stride(0), scales_b.stride(1),
-            s.stride(0), s.stride(1), _GEMM_OUT[round_dtype], float(eps), int(fuse), 0, ws_ptr, ws_bytes, stream)
+            s.stride(0), s.stride(1), _GEMM_OUT[round_dtype], float(eps), int(fuse), 0, flags, ws_ptr, ws_bytes, stream)
     _lib.check(rc, name)
     return q, s
 

@@ -20,13 +20,25 @@ def _declared_symbols():
     return re.findall(r"SGLK_API\s+[\w\s\*]+?\b(sglk_\w+)\s*\(", hdr)
 
 
-def test_library_exports_every_declared_symbol():
+def _exported_symbols(path):
+    import subprocess
+
+    out = subprocess.run(["nm", "-D", "--defined-only", path], capture_output=True, text=True, check=True).stdout
+    return {ln.split()[-1] for ln in out.splitlines() if " T " in ln}
+
+
+def test_library_exports_exactly_the_declared_symbols():
+    """header == exports == python binding table, in both directions: nothing undeclared is reachable through the
+    product library (laboratory code lives in libsglk_diag.so, built only by `make diag`)."""
     names = _declared_symbols()
     assert len(names) >= 10
     lib = ctypes.CDLL(_lib.LIB_PATH)
     for n in names:
         assert hasattr(lib, n), f"{n} declared in include/sglk_fp8.h but not exported"
     assert set(names) == set(_lib.SYMBOLS), "python binding table and header disagree"
+    exported = {n for n in _exported_symbols(_lib.LIB_PATH) if not n.startswith("_")}
+    assert exported == set(names), f"exported but undeclared: {sorted(exported - set(names))}; missing: {sorted(set(names) - exported)}"
+    assert not any("debug" in n or "diag" in n for n in exported)
     assert _lib.load().sglk_abi_version() == _lib.ABI_VERSION
 
 
@@ -66,7 +78,11 @@ def test_c_abi_rejects_bad_arguments_before_launch():
     assert g(None, p, p, p, p, 4, 128, 128, 128, 128, 128, 1, 4, 1, 1, _lib.BF16, None) == -1             # null
     assert g(p, p, p, p, p, 0, 128, 128, 128, 128, 128, 1, 4, 1, 1, _lib.BF16, None) == 0                 # empty
     ex = lib.sglk_fp8_blockwise_scaled_mm_ex
-    assert ex(p, p, p, p, p, 4, 128, 128, 128, 128, 128, 1, 4, 1, 1, _lib.BF16, 99, 0, None, 0, None) == -9        # variant
+    assert ex(p, p, p, p, p, 4, 128, 128, 128, 128, 128, 1, 4, 1, 1, _lib.BF16, 99, 0, 0, None, 0, None) == -9     # variant
+    for v in range(lib.sglk_gemm_num_variants()):       # laboratory ids (diagnostics with wrong results) are not launchable
+        if not lib.sglk_gemm_variant_is_product(v):
+            assert ex(p, p, p, p, p, 4, 128, 128, 128, 128, 128, 1, 4, 1, 1, _lib.BF16, v, 0, 0, None, 0, None) == -9
+            assert lib.sglk_gemm_variant_name(v).startswith((b"diag_", b"lab_"))
 
 
 def test_schemas_are_the_reference_strings():

@@ -11,7 +11,7 @@ import torch
 from oracle import torch_oracle as O
 
 import sgl_kernel
-from sgl_kernel import _lib
+from sgl_kernel import _lib, _ops
 
 pytestmark = pytest.mark.gpu
 DEV = "cuda"
@@ -39,14 +39,12 @@ def unfused(a, b, sa, sb, dt, fuse, col_major):
     if fuse:
         # the gate|up mode always runs whole tiles; give its reference the same K-summation order (stream-K would
         # change the fp32 order and with it a few bf16 roundings)
-        lib = _lib.load()
-        prev = lib.sglk_debug_set_stream_k_mode(-1)
-        try:
-            y = sgl_kernel.fp8_blockwise_scaled_mm(a, b, sa, sb, dt)
-        finally:
-            lib.sglk_debug_set_stream_k_mode(prev)
+        with _ops.stream_k_mode("never"):
+            y = _ops._gemm(a, b, sa, sb, dt, 13 if a.shape[0] > 128 else 2)
     else:
-        y = sgl_kernel.fp8_blockwise_scaled_mm(a, b, sa, sb, dt)
+        # the fused op runs the prefill kernel's tiles (13: split-N pairs, 2: single-CTA 256-wide below 129 rows) under
+        # the same scheduling decision; its unfused twin is that kernel, not the decode kernel small M defaults to
+        y = _ops._gemm(a, b, sa, sb, dt, 13 if a.shape[0] > 128 else 2)
     if fuse:
         M, N = y.shape
         # de-interleave the 128-column blocks back to [gate | up]
@@ -103,7 +101,8 @@ def test_interleave_gate_up_round_trip():
     wq, ws = O.per_block_cast_to_fp8(w)
     wq, ws = wq.to(DEV), ws.to(DEV)
     xq, xs = sgl_kernel.per_token_group_quant_fp8(x, 128, enable_v2=False)
-    y = sgl_kernel.fp8_blockwise_scaled_mm(xq, wq.t(), xs, ws.t(), torch.bfloat16)            # [M, gate | up]
+    with _ops.stream_k_mode("never"):
+        y = _ops._gemm(xq, wq.t(), xs, ws.t(), torch.bfloat16, 13)                            # [M, gate | up]
     q_ref, s_ref = sgl_kernel.per_token_group_quant_fp8(y, 128, fuse_silu_and_mul=True, enable_v2=True)
     wq_i, ws_i = sgl_kernel.interleave_gate_up(wq, ws)
     q, s = sgl_kernel.fp8_blockwise_scaled_mm_quant(xq, wq_i.t(), xs, ws_i.t(), torch.bfloat16, fuse_silu_and_mul=True)
@@ -132,20 +131,16 @@ def test_stream_k_and_whole_tile_schedules_agree():
     fp8_blockwise_scaled_mm, so it equals the separate ops under either schedule.  The gate|up mode always runs whole
     tiles (its paired epilogue warps must finish the same tiles), so its reference is the whole-tile GEMM: stream-K
     changes the fp32 summation order and with it a few bf16 roundings."""
-    lib = _lib.load()
     a, b, sa, sb = to_dev(*O.make_gemm_inputs(384, 1280, 7168, seed=11), True)
-    prev = lib.sglk_debug_set_stream_k_mode(-1)
-    try:
+    with _ops.stream_k_mode("never"):
         q0, s0 = sgl_kernel.fp8_blockwise_scaled_mm_quant(a, b, sa, sb, torch.bfloat16)
         (q_ref0, s_ref0), _ = unfused(a, b, sa, sb, torch.bfloat16, False, False)
         (qs_ref, ss_ref), _ = unfused(a, b, sa, sb, torch.bfloat16, True, False)
-        lib.sglk_debug_set_stream_k_mode(1)
+    with _ops.stream_k_mode("force"):
         q1, s1 = sgl_kernel.fp8_blockwise_scaled_mm_quant(a, b, sa, sb, torch.bfloat16)
         (q_ref1, s_ref1), _ = unfused(a, b, sa, sb, torch.bfloat16, False, False)
         qs, ss = sgl_kernel.fp8_blockwise_scaled_mm_quant(a, b, sa, sb, torch.bfloat16, fuse_silu_and_mul=True)
         torch.cuda.synchronize()
-    finally:
-        lib.sglk_debug_set_stream_k_mode(prev)
     assert_same(q0, s0, q_ref0, s_ref0)
     assert_same(q1, s1, q_ref1, s_ref1)
     assert_same(qs, ss, qs_ref, ss_ref)

@@ -338,7 +338,7 @@ def test_division_scheme_on_device():
     scales = (amax / 448.0).to(DEV)
     for dt in (_lib.BF16, _lib.F16):
         bad = torch.zeros(1, dtype=torch.int64, device=DEV)
-        rc = _lib.load().sglk_debug_check_division(scales.data_ptr(), scales.numel(), dt, bad.data_ptr(),
+        rc = _lib.load().sglk_selftest_division(scales.data_ptr(), scales.numel(), dt, bad.data_ptr(),
                                                    torch.cuda.current_stream().cuda_stream)
         assert rc == 0
         torch.cuda.synchronize()

@@ -1,5 +1,5 @@
 #!/usr/bin/env python
-"""Rasterisation sweep of the dense GEMM: m-blocks per raster group (sglk_debug_set_group_m), interleaved round-robin
+"""Rasterisation sweep of the dense GEMM: m-blocks per raster group (the SGLK_GEMM_GROUP_M_SHIFT bits of the flags argument), interleaved round-robin
 under the power cap, median per setting.  usage: group_m_sweep.py MxNxK g1,g2,... [rounds]   (ONCE=1: one launch per
 setting, for `ncu --metrics dram__bytes_read.sum,dram__bytes_write.sum`)"""
 import json, os, sys
@@ -19,9 +19,8 @@ sb = (torch.randn(-(N // -128), K // 128, device=dev) * 1e-3).t()
 flush = torch.zeros(256 << 20, dtype=torch.uint8, device=dev).view(torch.int64)
 ref = None
 for g in groups:
-    lib.sglk_debug_set_group_m(g)
     flush.sum()
-    out = _ops._gemm(a, bt.t(), sa, sb, torch.bfloat16, -1, 0, True)
+    out = _ops._gemm(a, bt.t(), sa, sb, torch.bfloat16, -1, 0, True, g)
     torch.cuda.synchronize()
     if ref is None:
         ref = out.clone()
@@ -32,16 +31,14 @@ if os.environ.get("ONCE") == "1":
 times = {g: [] for g in groups}
 for r in range(rounds + 2):
     for g in groups:
-        lib.sglk_debug_set_group_m(g)
         for _ in range(3):
             flush.sum()
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             e0.record()
-            _ops._gemm(a, bt.t(), sa, sb, torch.bfloat16, -1, 0, True)
+            _ops._gemm(a, bt.t(), sa, sb, torch.bfloat16, -1, 0, True, g)
             e1.record(); e1.synchronize()
             if r >= 2:
                 times[g].append(e0.elapsed_time(e1))
-lib.sglk_debug_set_group_m(0)
 for g in groups:
     t = sorted(times[g]); med = t[len(t) // 2]
     print(json.dumps({"shape": sys.argv[1], "group_m": g, "us_med": round(med * 1e3, 1),

@@ -6,6 +6,8 @@ sys.path[:0] = [ROOT, os.path.join(ROOT, "sgl-kernel-xpu_b200")]
 import torch
 import torch.distributed as dist
 import torch.distributed._symmetric_memory as symm_mem
+# laboratory tool: needs the diagnostics build (make -C sgl-kernel-xpu_b200/csrc diag)
+os.environ.setdefault("SGLK_LIBRARY", os.path.join(ROOT, "sgl-kernel-xpu_b200", "lib", "libsglk_diag.so"))
 from sgl_kernel import _lib
 
 rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])

@@ -5,6 +5,8 @@ import ctypes, os, sys, json
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path[:0] = [ROOT, os.path.join(ROOT, "sgl-kernel-xpu_b200")]
 import torch
+# laboratory tool: needs the diagnostics build (make -C sgl-kernel-xpu_b200/csrc diag)
+os.environ.setdefault("SGLK_LIBRARY", os.path.join(ROOT, "sgl-kernel-xpu_b200", "lib", "libsglk_diag.so"))
 import sgl_kernel
 from sgl_kernel import _lib
 lib = _lib.load()

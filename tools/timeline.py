@@ -2,6 +2,8 @@ import os, sys, json
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path[:0] = [ROOT, os.path.join(ROOT, "sgl-kernel-xpu_b200")]
 import torch
+# laboratory tool: needs the diagnostics build (make -C sgl-kernel-xpu_b200/csrc diag)
+os.environ.setdefault("SGLK_LIBRARY", os.path.join(ROOT, "sgl-kernel-xpu_b200", "lib", "libsglk_diag.so"))
 from sgl_kernel import _lib, _ops
 dev = "cuda"
 M, N, K = 8192, 8192, 8192

@@ -17,14 +17,11 @@ for sh in shapes:
     bt = ((torch.rand(N, K, device=dev) - 0.5) * 896).to(torch.float8_e4m3fn)
     sa = torch.randn(M, K // 128, device=dev) * 1e-3
     sb = (torch.randn(-(N // -128), K // 128, device=dev) * 1e-3).t()
-    for mode in (-1, 1):
-        prev = lib.sglk_debug_set_stream_k_mode(mode)
-        try:
+    for mode in ("never", "force"):
+        with _ops.stream_k_mode(mode):
             ya = _ops._gemm(a, bt.t(), sa, sb, torch.bfloat16, va, 0, True)
             yb = _ops._gemm(a, bt.t(), sa, sb, torch.bfloat16, vb, 0, True)
             torch.cuda.synchronize()
-        finally:
-            lib.sglk_debug_set_stream_k_mode(prev)
         nbad = int((ya.view(torch.int16) != yb.view(torch.int16)).sum())
         ref_ok = ""
         if M * N * K <= 2e10:
