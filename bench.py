@@ -5,14 +5,21 @@ Workload (BASELINE.json configs[4], the largest config and the one that shards):
     DeepSeek-V3 dense MLP prefill, M=16384 tokens, N=18432, K=7168, bf16 activations,
     e4m3 weights with 128x128 fp32 block scales.
 A *step* is one pass of the hot path over one batch:
-    per_token_group_quant_8bit (bf16 -> e4m3 + 1x128 fp32 scales, column-major)  ->  fp8_blockwise_scaled_mm
+    per_token_group_quant_8bit (bf16 -> e4m3 + 1x128 fp32 scales, row-major [M, K/128])  ->  fp8_blockwise_scaled_mm
 With --gpus N the weight is column-(N-)sharded over the N ranks (one process per GPU, torchrun),
 activations replicated; total work is fixed, so scaling is "strong".  The all-gather that
 reassembles [M, N] is timed separately ("with_all_gather") because only some consumers need it.
 
 Prints ONE JSON line (rank 0).  `--impl reference` times the reference's own CPU implementation
 (the torch oracle restated in oracle/torch_oracle.py; the reference's native code is Intel SYCL and
-cannot run here) on a bounded sample of the same workload on the host cores.
+cannot run here) on a bounded sample of the same workload on ALL host cores (torchrun exports
+OMP_NUM_THREADS=1; the CPU legs set the thread count back to os.cpu_count() so that the reference arm is the
+same machine at every N).
+
+At N=1 the line also carries `configs`: one sub-record per remaining BASELINE.json config (2: group-quant sweep
+points, 3: DSv3 decode projections timed GPU-side in a CUDA graph, 4: Llama-3-70B gate/up prefill), each with its
+own roofline.  At N>1 `with_all_gather.fused*` carry `matches_nccl` (bitwise equality with the NCCL-gathered result,
+MIN over ranks); a false flag makes the run exit non-zero.
 """
 import argparse
 import json
@@ -27,12 +34,38 @@ sys.path[:0] = [ROOT, os.path.join(ROOT, "sgl-kernel-xpu_b200")]
 M_FULL, N_FULL, K_FULL = 16384, 18432, 7168
 WORKLOAD = "dsv3_dense_mlp_prefill_M16384_N18432_K7168_group128"
 METRIC = "FP8 blockwise GEMM TFLOPS (% dense-FP8 peak); group-quant GB/s (% HBM)"
-# dram__bytes_read.sum + dram__bytes_write.sum per launch from the `ncu --set full` captures of this command
-# (profiles/r01d_gemm_ncu_metrics.csv, profiles/r01d_quant_ncu_metrics.csv); algorithmic: 853 MB / 356 MB
-# (GEMM: 2.41 GB before the rasterisation group went from 8 to 16 m-blocks, profiles/r01b_*; the r01d capture is of
-# variant 13 — the default since, 29, has the same tiles, ring contents and rasterisation, only a second staging box)
-GEMM_DRAM_TRAFFIC_BYTES = 1_164_657_000 + 590_170_112
-QUANT_DRAM_TRAFFIC_BYTES = 234_919_936 + 66_678_272
+PROFILES = os.path.join(ROOT, "profiles")
+_UNIT = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9, "Tbyte": 1e12}
+
+
+def profile_traffic(kernel, want=None):
+    """dram__bytes_read.sum + dram__bytes_write.sum of one launch, read from the newest committed
+    `ncu --set full` summary profiles/rNN*_<kernel>_ncu_metrics.csv (tools/summarize_profiles.py writes them from
+    the capture of THIS command).  `want`: substring the captured kernel's name must contain (the template
+    arguments of the variant that is timed) — a capture of another variant is not reported as this one's traffic.
+    Returns (bytes or None, source description)."""
+    import csv
+    import glob
+
+    files = sorted(glob.glob(os.path.join(PROFILES, f"r*_{kernel}_ncu_metrics.csv")))
+    for path in reversed(files):
+        rows = {r[0]: r for r in csv.reader(open(path)) if r}
+        name = rows.get("Kernel Name", ["", "", ""])[2]
+        if want and want not in name:
+            continue
+        try:
+            rd, wr = rows["dram__bytes_read.sum"], rows["dram__bytes_write.sum"]
+            total = float(rd[2]) * _UNIT[rd[1]] + float(wr[2]) * _UNIT[wr[1]]
+        except (KeyError, ValueError, IndexError):
+            continue
+        return int(total), f"{os.path.basename(path)}: {name[:120]}"
+    return None, None
+
+
+# template arguments of fp8_blockwise_gemm_kernel per product variant id (csrc/gemm.cu launch_by_id): what the
+# kernel name in an ncu capture must contain for its traffic to be reported against that variant
+GEMM_TEMPLATE_ARGS = {13: "<256, 6, 2, __nv_bfloat16, 1, 0, 1, 0, 0, 0, 0>", 29: "<256, 5, 2, __nv_bfloat16, 1, 0, 1, 0, 0, 0, 3>",
+                      0: "<128, 6, 1, __nv_bfloat16, 1, 0, 0, 0, 0, 0, 0>"}
 FP8_NOMINAL_TFLOPS = 4500.0
 HBM_NOMINAL_GBS = 8000.0
 
@@ -97,6 +130,20 @@ class ClockSampler(threading.Thread):
                 "reasons": sorted(self.reasons), "samples": len(s)}
 
 
+def use_all_host_threads():
+    """torchrun exports OMP_NUM_THREADS=1 to every rank; the CPU legs run on rank 0 alone and take the whole host."""
+    import torch
+
+    n = os.cpu_count() or 1
+    try:
+        n = len(os.sched_getaffinity(0))
+    except (AttributeError, OSError):
+        pass
+    if torch.get_num_threads() != n:
+        torch.set_num_threads(n)
+    return n
+
+
 def cpu_oracle_sample(rows, reps_budget_s=12.0, min_reps=2, max_reps=16):
     """Time the CPU oracle (quant + dequantised matmul, all host threads) on the first `rows` tokens of
     the workload.  Returns (best seconds, reps, threads)."""
@@ -104,6 +151,7 @@ def cpu_oracle_sample(rows, reps_budget_s=12.0, min_reps=2, max_reps=16):
 
     from oracle import torch_oracle as O
 
+    use_all_host_threads()
     g = torch.Generator().manual_seed(42)
     x = torch.randn(rows, K_FULL, generator=g).to(torch.bfloat16)
     wq_t = ((torch.rand(N_FULL, K_FULL, generator=g) - 0.5) * 896).to(torch.float8_e4m3fn).t()
@@ -146,6 +194,126 @@ def run_reference(args, rank, world):
     print(json.dumps(line), flush=True)
 
 
+def other_configs(torch, sgl_kernel, dev, peaks, flush):
+    """Sub-records for BASELINE.json configs 2-4 (the headline line is config 5), rank 0 / one GPU.
+    Shapes: the reference's own sweeps, benchmark/bench_per_token_group_quant_8bit.py:213-252 (byte model
+    3*M*K + 4*M*K/128) and benchmark/bench_fp8_blockwise_gemm.py:16-52 (DeepSeek-V3 / Llama weight shapes).
+      * quant, K=7168, M in {4096, 32768}, row- and column-major scales: CUDA events, 256 MiB read-only L2 flush
+        between launches, median of 9; roofline = algorithmic bytes / t against the measured copy bandwidth;
+      * decode GEMM, N in {2112, 24576}, K=7168, M in {1, 16, 64, 128, 256}: GPU-side time of 16-17 launches in one
+        CUDA graph (median of 9 replays); the launches rotate over enough weight copies to exceed 2 x L2
+        (17 x 15 MB, 2 x 176 MB) so that every launch streams its weight from HBM; roofline = algorithmic bytes
+        M*K + N*K + 2*M*N + scales over t against the measured copy bandwidth; each result is compared with the
+        128-row tile kernel (variant 0) on the same inputs;
+      * Llama-3-70B gate/up prefill M=8192 N=28672 K=8192: CUDA events with L2 flush, median of 7; roofline tensor."""
+    from sgl_kernel import _ops
+
+    lib = sgl_kernel._lib.load()
+    hbm, fp8_peak = peaks["hbm_gbs"], 2.0 * peaks["bf16_tflops"]
+    recs = []
+
+    def median_events(fn, reps, warm=3):
+        for _ in range(warm):
+            fn()
+        ts = []
+        for _ in range(reps):
+            flush.view(torch.int64).sum()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            fn()
+            e1.record()
+            e1.synchronize()
+            ts.append(e0.elapsed_time(e1))
+        return sorted(ts)[len(ts) // 2] * 1e3                      # us
+
+    # ---- config 2: group quant sweep points ----
+    K = 7168
+    for m in (4096, 32768):
+        x = torch.randn(m, K, device=dev, dtype=torch.bfloat16)
+        q = torch.empty(m, K, dtype=torch.float8_e4m3fn, device=dev)
+        for col in (False, True):
+            sc = sgl_kernel.create_per_token_group_quant_fp8_output_scale((m, K), dev, 128, col, col, False)
+            us = median_events(lambda: sgl_kernel.sgl_per_token_group_quant_8bit(x, q, sc, 128, 1e-10, -448.0, 448.0,
+                                                                                  enable_v2=False), 9)
+            by = 3 * m * K + 4 * m * (K // 128)
+            recs.append({"config": f"2 quant K=7168 M={m} {'column' if col else 'row'}-major scales", "op": "sgl_per_token_group_quant_8bit",
+                         "M": m, "K": K, "us": round(us, 2), "value": by / us / 1e3, "unit": "GB/s",
+                         "timing": "cuda events, L2 flushed between launches, median of 9",
+                         "roofline": {"bound": "hbm", "achieved": by / us / 1e3, "peak": hbm, "unit": "GB/s",
+                                      "frac": by / us / 1e3 / hbm, "algorithmic_bytes": by}})
+        del x, q
+
+    # ---- config 3: DeepSeek-V3 decode projections, GPU-side in a CUDA graph ----
+    def graph_us(fns, reps=9):
+        # warm up ON the capture stream: the stream-K workspace is cached per (device, stream) and never created
+        # inside a capture, where the op would fall back to whole tiles (sgl_kernel/_ops.py _get_workspace)
+        g, st = torch.cuda.CUDAGraph(), torch.cuda.Stream()
+        with torch.cuda.stream(st):
+            for f in fns[:2]:
+                f()
+        torch.cuda.synchronize()
+        with torch.cuda.stream(st):
+            with torch.cuda.graph(g, stream=st):
+                for f in fns:
+                    f()
+        g.replay()
+        torch.cuda.synchronize()
+        ts = []
+        for _ in range(reps):
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            g.replay()
+            e1.record()
+            e1.synchronize()
+            ts.append(e0.elapsed_time(e1) / len(fns))
+        return sorted(ts)[len(ts) // 2] * 1e3
+
+    for N in (2112, 24576):
+        copies = -(-(256 << 20) // (N * K))
+        launches = copies * -(-16 // copies)
+        bts = [(torch.rand(N, K, device=dev) - 0.5).mul_(896).to(torch.float8_e4m3fn) for _ in range(copies)]
+        sb = (torch.randn(-(N // -128), K // 128, device=dev) * 1e-3).t()
+        for M in (1, 16, 64, 128, 256):
+            a = (torch.rand(M, K, device=dev) - 0.5).mul_(896).to(torch.float8_e4m3fn)
+            sa = torch.randn(M, K // 128, device=dev) * 1e-3
+            outs = [torch.empty(M, N, dtype=torch.bfloat16, device=dev) for _ in range(2)]
+            y = sgl_kernel.fp8_blockwise_scaled_mm(a, bts[0].t(), sa, sb, torch.bfloat16)
+            y0 = _ops._gemm(a, bts[0].t(), sa, sb, torch.bfloat16, 0)
+            rel = float((y.float() - y0.float()).norm() / y0.float().norm())
+            fns = [(lambda i=i: sgl_kernel.fp8_blockwise_scaled_mm(a, bts[i % copies].t(), sa, sb, torch.bfloat16))
+                   for i in range(launches)]
+            us = graph_us(fns)
+            by = M * K + N * K + 2 * M * N + 4 * (M * (K // 128) + (K // 128) * -(N // -128))
+            vid = lib.sglk_gemm_pick_variant(M, N, K)
+            recs.append({"config": f"3 DSv3 decode M={M} N={N} K={K}", "op": "fp8_blockwise_scaled_mm", "M": M, "N": N, "K": K,
+                         "us": round(us, 2), "value": 2.0 * M * N * K / us / 1e6, "unit": "TFLOPS",
+                         "gemm_variant": lib.sglk_gemm_variant_name(vid).decode(), "gemm_variant_id": vid,
+                         "rel_err_vs_tile_kernel": rel, "matches_tile_kernel": rel <= 2e-3,
+                         "timing": f"GPU-side: {launches} launches in one CUDA graph rotating over {copies} weight copies "
+                                   f"({copies * N * K / 1e6:.0f} MB > 2 x L2), median of 9 replays",
+                         "roofline": {"bound": "hbm", "achieved": by / us / 1e3, "peak": hbm, "unit": "GB/s",
+                                      "frac": by / us / 1e3 / hbm, "algorithmic_bytes": by}})
+            del outs
+        del bts
+
+    # ---- config 4: Llama-3-70B gate/up prefill ----
+    M, N, K4 = 8192, 28672, 8192
+    a = (torch.rand(M, K4, device=dev) - 0.5).mul_(896).to(torch.float8_e4m3fn)
+    bt = (torch.rand(N, K4, device=dev) - 0.5).mul_(896).to(torch.float8_e4m3fn)
+    sa = (torch.rand(M, K4 // 128, device=dev) + 0.5) * 1e-3
+    sb = ((torch.rand(N // 128, K4 // 128, device=dev) + 0.5) * 1e-3).t()
+    us = median_events(lambda: sgl_kernel.fp8_blockwise_scaled_mm(a, bt.t(), sa, sb, torch.bfloat16), 7)
+    fl = 2.0 * M * N * K4
+    vid = lib.sglk_gemm_pick_variant(M, N, K4)
+    recs.append({"config": f"4 Llama-3-70B gate/up prefill M={M} N={N} K={K4}", "op": "fp8_blockwise_scaled_mm", "M": M, "N": N,
+                 "K": K4, "us": round(us, 1), "value": fl / us / 1e6, "unit": "TFLOPS",
+                 "gemm_variant": lib.sglk_gemm_variant_name(vid).decode(), "gemm_variant_id": vid,
+                 "timing": "cuda events, L2 flushed between launches, median of 7",
+                 "roofline": {"bound": "tensor", "achieved": fl / us / 1e6, "peak": fp8_peak, "unit": "TFLOP/s",
+                              "frac": fl / us / 1e6 / fp8_peak, "algorithmic_flops": fl}})
+    return recs
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -155,6 +323,7 @@ def main():
     ap.add_argument("--cpu-rows", type=int, default=1024, help="tokens in the CPU-oracle sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-configs", action="store_true", help="skip the sub-records of BASELINE configs 2-4 (N=1 only)")
     ap.add_argument("--m", type=int, default=M_FULL, help="debug only: override token count")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
@@ -239,6 +408,14 @@ def main():
 
     # ---- step + all-gather of the output panels (only for consumers that need [M, N]) ----
     with_gather = None
+    gather_mismatch = False
+
+    def same_on_all_ranks(a, b):
+        """bitwise equality of two [M, N] results, MIN over ranks"""
+        ok = torch.tensor([1 if torch.equal(a, b) else 0], device=dev, dtype=torch.int32)
+        dist.all_reduce(ok, op=dist.ReduceOp.MIN)
+        return bool(ok.item())
+
     if world > 1:
         full = torch.empty(M, N, dtype=torch.bfloat16, device=dev)
         staged_unused = None
@@ -256,7 +433,8 @@ def main():
         dist.all_reduce(tg, op=dist.ReduceOp.MAX)
         with_gather = {"ms_per_step": float(tg.item()), "value": 2.0 * M * N * K / (float(tg.item()) * 1e-3) / 1e12,
                        "unit": "TFLOPS", "collective": "nccl all_gather_into_tensor + panel interleave copy"}
-        del full, staged_unused
+        sharded.gather(step(), full)          # the NCCL-gathered [M, N] the fused forms must reproduce bit for bit
+        del staged_unused
         # fused form: the GEMM epilogue TMA-stores each output box into every peer's [M, N] buffer over NVLink
         try:
             sharded.enable_fused_gather(M)
@@ -272,8 +450,10 @@ def main():
             barrier()
             tf = torch.tensor([sum(a.elapsed_time(b) for a, b in evf) / args.steps], device=dev, dtype=torch.float64)
             dist.all_reduce(tf, op=dist.ReduceOp.MAX)
+            ok_uni = same_on_all_ranks(sharded.forward_fused_gather(x), full)
+            gather_mismatch |= not ok_uni
             with_gather["fused"] = {
-                "ms_per_step": float(tf.item()), "value": 2.0 * M * N * K / (float(tf.item()) * 1e-3) / 1e12, "unit": "TFLOPS",
+                "matches_nccl": ok_uni, "ms_per_step": float(tf.item()), "value": 2.0 * M * N * K / (float(tf.item()) * 1e-3) / 1e12, "unit": "TFLOPS",
                 "collective": "none (NCCL-free): GEMM epilogue TMA-stores to peer-mapped symmetric memory + 2 device barriers",
                 "nvlink_bytes_in_per_rank": int(M * (N - n_loc) * 2)}
             # NVLS multicast form: each rank sends its panel once, the NVSwitch replicates it
@@ -289,11 +469,14 @@ def main():
             barrier()
             tm = torch.tensor([sum(a.elapsed_time(b) for a, b in evm) / args.steps], device=dev, dtype=torch.float64)
             dist.all_reduce(tm, op=dist.ReduceOp.MAX)
+            ok_mc = same_on_all_ranks(sharded.forward_fused_gather(x, multicast=True), full)
+            gather_mismatch |= not ok_mc
             with_gather["fused_multicast"] = {
-                "ms_per_step": float(tm.item()), "value": 2.0 * M * N * K / (float(tm.item()) * 1e-3) / 1e12, "unit": "TFLOPS",
+                "matches_nccl": ok_mc, "ms_per_step": float(tm.item()), "value": 2.0 * M * N * K / (float(tm.item()) * 1e-3) / 1e12, "unit": "TFLOPS",
                 "collective": "none (NCCL-free): GEMM epilogue multimem.st to the NVLS multicast mapping + 2 device barriers"}
         except Exception as e:  # noqa: BLE001
             with_gather["fused_error"] = str(e)[:200]
+        del full
 
     # ---- end to end through the public API with HOST buffers (pinned), copies inside the timed region ----
     e2e = None
@@ -333,11 +516,28 @@ def main():
                         "host memory, every step; phases of consecutive steps overlap on three streams; wall clock over all "
                         "steps incl. final sync, max over ranks; bytes are whole-job (all ranks)")}
 
+    # CPU baseline on rank 0 with every host thread; the other ranks sleep on the rendezvous store meanwhile (a
+    # device-side barrier would keep one host thread per rank spinning in cudaStreamSynchronize and steal cores)
+    cpu_sample = None
+    store = dist.distributed_c10d._get_default_store() if world > 1 else None
+    if rank == 0 and not args.no_cpu_baseline:
+        cpu_sample = cpu_oracle_sample(args.cpu_rows)
+    if store is not None:
+        import datetime
+
+        if rank == 0:
+            store.set("sglk_bench_cpu_done", "1")
+        else:
+            store.wait(["sglk_bench_cpu_done"], datetime.timedelta(minutes=15))
+
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
+        if gather_mismatch:
+            raise SystemExit(1)
         return
 
+    lib = sgl_kernel._lib.load()
     peaks = load_peaks()
     fp8_peak = 2.0 * peaks["bf16_tflops"]
     gemm_tflops_rank = 2.0 * M * n_loc * K / (t_gemm * 1e-3) / 1e12
@@ -345,9 +545,18 @@ def main():
     quant_gbs = quant_bytes / (t_quant * 1e-3) / 1e9
     value = 2.0 * M * N * K / (t_step * 1e-3) / 1e12
 
+    # ncu DRAM traffic of the kernels that were just timed (only meaningful for the full single-GPU shape the
+    # capture was taken on; the name check ties it to the variant's template instantiation)
+    gemm_traffic = gemm_traffic_src = quant_traffic = quant_traffic_src = None
+    variant_id = lib.sglk_gemm_pick_variant(M, n_loc, K)
+    if M == M_FULL:
+        quant_traffic, quant_traffic_src = profile_traffic("quant", "ptgq_kernel")
+        if world == 1:
+            gemm_traffic, gemm_traffic_src = profile_traffic("gemm", GEMM_TEMPLATE_ARGS.get(variant_id, "\0"))
+
     cpu_baseline = None
-    if world == 1 and not args.no_cpu_baseline:
-        best, reps, threads = cpu_oracle_sample(args.cpu_rows)
+    if cpu_sample is not None:
+        best, reps, threads = cpu_sample
         cpu_baseline = {
             "value": 2.0 * args.cpu_rows * N * K / best / 1e12, "unit": "TFLOPS", "cores": threads, "kind": "port",
             "sample": f"first {args.cpu_rows} of {M} tokens, full N={N} K={K}: oracle quant + fp32 dequant torch.mm, "
@@ -362,27 +571,34 @@ def main():
                    "parallelism": f"column(N)-sharded x{world}, activations replicated" if world > 1 else "single GPU",
                    "step": "per_token_group_quant_8bit (row-major scales) + fp8_blockwise_scaled_mm, no collective in value",
                    "l2": "256 MiB read-only flush between steps (outside the events); inputs 235 MB + weights > L2",
-                   "gemm_variant": sgl_kernel._lib.load().sglk_gemm_variant_name(
-                       sgl_kernel._lib.load().sglk_gemm_pick_variant(M, n_loc, K)).decode()},
+                   "gemm_variant": lib.sglk_gemm_variant_name(variant_id).decode(), "gemm_variant_id": variant_id},
         "gemm_tflops": 2.0 * M * N * K / (t_gemm * 1e-3) / 1e12, "gemm_ms": t_gemm,
         "quant_gbps": quant_gbs, "quant_ms": t_quant,
         "roofline": {"bound": "tensor", "achieved": gemm_tflops_rank, "peak": fp8_peak, "unit": "TFLOP/s",
                      "frac": gemm_tflops_rank / fp8_peak,
-                     "traffic": (GEMM_DRAM_TRAFFIC_BYTES if (world == 1 and M == M_FULL) else None),
+                     "traffic": gemm_traffic, "traffic_source": gemm_traffic_src,
                      "kernel": "fp8_blockwise_gemm_kernel", "algorithmic_flops_per_launch": 2.0 * M * n_loc * K,
                      "peak_source": f"2 x {peaks['source']} cuBLAS bf16 burst ({peaks['bf16_tflops']} TF/s): fp8 dense = 2x bf16 rate; "
                                     f"frac of nominal 4500 TF/s = {gemm_tflops_rank / FP8_NOMINAL_TFLOPS:.3f}"},
         "roofline_quant": {"bound": "hbm", "achieved": quant_gbs, "peak": peaks["hbm_gbs"], "unit": "GB/s",
                            "frac": quant_gbs / peaks["hbm_gbs"],
-                           "traffic": (QUANT_DRAM_TRAFFIC_BYTES if M == M_FULL else None), "kernel": "ptgq_kernel",
+                           "traffic": quant_traffic, "traffic_source": quant_traffic_src, "kernel": "ptgq_kernel",
                            "algorithmic_bytes_per_launch": quant_bytes,
                            "peak_source": f"{peaks['source']} copy bandwidth; frac of nominal 8000 GB/s = {quant_gbs / HBM_NOMINAL_GBS:.3f}"},
         "cpu_baseline": cpu_baseline, "e2e": e2e, "with_all_gather": with_gather,
         "gpu_launches": 2 * args.steps * world, "clocks": clocks, "wall_s_timed_region": t_wall,
     }
+    if world == 1 and not args.no_configs and M == M_FULL:
+        del out, x, xq, xs, layer, wq, ws
+        torch.cuda.empty_cache()
+        t0 = time.perf_counter()
+        line["configs"] = other_configs(torch, sgl_kernel, dev, peaks, flush)
+        line["configs_wall_s"] = round(time.perf_counter() - t0, 2)
     print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
+    if gather_mismatch:
+        raise SystemExit("fused gather result differs from the NCCL-gathered result (see with_all_gather.*.matches_nccl)")
 
 
 if __name__ == "__main__":

@@ -1066,6 +1066,7 @@ static const Variant kVariants[] = {
     {"swapab_cta2", 128, 0, 2, false, false, true},                  // decode, CTA pair: 256 weight rows, tokens split over the pair
 };
 constexpr int kDecodeVariant1 = 30, kDecodeVariant2 = 31;
+constexpr int kDecodeMaxTokens = 16;   // the default dispatch uses the swap-AB kernel up to here (pick_variant)
 constexpr int kFirstStampVariant = 15, kLastStampVariant = 22;
 constexpr int kNumVariants = int(sizeof(kVariants) / sizeof(kVariants[0]));
 
@@ -1168,12 +1169,15 @@ static bool tma_store_ok(const void* C, int64_t ldc, int out_bytes) {
 // prefill shape, whole GPU suite green on it.  Decode (M <= 256, plain [M, N] output): the swap-AB kernel of
 // gemm_decode.cu, single CTAs for a few tokens, CTA pairs (tokens split over the pair: half the L2 -> smem traffic of the
 // activation tile) from 33 tokens up.
-static int pick_variant(int64_t M, int64_t N, int64_t K, bool plain_output) {
-  // swap-AB decode kernel (gemm_decode.cu): weight rows on the MMA's M axis, <= 32 tokens on its N axis.  Measured in a
-  // CUDA graph on B200 (tools/decode_bench.py, N=24576 K=7168): 35.8 / 36.1 / 38.8 us at M = 1 / 16 / 32 against 41.0
-  // for the 128-row tile kernel below; from 64 tokens on the token-major kernel wins again (41.5 vs 44.6 us), so the
-  // cut is at 32.  (no plain output: fused all-gather / fused quantisation epilogues live in the prefill kernel)
-  if (plain_output && M <= 32 && decode_supported(M, N, K)) return kDecodeVariant2;
+static int pick_variant(int64_t M, int64_t N, int64_t K, bool plain_output, int num_sms = 0) {
+  // swap-AB decode kernel (gemm_decode.cu): weight rows on the MMA's M axis, <= 16 tokens on its N axis.  Measured in a
+  // CUDA graph on B200 (tools/decode_bench.py, K=7168), swap-AB against the 128-row tile kernel below with stream-K:
+  // N=24576: 35.8 / 36.1 us (CTA pairs, whole tiles) against 36.6 at M = 1 / 16, 38.7 against 37.2 at M = 32;
+  // N=2112: 10.8 us (single CTAs, 4 workers per tile) against 12.9 at M = 16.  The pair kernel halves the activation
+  // traffic per weight byte and wins when there is a tile for every pair; below that the single-CTA form has twice
+  // the tiles to spread.  (no plain output: the fused all-gather / quantisation epilogues live in the tile kernel)
+  if (plain_output && M <= kDecodeMaxTokens && decode_supported(M, N, K))
+    return (N + 127) / 128 < (num_sms > 0 ? num_sms : 148) ? kDecodeVariant1 : kDecodeVariant2;
   // a handful of wide tiles on a narrow weight (N=2112, 129 <= M <= 256: 9 pair tiles for 74 pairs): 128-wide single-CTA
   // tiles give stream-K twice the units to balance
   if (M > 128 && M <= 256 && N < 4096) return 0;
@@ -1276,7 +1280,7 @@ static int gemm_entry(const void* A, const void* B, const float* sa, const float
   if ((reinterpret_cast<uintptr_t>(A) & 15) || (reinterpret_cast<uintptr_t>(B) & 15)) return SGLK_E_STRIDE;
   if (M >= (int64_t(1) << 31) || N >= (int64_t(1) << 31) || K >= (int64_t(1) << 31)) return SGLK_E_SHAPE;
   const bool plain_output = !qo && num_extra == 0 && !mc_ptr;
-  if (variant < 0) variant = pick_variant(M, N, K, plain_output);
+  if (variant < 0) variant = pick_variant(M, N, K, plain_output, num_sms);
   if (!variant_available(variant)) return SGLK_E_VARIANT;
   if (variant == kDecodeVariant1 || variant == kDecodeVariant2) {
     if (!plain_output || !decode_supported(M, N, K)) return SGLK_E_VARIANT;
@@ -1515,7 +1519,7 @@ extern "C" int sglk_fp8_blockwise_scaled_mm_quant(const void* A, const void* B, 
 
 extern "C" int64_t sglk_gemm_workspace_bytes(int64_t M, int64_t N, int64_t K, int variant, int num_sms, int flags) {
   if (M <= 0 || N <= 0 || K <= 0) return 0;
-  if (variant < 0) variant = sglk::pick_variant(M, N, K, true);
+  if (variant < 0) variant = sglk::pick_variant(M, N, K, true, num_sms);
   if (!sglk::variant_available(variant)) return 0;
   if (num_sms <= 0) num_sms = sglk::device_sm_count();
   if (variant == sglk::kDecodeVariant1 || variant == sglk::kDecodeVariant2)

@@ -606,18 +606,27 @@ static DecodePlan make_decode_plan(int64_t M, int64_t N, int64_t K, int cg, int 
   const int T = pl.num_tiles, G = pl.num_kb;
   const int whole = T / w0, rem = T % w0;
   const int64_t rem_units = int64_t(rem) * G;
+  // Schedule, from measurements in a CUDA graph on B200 (tools/decode_bench.py, tools/decode_split.py; K=7168):
+  //  * at least one tile per worker (T >= W, e.g. N=24576): whole tiles.  The kernel is HBM-bound there and a second,
+  //    partly filled wave still saturates the memory system (pair kernel, 96 tiles on 74 pairs: 35.8 us whole against
+  //    39.5 us with the remainder tiles cut stream-K style — the fix-up traffic costs more than the balance gains);
+  //  * fewer tiles than workers (N <= 9472 / 18944): each tile is split over min(W / T, 4) workers — more than four
+  //    partial tiles per finisher cost more than the shorter K ranges gain (N=2112, M=16: 15.0 / 12.8 / 11.3 / 10.8 /
+  //    10.9 / 10.9 / 14.0 us at 1 / 2 / 3 / 4 / 6 / 8 / 12 workers per tile).
+  // SGLK_GEMM_STREAMK_FORCE keeps the general hybrid (remainder tiles split over all workers) for tests and tuning,
+  // and bits 16..23 of flags override the workers per tile.
+  const int sk_mode = (flags & SGLK_GEMM_STREAMK_FORCE) ? 1 : ((flags & SGLK_GEMM_STREAMK_NEVER) ? -1 : 0);
   int sk_workers = w0;
+  bool want = sk_mode > 0;
   if (whole == 0) {
-    const int per_tile = (flags >> 16) & 0xFF;
+    int per_tile = (flags >> 16) & 0xFF;
+    if (per_tile == 0 && sk_mode == 0) per_tile = w0 / T > 4 ? 4 : w0 / T;
     if (per_tile > 0 && int64_t(T) * per_tile < sk_workers) sk_workers = T * per_tile;
+    if (sk_mode == 0) want = sk_workers > T;
   }
   if (rem_units < sk_workers) sk_workers = int(rem_units);   // every stream-K worker owns at least one unit
-  const int64_t fixup = (whole > 0 ? 2 : 6) + pl.nt / 32;
-  const int64_t cost_whole = int64_t(whole + (rem ? 1 : 0)) * G;
-  const int64_t cost_hybrid = int64_t(whole) * G + (rem_units + sk_workers - 1) / (sk_workers > 0 ? sk_workers : 1) + fixup;
-  const int sk_mode = (flags & SGLK_GEMM_STREAMK_FORCE) ? 1 : ((flags & SGLK_GEMM_STREAMK_NEVER) ? -1 : 0);
   const bool possible = have_ws && G >= 2 && rem > 0 && int64_t(T) * cg * kew * 4 <= kCounterAreaBytes;
-  pl.stream_k = (possible && sk_mode >= 0 && (sk_mode > 0 || cost_hybrid < cost_whole)) ? 1 : 0;
+  pl.stream_k = (possible && sk_mode >= 0 && want) ? 1 : 0;
   pl.sk_workers = pl.stream_k ? sk_workers : 0;
   pl.workers = pl.stream_k ? (whole > 0 ? w0 : sk_workers) : (T < w0 ? T : w0);
   if (pl.workers < 1) pl.workers = 1;

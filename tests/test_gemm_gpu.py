@@ -360,13 +360,14 @@ def test_decode_kernel(variant, M, N, K, sched):
 
 
 def test_decode_is_the_default_for_small_m():
-    """the swap-AB kernel is the default exactly where it measured faster (M <= 32, gemm.cu pick_variant); larger
-    batches stay on the token-major tiles"""
+    """the swap-AB kernel is the default exactly where it measured faster (M <= 16, gemm.cu pick_variant): single CTAs
+    when the weight has fewer 128-row tiles than SMs, CTA pairs otherwise; larger batches stay on the token-major tiles"""
     lib = _lib.load()
+    for M in (1, 8, 16):
+        assert lib.sglk_gemm_pick_variant(M, 2112, 7168) == 30
+        assert lib.sglk_gemm_pick_variant(M, 24576, 7168) == 31
     for N in (2112, 24576):
-        for M in (1, 16, 32):
-            assert lib.sglk_gemm_pick_variant(M, N, 7168) == 31
-        for M in (33, 64, 128):
+        for M in (17, 32, 64, 128):
             assert lib.sglk_gemm_pick_variant(M, N, 7168) == 0
     assert lib.sglk_gemm_pick_variant(256, 2112, 7168) == 0
     assert lib.sglk_gemm_pick_variant(256, 24576, 7168) == 29

@@ -9,8 +9,12 @@ from sgl_kernel import _ops
 dev = "cuda"
 
 def graph_time(fn, n=20, reps=10):
-    fn(); torch.cuda.synchronize()
+    # warm up ON the capture stream: the stream-K workspace is cached per (device, stream) and is never created inside
+    # a capture (sgl_kernel/_ops.py _get_workspace) — without this the captured launches run whole tiles only
     g = torch.cuda.CUDAGraph(); st = torch.cuda.Stream()
+    with torch.cuda.stream(st):
+        fn()
+    torch.cuda.synchronize()
     with torch.cuda.stream(st):
         with torch.cuda.graph(g, stream=st):
             for _ in range(n): fn()
