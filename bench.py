@@ -504,10 +504,47 @@ def main():
             dist.all_reduce(te, op=dist.ReduceOp.MAX)
         # sanity: the host result of the last step is the device result
         e2e_ok = bool(torch.equal(out_hosts[(e2e_steps - 1) & 1][:64].to(dev), out[:64]))
+        # denominator: the same host->device and device->host byte volume per step as plain asynchronous copies
+        # (one cudaMemcpyAsync per direction per step, through Tensor.copy_(non_blocking=True)) on the same pinned
+        # buffers, two streams so that both PCIe directions run concurrently, every rank at once — no compute,
+        # no collective.  frac = copy time / e2e time: 1.0 means the pipeline is at the PCIe roofline.
+        chunk = -(-M // world)
+        r_lo, r_hi = min(rank * chunk, M), min((rank + 1) * chunk, M)
+        x_stage = torch.empty(max(r_hi - r_lo, 1), K, dtype=torch.bfloat16, device=dev)
+        s_up, s_dn = torch.cuda.Stream(dev), torch.cuda.Stream(dev)
+
+        def copies_only():
+            with torch.cuda.stream(s_up):
+                if r_hi > r_lo:
+                    x_stage[: r_hi - r_lo].copy_(x_host[r_lo:r_hi], non_blocking=True)
+            with torch.cuda.stream(s_dn):
+                out_hosts[0].copy_(out, non_blocking=True)
+
+        for _ in range(2):
+            copies_only()
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(e2e_steps):
+            copies_only()
+        s_up.synchronize()
+        s_dn.synchronize()
+        tc_local = (time.perf_counter() - t0) * 1e3 / e2e_steps
+        barrier()
+        tcp = torch.tensor([tc_local], device=dev, dtype=torch.float64)
+        if world > 1:
+            dist.all_reduce(tcp, op=dist.ReduceOp.MAX)
+        t_copy = float(tcp.item())
+        up_bytes, dn_bytes = int(M * K * 2), int(M * N * 2)
+        del x_stage
         e2e = {"value": 2.0 * M * N * K / (float(te.item()) * 1e-3) / 1e12, "unit": "TFLOPS",
                "ms_per_step": float(te.item()), "steps": e2e_steps,
                "h2d_bytes_per_step": int(x_host.numel() * 2), "d2h_bytes_per_step": int(M * N * 2),
                "matches_device_result": e2e_ok,
+               "roofline": {"bound": "pcie", "ms_copies_only": t_copy, "frac": t_copy / float(te.item()),
+                            "h2d_gbs": up_bytes / t_copy / 1e6, "d2h_gbs": dn_bytes / t_copy / 1e6,
+                            "what": "same H2D + D2H bytes per step as plain async copies on the same pinned buffers, both "
+                                    "directions concurrently on two streams, all ranks at once, no compute; whole-job GB/s"},
+               "frac": t_copy / float(te.item()),
                "note": ("sgl_kernel.HostStreamedFp8Linear: pinned host x -> HBM, quant + GEMM ops, result panel -> pinned host, "
                         "every step; the three phases of consecutive steps overlap on three streams; wall clock over "
                         "all steps incl. final sync; bytes are whole-job (all ranks)") if world == 1 else
