@@ -14,8 +14,15 @@ from .gemm import fp8_blockwise_scaled_mm, sgl_per_token_group_quant_8bit
 FP8_MAX = 448.0  # torch.finfo(torch.float8_e4m3fn).max
 
 
-def _ceil_align(x: int, a: int) -> int:
-    return (x + a - 1) // a * a
+def _round_up(v: int, to: int) -> int:
+    return -(-v // to) * to
+
+
+def _token_major_view(lead, tokens: int, tokens_alloc: int, cols: int, dtype, device) -> torch.Tensor:
+    """[*lead, tokens, cols] tensor whose TOKEN index is the unit-stride one ("column-major scales"): storage is
+    [*lead, cols, tokens_alloc], seen through swapped last axes and cut back to the tokens that exist."""
+    store = torch.empty(tuple(lead) + (cols, tokens_alloc), dtype=dtype, device=device)
+    return store.transpose(-1, -2).narrow(-2, 0, tokens)
 
 
 def create_per_token_group_quant_fp8_output_scale(
@@ -26,28 +33,27 @@ def create_per_token_group_quant_fp8_output_scale(
     scale_tma_aligned: bool,
     scale_ue8m0: bool,
 ) -> torch.Tensor:
-    """The four scale layouts of the reference's `create_fp8_output_scale`
-    (tests/test_per_token_group_quant_8bit.py:86-126): row-major fp32; column-major fp32;
-    column-major fp32 with rows padded to 4 ("TMA aligned"); UE8M0 packed int32, column-major."""
+    """Allocate the scale tensor of `sgl_per_token_group_quant_8bit` for codes of shape `x_shape`, in one of the four
+    layouts callers of the reference use (contract: tests/test_per_token_group_quant_8bit.py:86-126):
+
+      row-major fp32              [..., tokens, groups]                      (neither flag)
+      column-major fp32           same shape, token stride 1                 (column_major_scales)
+      ... TMA aligned             token extent of the storage padded to 4    (+ scale_tma_aligned)
+      packed UE8M0                int32 words of four exponent bytes, [..., tokens, ceil(groups/4)], token stride 1,
+                                  storage padded to 4 tokens; group size 128 (+ scale_ue8m0)"""
+    *lead, tokens, hidden = tuple(x_shape)
     if scale_ue8m0:
-        assert column_major_scales and scale_tma_aligned
-        *x_batch, x_q_mn, x_q_k = x_shape
-        x_s_mn, x_s_k = x_q_mn, x_q_k // 128
-        aligned_mn = _ceil_align(x_s_mn, 4)
-        aligned_k = _ceil_align(x_s_k, 4)
-        return torch.empty((*x_batch, aligned_k // 4, aligned_mn), device=device, dtype=torch.int).transpose(-1, -2)[
-            ..., :x_s_mn, :
-        ]
-    if column_major_scales:
-        if scale_tma_aligned:
-            aligned_size = _ceil_align(x_shape[-2], 4)
-            return torch.empty(
-                tuple(x_shape[:-2]) + (x_shape[-1] // group_size, aligned_size), device=device, dtype=torch.float32
-            ).transpose(-1, -2)[: x_shape[-2], :]
-        return torch.empty(
-            (x_shape[-1] // group_size,) + tuple(x_shape[:-1]), device=device, dtype=torch.float32
-        ).permute(-1, -2)
-    return torch.empty(tuple(x_shape[:-1]) + (x_shape[-1] // group_size,), device=device, dtype=torch.float32)
+        if not (column_major_scales and scale_tma_aligned):
+            raise AssertionError("UE8M0 scales are column-major and TMA aligned")
+        words = _round_up(hidden // 128, 4) // 4
+        return _token_major_view(lead, tokens, _round_up(tokens, 4), words, torch.int32, device)
+    groups = hidden // group_size
+    if not column_major_scales:
+        return torch.empty((*lead, tokens, groups), dtype=torch.float32, device=device)
+    return _token_major_view(lead, tokens, _round_up(tokens, 4) if scale_tma_aligned else tokens, groups, torch.float32, device)
+
+
+_CODE_RANGE = {torch.float8_e4m3fn: (-FP8_MAX, FP8_MAX), torch.int8: (-128.0, 127.0)}
 
 
 def per_token_group_quant_fp8(
@@ -62,27 +68,27 @@ def per_token_group_quant_fp8(
     enable_v2: Optional[bool] = None,
     dtype: torch.dtype = torch.float8_e4m3fn,
 ) -> Tuple[torch.Tensor, torch.Tensor]:
-    """Allocate outputs and quantise — `sglapi_per_token_group_quant_fp8`,
-    tests/test_per_token_group_quant_8bit.py:129-164."""
-    assert x.shape[-1] % group_size == 0, "the last dimension of `x` cannot be divisible by `group_size`"
-    assert x.is_contiguous(), "`x` is not contiguous"
-    out_shape = (*x.shape[:-1], x.shape[-1] // (2 if fuse_silu_and_mul else 1))
-    x_q = torch.empty(out_shape, device=x.device, dtype=dtype)
-    x_s = create_per_token_group_quant_fp8_output_scale(
-        out_shape, x.device, group_size, column_major_scales, scale_tma_aligned, scale_ue8m0
-    )
-    if dtype == torch.int8:
-        qmin, qmax = -128.0, 127.0
-    else:
-        qmax = torch.finfo(dtype).max
-        qmin = -qmax
-    if x.shape[0] > 0:
-        if fuse_silu_and_mul and enable_v2 is None:
-            enable_v2 = True
-        sgl_per_token_group_quant_8bit(
-            x, x_q, x_s, group_size, eps, qmin, qmax, scale_ue8m0, fuse_silu_and_mul, masked_m, enable_v2
-        )
-    return x_q, x_s
+    """Allocating form of the op: returns (codes, scales) for `x` — the helper every caller of the reference wraps
+    around the in-place op (same keywords as tests/test_per_token_group_quant_8bit.py:129-164).  With
+    `fuse_silu_and_mul` the input is [..., 2*hidden] (gate | up) and the codes are [..., hidden]; that form and
+    `masked_m` exist only in the v2 op, which is then selected unless the caller says otherwise."""
+    if x.shape[-1] % group_size:
+        raise AssertionError("the last dimension of `x` must be divisible by `group_size`")
+    if not x.is_contiguous():
+        raise AssertionError("`x` is not contiguous")
+    hidden = x.shape[-1] // 2 if fuse_silu_and_mul else x.shape[-1]
+    codes_shape = tuple(x.shape[:-1]) + (hidden,)
+    codes = torch.empty(codes_shape, dtype=dtype, device=x.device)
+    scales = create_per_token_group_quant_fp8_output_scale(codes_shape, x.device, group_size, column_major_scales,
+                                                           scale_tma_aligned, scale_ue8m0)
+    if x.shape[0] == 0:
+        return codes, scales
+    lo, hi = _CODE_RANGE[dtype]
+    if enable_v2 is None and fuse_silu_and_mul:
+        enable_v2 = True
+    sgl_per_token_group_quant_8bit(x, codes, scales, group_size, eps, lo, hi, scale_ue8m0, fuse_silu_and_mul, masked_m,
+                                   enable_v2)
+    return codes, scales
 
 
 class Fp8BlockLinear:

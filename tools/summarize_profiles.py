@@ -82,5 +82,7 @@ dump_launches()
 dump_kernel("gemm")
 dump_kernel("quant")
 dump_kernel("decode")
+dump_kernel("decoden")
+dump_kernel("decode64")
 dump_kernel("tokenquant")
 print(sorted(os.listdir(P)))
