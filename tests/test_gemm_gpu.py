@@ -103,6 +103,39 @@ def test_reference_grid_slice(M, N, K, odt):
     check(out, ref)
 
 
+def device_baseline_scaled_mm(a, b, sa, sb, odt):
+    """the reference test's baseline evaluated where the reference evaluates it — on the device, in fp32
+    (tests/test_fp8_blockwise_gemm.py:23-63: broadcast both scale tensors over their 1x128 / 128x128 groups, dequantise,
+    one fp32 torch.mm, cast); restated with repeat_interleave"""
+    K, N = b.shape
+    sa_full = sa.repeat_interleave(128, dim=1)[:, :K]
+    sb_full = sb.repeat_interleave(128, dim=0)[:K].repeat_interleave(128, dim=1)[:, :N]
+    return torch.mm(sa_full * a.to(torch.float32), sb_full * b.to(torch.float32)).to(odt)
+
+
+@pytest.mark.parametrize("M", [1, 3, 5, 127, 128, 512, 1024, 4096])
+@pytest.mark.parametrize("N", [128, 512, 1024, 4096, 8192, 14080])
+@pytest.mark.parametrize("K", [512, 1024, 4096, 8192, 14080, 16384])
+@pytest.mark.parametrize("odt", [torch.bfloat16, torch.float16])
+def test_reference_grid_full(M, N, K, odt):
+    """ALL 576 cases of the reference's own accuracy grid (tests/test_fp8_blockwise_gemm.py:66-91): its generator
+    ((rand - 0.5) * 2 * 448 codes, randn * 1e-3 scales made column-major), its baseline on the device, its
+    assert_close(rtol=0.02, atol=1) — plus this repo's bars (rel-err <= 1e-2, cosine >= 0.9999)."""
+    assert not torch.backends.cuda.matmul.allow_tf32
+    g = torch.Generator(device=DEV).manual_seed(M * 1000003 + N * 1009 + K)
+    a = ((torch.rand(M, K, device=DEV, generator=g) - 0.5) * 2 * 448.0).clamp(-448.0, 448.0).to(torch.float8_e4m3fn)
+    b = ((torch.rand(N, K, device=DEV, generator=g) - 0.5) * 2 * 448.0).clamp(-448.0, 448.0).to(torch.float8_e4m3fn).t()
+    sa = (torch.randn(M, K // 128, device=DEV, generator=g) * 0.001).t().contiguous().t()
+    sb = (torch.randn(K // 128, N // 128, device=DEV, generator=g) * 0.001).t().contiguous().t()
+    ref = device_baseline_scaled_mm(a, b, sa, sb, odt)
+    out = sgl_kernel.fp8_blockwise_scaled_mm(a, b, sa, sb, odt)
+    torch.testing.assert_close(ref, out, rtol=0.02, atol=1)
+    of, rf = out.float(), ref.float()
+    rel = float((of - rf).norm() / rf.norm())
+    cos = float(torch.nn.functional.cosine_similarity(of.flatten(), rf.flatten(), dim=0))
+    assert rel <= REL_TOL and cos >= COS_TOL, f"rel_err={rel:.3e} cosine={cos:.6f}"
+
+
 def test_quant_then_gemm_chain_config1():
     """BASELINE.json config 1: M=128 N=4096 K=7168 group 128, the realistic chain, GPU vs CPU oracle.
     Quant is bit-exact, so both GEMMs see identical codes and scales."""

@@ -313,6 +313,99 @@ def test_v2_masked_moe_layout(experts, tokens, hidden, counts):
         assert torch.equal(got, expect), f"expert {e}"
 
 
+# ---- the reference's v2 grid (tests/test_per_token_group_quant_8bit_v2.py:326-402), every axis ----
+V2_TOKENS = [1, 4, 16, 64, 127, 128, 512, 1024, 4096, 8192]
+V2_HIDDEN = [128, 256, 384, 512, 1024, 1536, 1664, 2048, 4096, 7168, 16384]
+V2_LAYOUTS = [dict(column_major=False, tma_aligned=False, ue8m0=False), dict(column_major=True, tma_aligned=False, ue8m0=False),
+              dict(column_major=True, tma_aligned=True, ue8m0=False), dict(column_major=True, tma_aligned=True, ue8m0=True)]
+
+
+def _raw_bytes(t):
+    """the elements of t as bytes, in logical order (size-1 dimensions keep arbitrary strides through .contiguous(), which
+    view(uint8) then rejects: copy into a fresh dense tensor instead)"""
+    return torch.empty(t.shape, dtype=t.dtype).copy_(t).view(torch.uint8)
+
+
+def reference_v2_input(tokens, hidden):
+    """create_per_token_group_quant_test_data (:22-80): seed tokens*10000 + hidden, randn bf16 with a random ~50 % of
+    the elements (those where a second randn draw is < 0.001) scaled by 10"""
+    g = torch.Generator(device=DEV).manual_seed(tokens * 10000 + hidden)
+    x = torch.randn(tokens, hidden, device=DEV, dtype=torch.bfloat16, generator=g)
+    x[torch.randn(x.shape, device=DEV, generator=g) < 0.001] *= 10
+    return x
+
+
+@pytest.mark.parametrize("tokens", V2_TOKENS)
+@pytest.mark.parametrize("hidden", V2_HIDDEN)
+def test_v2_reference_grid(tokens, hidden):
+    """Every (tokens, hidden) of the reference's v2 grid, and inside each the group sizes 16/32/64/128 x {e4m3, int8} x
+    the four scale layouts (the reference skips UE8M0 with group != 128 and int8 with column-major scales, :760-765):
+    1870 op calls.  Bar: codes and scales BIT-EXACT against the CPU oracle — tighter than the reference's own
+    assert_all_close_or_tiny_diff / rtol 1e-3 — on every row up to 1 Mi elements and on 128 evenly spaced rows above
+    (rows are independent; the interleaved column-major addressing is undone on the whole tensor first)."""
+    xd = reference_v2_input(tokens, hidden)
+    rows = None if tokens * hidden <= (1 << 20) else torch.linspace(0, tokens - 1, 128).long().unique()
+    x_rows = (xd if rows is None else xd[rows.to(DEV)]).cpu().contiguous()
+    calls = 0
+    for group in (16, 32, 64, 128):
+        if hidden % group:
+            continue
+        G = hidden // group
+        oracle = {}
+        for dst in (torch.float8_e4m3fn, torch.int8):
+            for lay in V2_LAYOUTS:
+                if (lay["ue8m0"] and group != 128) or (dst == torch.int8 and lay["column_major"]):
+                    continue
+                q, s = sgl_kernel.per_token_group_quant_fp8(xd, group, EPS, lay["column_major"], lay["tma_aligned"],
+                                                            lay["ue8m0"], dtype=dst, enable_v2=True)
+                calls += 1
+                key = (dst, lay["ue8m0"])
+                if key not in oracle:
+                    if dst == torch.int8:
+                        oracle[key] = O.per_token_group_quant_int8_ref(x_rows, group, EPS)
+                    else:
+                        oracle[key] = O.per_token_group_quant_fp8_ref(x_rows, group, EPS, scale_ue8m0=lay["ue8m0"])
+                q_ref, s_ref = oracle[key]
+                s = s.cpu()
+                if lay["ue8m0"]:
+                    s = O.v2_column_major_deinterleave(O.unpack_ue8m0_words(s, G))
+                    s_ref = O.ue8m0_scale_bytes_ref(x_rows, group, EPS)
+                elif lay["column_major"]:
+                    s = O.v2_column_major_deinterleave(s)
+                q = q.cpu()
+                if rows is not None:
+                    q, s = q[rows], s[rows]
+                what = f"group {group} {dst} {lay}"
+                assert torch.equal(q.view(torch.uint8), q_ref.view(torch.uint8)), f"codes differ: {what}"
+                assert torch.equal(_raw_bytes(s), _raw_bytes(s_ref)), f"scales differ: {what}"
+    assert calls > 0
+
+
+@pytest.mark.parametrize("tokens", [1, 4, 8, 32, 512, 2048, 6144])
+@pytest.mark.parametrize("group_ranks", [8, 16, 32, 48])
+def test_v2_reference_grid_fused_silu_mul(tokens, group_ranks):
+    """second half of the reference's grid (:362-402): hidden 2048, group 128, packed UE8M0 column-major scales, fused
+    silu*mul, no masked layout (num_ranks is unused then, kept as a parameter so the 28 ids match the reference's).
+    The fused form is held to the REFERENCE'S tolerant rule (assert_all_close_or_tiny_diff, :599-628: no code off by
+    two or more, no sign flips, < 0.5 % off by one — < 4 % on tensors of <= 4096 codes), not to bit-exactness: silu
+    is evaluated with the device's exp, the oracle's with the host's.  The UE8M0 scale bytes are compared exactly."""
+    hidden = 2048
+    g = torch.Generator(device=DEV).manual_seed(tokens * 10000 + hidden)
+    xd = torch.randn(tokens, 2 * hidden, device=DEV, dtype=torch.bfloat16, generator=g)
+    xd[torch.randn(xd.shape, device=DEV, generator=g) < 0.001] *= 10
+    q, s = sgl_kernel.per_token_group_quant_fp8(xd, 128, EPS, True, True, True, fuse_silu_and_mul=True, enable_v2=True)
+    y = O.silu_and_mul_ref(xd.cpu()).contiguous()
+    q_ref, _ = O.per_token_group_quant_fp8_ref(y, 128, EPS, scale_ue8m0=True)
+    bytes_ref = O.ue8m0_scale_bytes_ref(y, 128, EPS)
+    got = O.v2_column_major_deinterleave(O.unpack_ue8m0_words(s.cpu(), hidden // 128))
+    assert torch.equal(got, bytes_ref), "UE8M0 scale bytes differ"
+    d = (q.cpu().view(torch.uint8).to(torch.int16) - q_ref.view(torch.uint8).to(torch.int16)).abs()
+    n = d.numel()
+    assert int((d >= 2).sum()) == 0          # (a sign flip is a distance of 128)
+    tiny = float((d == 1).sum()) / n
+    assert tiny < 0.005 or (tiny < 0.04 and n <= 4096)
+
+
 def test_v2_argument_checks():
     x = torch.randn(8, 256, dtype=torch.bfloat16, device=DEV)
     q = torch.empty(8, 256, dtype=torch.float8_e4m3fn, device=DEV)
