@@ -1064,8 +1064,9 @@ static const Variant kVariants[] = {
     {"n256_s5_cta2_tma_splitn_2box", 256, 5, 2, true, false, true},  // split-N pair tiles, two staging boxes per epilogue warp
     {"swapab_cta1", 128, 0, 1, false, false, true},                  // decode (gemm_decode.cu): weights are the MMA M side
     {"swapab_cta2", 128, 0, 2, false, false, true},                  // decode, CTA pair: 256 weight rows, tokens split over the pair
+    {"swapab_rows", 128, 0, 1, false, false, true},                  // decode, row-balanced: one contiguous weight-row range per CTA, no split-K
 };
-constexpr int kDecodeVariant1 = 30, kDecodeVariant2 = 31;
+constexpr int kDecodeVariant1 = 30, kDecodeVariant2 = 31, kRowsVariant = 32;
 constexpr int kDecodeMaxTokens = 16;   // the default dispatch uses the swap-AB kernel up to here (pick_variant)
 constexpr int kFirstStampVariant = 15, kLastStampVariant = 22;
 constexpr int kNumVariants = int(sizeof(kVariants) / sizeof(kVariants[0]));
@@ -1170,14 +1171,19 @@ static bool tma_store_ok(const void* C, int64_t ldc, int out_bytes) {
 // gemm_decode.cu, single CTAs for a few tokens, CTA pairs (tokens split over the pair: half the L2 -> smem traffic of the
 // activation tile) from 33 tokens up.
 static int pick_variant(int64_t M, int64_t N, int64_t K, bool plain_output, int num_sms = 0) {
-  // swap-AB decode kernel (gemm_decode.cu): weight rows on the MMA's M axis, <= 16 tokens on its N axis.  Measured in a
-  // CUDA graph on B200 (tools/decode_bench.py, K=7168), swap-AB against the 128-row tile kernel below with stream-K:
-  // N=24576: 35.8 / 36.1 us (CTA pairs, whole tiles) against 36.6 at M = 1 / 16, 38.7 against 37.2 at M = 32;
-  // N=2112: 10.8 us (single CTAs, 4 workers per tile) against 12.9 at M = 16.  The pair kernel halves the activation
-  // traffic per weight byte and wins when there is a tile for every pair; below that the single-CTA form has twice
-  // the tiles to spread.  (no plain output: the fused all-gather / quantisation epilogues live in the tile kernel)
-  if (plain_output && M <= kDecodeMaxTokens && decode_supported(M, N, K))
-    return (N + 127) / 128 < (num_sms > 0 ? num_sms : 148) ? kDecodeVariant1 : kDecodeVariant2;
+  // Row-balanced swap-AB kernel (gemm_decode.cu, swapab_rows): every CTA streams one contiguous range of
+  // R = ceil8(N / #SMs) weight rows for all of K.  Measured in a CUDA graph on B200 with every launch streaming its
+  // weight from HBM (tools/decode_ab.py, K=7168), against the best of the tile kernels (swap-AB tiles 30/31, 128-row
+  // token-major tiles 0): N=24576 (R=168): 30.2 / 30.3 / 31.5 / 33.2 us at M = 1 / 16 / 32 / 64 against 36.1 / 36.6 /
+  // 38.0 / 38.7 (0.89 -> 0.83 of the measured copy bandwidth instead of 0.75 -> 0.71); at M = 128 it loses (49.3 against
+  // 40.9): every CTA re-reads the whole activation matrix from L2, M / R of its weight bytes.  N=2112 (R=16): equal to
+  // the 4-way split tiles at M <= 16 (11.8 us: launch + prologue + one DRAM round trip, not bytes), behind them above.
+  // Hence: up to 16 tokens always, beyond that while the activation re-reads stay under half of the weight bytes.
+  if (plain_output && rows_supported(M, N, K)) {
+    const int64_t W = num_sms > 0 ? num_sms : 148;
+    const int64_t R = ((N + W - 1) / W + 7) / 8 * 8;
+    if (M <= kDecodeMaxTokens || 2 * M <= R) return kRowsVariant;
+  }
   // a handful of wide tiles on a narrow weight (N=2112, 129 <= M <= 256: 9 pair tiles for 74 pairs): 128-wide single-CTA
   // tiles give stream-K twice the units to balance
   if (M > 128 && M <= 256 && N < 4096) return 0;
@@ -1282,6 +1288,10 @@ static int gemm_entry(const void* A, const void* B, const float* sa, const float
   const bool plain_output = !qo && num_extra == 0 && !mc_ptr;
   if (variant < 0) variant = pick_variant(M, N, K, plain_output, num_sms);
   if (!variant_available(variant)) return SGLK_E_VARIANT;
+  if (variant == kRowsVariant) {
+    if (!plain_output || !rows_supported(M, N, K)) return SGLK_E_VARIANT;
+    return rows_entry(A, B, sa, sb, Cout, M, N, K, lda, ldb, ldc, sa_sm, sa_sk, sb_sk, sb_sn, out_dtype, num_sms, flags, st);
+  }
   if (variant == kDecodeVariant1 || variant == kDecodeVariant2) {
     if (!plain_output || !decode_supported(M, N, K)) return SGLK_E_VARIANT;
     return decode_entry(A, B, sa, sb, Cout, M, N, K, lda, ldb, ldc, sa_sm, sa_sk, sb_sk, sb_sn, out_dtype,
@@ -1522,6 +1532,7 @@ extern "C" int64_t sglk_gemm_workspace_bytes(int64_t M, int64_t N, int64_t K, in
   if (variant < 0) variant = sglk::pick_variant(M, N, K, true, num_sms);
   if (!sglk::variant_available(variant)) return 0;
   if (num_sms <= 0) num_sms = sglk::device_sm_count();
+  if (variant == sglk::kRowsVariant) return 0;   // no split-K, no workspace
   if (variant == sglk::kDecodeVariant1 || variant == sglk::kDecodeVariant2)
     return sglk::decode_workspace_bytes(M, N, K, variant == sglk::kDecodeVariant2 ? 2 : 1, num_sms, flags);
   const sglk::Plan pl = sglk::make_plan(M, N, K, variant, num_sms, true, flags);

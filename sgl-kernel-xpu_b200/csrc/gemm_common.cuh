@@ -86,6 +86,23 @@ inline bool make_tmap_2d(CUtensorMap* m, CUtensorMapDataType dt, int elem_bytes,
              CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
 }
 
+// The same row-major [rows, cols] byte matrix (cols % 128 == 0) seen as [kblock][row][128 B]: one box of
+// [box_kblocks][box_rows][128 B] fetches `box_kblocks` consecutive 128-byte K blocks of `box_rows` rows with ONE TMA
+// instruction, and lands them as box_kblocks back-to-back K-major swizzled tiles (box_rows % 8 == 0 keeps every tile
+// 1 KB aligned).  Coordinates: {0, row, kblock}.
+inline bool make_tmap_kblocks(CUtensorMap* m, const void* ptr, uint64_t rows, uint64_t cols, uint64_t ld, uint32_t box_rows,
+                              uint32_t box_kblocks) {
+  EncodeTiledFn enc = get_encode_fn();
+  if (!enc || cols % 128 != 0) return false;
+  const cuuint64_t dims[3] = {128, rows, cols / 128};
+  const cuuint64_t strides[2] = {ld, 128};
+  const cuuint32_t box[3] = {128, box_rows, box_kblocks};
+  const cuuint32_t estr[3] = {1, 1, 1};
+  return enc(m, CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, const_cast<void*>(ptr), dims, strides, box, estr,
+             CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+             CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
 
 // cudaFuncAttributeMaxDynamicSharedMemorySize is a property of the current device's context: opt in once per
 // (kernel instantiation, device ordinal).  `configured` is the instantiation's own flag word.
@@ -108,5 +125,10 @@ int decode_entry(const void* A, const void* B, const float* sa, const float* sb,
                  cudaStream_t st);
 int64_t decode_workspace_bytes(int64_t M, int64_t N, int64_t K, int cg, int num_sms, int flags);
 bool decode_supported(int64_t M, int64_t N, int64_t K);
+// row-balanced swap-AB kernel (gemm_decode.cu): every CTA owns one contiguous range of weight rows for all of K
+int rows_entry(const void* A, const void* B, const float* sa, const float* sb, void* Cout, int64_t M, int64_t N, int64_t K,
+               int64_t lda, int64_t ldb, int64_t ldc, int64_t sa_sm, int64_t sa_sk, int64_t sb_sk, int64_t sb_sn,
+               int out_dtype, int num_sms, int flags, cudaStream_t st);
+bool rows_supported(int64_t M, int64_t N, int64_t K);
 
 }  // namespace sglk

@@ -735,4 +735,491 @@ int decode_entry(const void* A, const void* B, const float* sa, const float* sb,
   return launch_decode_nt<1, __half>(pl.nt, tw, tx0, tx1, p, pl.workers, st);
 }
 
+// ============================================================================================================
+// Row-balanced swap-AB kernel (variant `swapab_rows`, M <= 128 tokens)
+// ============================================================================================================
+// The tile kernels above cut N into 128 / 256-row tiles and then have to balance a tile count that is not a multiple of
+// the SM count (N=24576: 96 pair tiles on 74 pairs; N=2112: 17 tiles on 148 SMs) with a second, partly filled wave or
+// with split-K partials and a fix-up.  A decode GEMM is a weight stream, and a stream balances by BYTES: here every CTA
+// owns one contiguous range of R = ceil8(N / #SMs) weight rows (168 at N=24576, 16 at N=2112) for the WHOLE of K — no
+// second wave, no partials, no workspace, no atomics.  A range is walked in passes of at most 256 rows; a pass is one or
+// two MMA "sub-tiles" (128 rows + the rest), each with its own TMA box cut to the rows that exist (a box never reads
+// more than 7 rows past the range; the MMA reads 128 smem rows regardless, the stale ones only feed TMEM lanes that are
+// never stored) and its own accumulator columns in TMEM.  Rows of one range may lie in up to three 128-row weight-scale
+// blocks, so sb is a per-LANE factor (lane = weight row), picked from four staged values.
+// A ring stage holds G K blocks (4 for the small shapes: the issuer's and the promotion warps' per-hand-off latencies
+// are paid once per 4 blocks) and is one accumulator hand-off.
+struct RowsParams {
+  const float* sa;
+  const float* sb;
+  void* C;
+  int64_t M, N, K, ldc;
+  int64_t sa_sm, sa_sk, sb_sk, sb_sn;
+  int32_t num_k_blocks, num_sb_cols;
+  int32_t rows_per_worker;   // R = passes * rows_per_pass
+  int32_t passes;
+  int32_t rows_per_pass;     // multiple of 8, <= 128 * S
+  int32_t num_stages;
+  // a ring stage holds G K blocks, operand-major: [sub-tile 0: G tiles][sub-tile 1: G tiles][activations: G tiles]; a tile
+  // is box-rows x 128 bytes (box rows are multiples of 8, so every tile starts 1 KB aligned)
+  uint32_t stage_bytes;
+  uint32_t sub_tile_bytes[2], x_tile_bytes;
+  uint32_t sub1_off, x_off;  // offsets of the sub-tile 1 / activation regions inside a stage
+  uint32_t kb_tx_bytes;      // bytes TMA delivers per K block (boxes are always delivered whole, out-of-bounds zero-filled)
+  int32_t kb3d;              // K % 128 == 0: the tensor maps are the [kblock][row][128 B] views, one TMA instruction per
+                             // operand per stage; else 2-D maps (which zero-fill the K tail), one per operand per K block
+};
+
+template <int NT, int S, int G>
+struct RowsCfg {
+  static constexpr int kEW = 8;                              // promotion / epilogue warps: two per TMEM lane quarter
+  static constexpr int kThreads = 128 + kEW * 32;
+  static constexpr int CW = NT / 2;                          // token columns per promotion warp
+  static constexpr int IW = CW < 32 ? CW : 32;               // columns per tcgen05.ld item
+  static constexpr int IPB = CW / IW;                        // items per (K block, sub-tile) per warp
+  static constexpr int ITEMS = G * S * IPB;                  // items per hand-off
+  static constexpr bool kOneBatch = ITEMS * IW <= 64;        // the whole hand-off fits the staging registers
+  static constexpr int NBUF = kOneBatch ? ITEMS : 2;
+  static constexpr int SLOT_COLS = G * S * NT;               // TMEM columns of one hand-off
+  static constexpr int kSlots = (512 / SLOT_COLS) < 8 ? (512 / SLOT_COLS) : 8;
+  static constexpr int TMEM_COLS = kSlots * SLOT_COLS;
+  static constexpr int KB_SCALE_BYTES = (NT + 4) * 4;        // sa[0..NT) + four sb values per K block
+  static constexpr int SCALE_SLOT = G * KB_SCALE_BYTES;      // per ring stage
+  static_assert(NT % 16 == 0 && NT >= 16 && NT <= 128 && (S == 1 || S == 2), "shape");
+  static_assert(kSlots >= 2 && (TMEM_COLS & (TMEM_COLS - 1)) == 0 && TMEM_COLS >= 32 && TMEM_COLS <= 512, "TMEM columns");
+  static_assert(4 * 32 * 40 + kEW * 32 * 232 <= kThreads * 168, "register re-split");
+};
+
+constexpr int kRowsTailBytes = 16384;   // behind the ring: factor slots + barriers; also what the last sub-tile's MMA may over-read
+
+template <int NT, int S, int G, typename OutT>
+__global__ void __launch_bounds__(RowsCfg<NT, S, G>::kThreads, 1)
+fp8_blockwise_gemm_rows_kernel(const __grid_constant__ CUtensorMap tmap_w0, const __grid_constant__ CUtensorMap tmap_w1,
+                               const __grid_constant__ CUtensorMap tmap_x, const RowsParams p) {
+  using C = RowsCfg<NT, S, G>;
+  constexpr int CW = C::CW, kSlots = C::kSlots, kEW = C::kEW;
+
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  if ((ptx::smem_u32(smem_raw) & 1023u) != 0) __trap();
+  const uint32_t smem_base = ptx::smem_u32(smem_raw);
+  const int nstages = p.num_stages;
+  const uint32_t stage_bytes = p.stage_bytes;
+  const uint32_t scale_base = smem_base + uint32_t(nstages) * stage_bytes;
+  const uint32_t bar_base = scale_base + uint32_t(nstages) * C::SCALE_SLOT;          // 16-byte aligned
+  auto full_bar = [&](int s) { return bar_base + 8u * s; };
+  auto empty_bar = [&](int s) { return bar_base + 8u * (kDecMaxStages + s); };
+  auto sfull_bar = [&](int s) { return bar_base + 8u * (2 * kDecMaxStages + s); };
+  auto sempty_bar = [&](int s) { return bar_base + 8u * (3 * kDecMaxStages + s); };
+  auto tfull_bar = [&](int s) { return bar_base + 8u * (4 * kDecMaxStages + s); };
+  auto tempty_bar = [&](int s) { return bar_base + 8u * (4 * kDecMaxStages + 8 + s); };
+  const uint32_t tmem_slot = bar_base + 8u * (4 * kDecMaxStages + 16);
+  // (the host sized the ring so that nstages factor slots + the barriers fit the 16 KB tail: make_rows_plan)
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+
+  if (warp == 0 && lane == 0) {
+    ptx::prefetch_tensormap(&tmap_w0);
+    if (S == 2) ptx::prefetch_tensormap(&tmap_w1);
+    ptx::prefetch_tensormap(&tmap_x);
+  }
+  if (warp == 1 && lane == 0) {
+    for (int s = 0; s < nstages; ++s) {
+      ptx::mbar_init(full_bar(s), 1);                  // the producer's arrive.expect_tx
+      ptx::mbar_init(empty_bar(s), 1);                 // one tcgen05.commit
+      ptx::mbar_init(sfull_bar(s), 32);                // every lane of the scale loader
+      ptx::mbar_init(sempty_bar(s), kEW);              // the promotion warps have read the slot
+    }
+    for (int s = 0; s < kSlots; ++s) {
+      ptx::mbar_init(tfull_bar(s), 1);
+      ptx::mbar_init(tempty_bar(s), kEW);
+    }
+    ptx::fence_mbar_init();
+  }
+  if (warp == 2) {
+    ptx::tmem_alloc<1>(tmem_slot, C::TMEM_COLS);
+    ptx::tmem_relinquish<1>();
+  }
+  if (warp == 3) {
+    // factor slots of tokens >= M are never filled: give them a defined value (their columns are never stored)
+    for (uint32_t off = uint32_t(lane) * 4u; off < uint32_t(nstages) * C::SCALE_SLOT; off += 128u)
+      *reinterpret_cast<float*>(smem_raw + (scale_base - smem_base) + off) = 0.0f;
+  }
+  ptx::tc_fence_before();
+  __syncthreads();
+  ptx::tc_fence_after();
+  const uint32_t tmem_base = *reinterpret_cast<volatile uint32_t*>(smem_raw + (tmem_slot - smem_base));
+
+  // this CTA's weight rows [row0, row_end), walked in `passes` passes of rows_per_pass rows; every role runs the same loop
+  const int num_kb = p.num_k_blocks;
+  const int num_groups = (num_kb + G - 1) / G;
+  const int row0 = int(blockIdx.x) * p.rows_per_worker;
+  const int row_end = min(row0 + p.rows_per_worker, int(p.N));
+
+  if (warp == 0) {
+    // =========================== TMA producer ===========================
+    ptx::reg_dealloc<40>();
+    const uint64_t pol_w = ptx::policy_evict_first();      // weights pass through once
+    const uint64_t pol_x = ptx::policy_evict_last();       // the activation K blocks are re-read by every CTA
+    int stage = 0;
+    uint32_t phase = 0;
+    for (int pass = 0; pass < p.passes; ++pass) {
+      const int base = row0 + pass * p.rows_per_pass;
+      if (base >= row_end) break;
+      for (int g = 0; g < num_groups; ++g) {
+        const int nb = min(G, num_kb - g * G);
+        ptx::mbar_wait(empty_bar(stage), phase ^ 1);
+        if (ptx::elect_one()) {
+          const uint32_t dst = smem_base + uint32_t(stage) * stage_bytes;
+          if (p.kb3d) {
+            // whole boxes of G K blocks (K blocks past the end are zero-filled and never multiplied)
+            ptx::mbar_arrive_expect_tx(full_bar(stage), uint32_t(G) * p.kb_tx_bytes);
+            ptx::tma_load_3d(&tmap_w0, full_bar(stage), dst, 0, base, g * G, pol_w);
+            if constexpr (S == 2) ptx::tma_load_3d(&tmap_w1, full_bar(stage), dst + p.sub1_off, 0, base + BLOCK_M, g * G, pol_w);
+            ptx::tma_load_3d(&tmap_x, full_bar(stage), dst + p.x_off, 0, 0, g * G, pol_x);
+          } else {
+            ptx::mbar_arrive_expect_tx(full_bar(stage), uint32_t(nb) * p.kb_tx_bytes);
+            for (int j = 0; j < nb; ++j) {
+              const int kb = g * G + j;
+              ptx::tma_load_2d(&tmap_w0, full_bar(stage), dst + uint32_t(j) * p.sub_tile_bytes[0], kb * BLOCK_K, base, pol_w);
+              if constexpr (S == 2)
+                ptx::tma_load_2d(&tmap_w1, full_bar(stage), dst + p.sub1_off + uint32_t(j) * p.sub_tile_bytes[1], kb * BLOCK_K,
+                                 base + BLOCK_M, pol_w);
+              ptx::tma_load_2d(&tmap_x, full_bar(stage), dst + p.x_off + uint32_t(j) * p.x_tile_bytes, kb * BLOCK_K, 0, pol_x);
+            }
+          }
+        }
+        __syncwarp();
+        if (++stage == nstages) { stage = 0; phase ^= 1; }
+      }
+    }
+    __syncwarp();
+  } else if (warp == 1) {
+    // =========================== MMA issuer ===========================
+    ptx::reg_dealloc<40>();
+    constexpr uint32_t idesc = make_idesc(BLOCK_M, NT);
+    const uint32_t tmem_base_u = __shfl_sync(0xFFFFFFFFu, tmem_base, 0);
+    const uint64_t desc_hi = make_smem_desc(0);
+    int stage = 0, slot = 0;
+    uint32_t phase = 0, slot_phase = 0;
+    for (int pass = 0; pass < p.passes; ++pass) {
+      if (row0 + pass * p.rows_per_pass >= row_end) break;
+      for (int g = 0; g < num_groups; ++g) {
+        const int nb = min(G, num_kb - g * G);
+        ptx::mbar_wait(full_bar(stage), phase);
+        ptx::mbar_wait(tempty_bar(slot), slot_phase ^ 1);   // slot drained by every promotion warp?
+        ptx::tc_fence_after();
+        const uint32_t st_addr = smem_base + uint32_t(stage) * stage_bytes;
+        if (ptx::elect_one()) {
+          // The four K=32 MMAs of one (K block, sub-tile) accumulate into the same TMEM columns: a dependent chain, and at
+          // these widths (N = 16..128) an MMA is latency-, not throughput-bound (measured ~290 clk per chain of four at
+          // N=16, where the pipe time is 4 x 8 clk).  The G x S chains of a stage are independent, so they are issued
+          // round-robin: chain latency overlaps across chains.
+#pragma unroll
+          for (int k = 0; k < BLOCK_K / UMMA_K; ++k) {
+#pragma unroll
+            for (int j = 0; j < G; ++j) {
+              if (j < nb) {
+                const uint64_t db = desc_hi | uint64_t(((st_addr + p.x_off + uint32_t(j) * p.x_tile_bytes) & 0x3FFFFu) >> 4);
+#pragma unroll
+                for (int s = 0; s < S; ++s) {
+                  const uint32_t a_addr = st_addr + (s ? p.sub1_off : 0u) + uint32_t(j) * p.sub_tile_bytes[s];
+                  const uint64_t da = desc_hi | uint64_t((a_addr & 0x3FFFFu) >> 4);
+                  const uint32_t d_tmem = tmem_base_u + uint32_t(slot * C::SLOT_COLS + (j * S + s) * NT);
+                  ptx::mma_f8f6f4<1>(d_tmem, da + uint64_t(k * (UMMA_K >> 4)), db + uint64_t(k * (UMMA_K >> 4)), idesc,
+                                     k > 0 ? 1u : 0u);
+                }
+              }
+            }
+          }
+          ptx::tc_commit<1>(empty_bar(stage));     // smem stage reusable once these MMAs have read it
+          ptx::tc_commit<1>(tfull_bar(slot));      // the hand-off's partials are complete
+        }
+        __syncwarp();
+        if (++stage == nstages) { stage = 0; phase ^= 1; }
+        if (++slot == kSlots) { slot = 0; slot_phase ^= 1; }
+      }
+    }
+    __syncwarp();
+  } else if (warp == 2) {
+    ptx::reg_dealloc<40>();                        // TMEM owner: only waits for the end
+  } else if (warp == 3) {
+    // =========================== scale loader ===========================
+    // per K block: sa[token, kb] for every token and the sb[kb, .] of the (up to three) 128-row scale blocks this pass
+    // touches -> the stage's factor slot, 4 bytes per cp.async (any strides), completion tracked by the slot's mbarrier
+    ptx::reg_dealloc<40>();
+    int stage = 0;
+    uint32_t phase = 0;
+    for (int pass = 0; pass < p.passes; ++pass) {
+      const int base = row0 + pass * p.rows_per_pass;
+      if (base >= row_end) break;
+      const int sbc = min(base / 128 + min(lane, 3), p.num_sb_cols - 1);
+      const float* sb_ptr = p.sb + int64_t(sbc) * p.sb_sn;
+      for (int g = 0; g < num_groups; ++g) {
+        const int nb = min(G, num_kb - g * G);
+        ptx::mbar_wait(sempty_bar(stage), phase ^ 1);
+        const uint32_t slot = scale_base + uint32_t(stage) * C::SCALE_SLOT;
+        for (int j = 0; j < nb; ++j) {
+          const int kb = g * G + j;
+          const uint32_t kslot = slot + uint32_t(j) * C::KB_SCALE_BYTES;
+#pragma unroll
+          for (int q = 0; q < (NT + 31) / 32; ++q) {
+            const int t = lane + 32 * q;
+            if (t < NT && t < p.M) ptx::cp_async4(kslot + 4u * t, p.sa + int64_t(t) * p.sa_sm + int64_t(kb) * p.sa_sk);
+          }
+          if (lane < 4) ptx::cp_async4(kslot + 4u * NT + 4u * lane, sb_ptr + int64_t(kb) * p.sb_sk);
+        }
+        dptx::cp_async_mbar_arrive_noinc(sfull_bar(stage));
+        if (++stage == nstages) { stage = 0; phase ^= 1; }
+      }
+    }
+    ptx::cp_async_commit();
+    ptx::cp_async_wait<0>();
+    __syncwarp();
+  } else {
+    // =========================== promotion + epilogue warps ===========================
+    ptx::reg_alloc<232>();
+    const int ew = warp - 4;
+    const int quarter = warp & 3;                      // TMEM lanes this warp may touch: 32*quarter .. +31
+    const int colgroup = ew >> 2;                      // which half of the token columns
+    const uint32_t lane_base = uint32_t(quarter * 32) << 16;
+    const int t0 = colgroup * CW;                      // first token column of this warp
+    constexpr int IW = C::IW, IPB = C::IPB, ITEMS = C::ITEMS, NBUF = C::NBUF;
+    int stage = 0, slot = 0;
+    uint32_t phase = 0, slot_phase = 0;
+    OutT* Cp = reinterpret_cast<OutT*>(p.C);
+    const bool pair_ok = (p.ldc % 2 == 0) && (p.N % 2 == 0) && ((reinterpret_cast<uintptr_t>(p.C) & 3) == 0);
+    for (int pass = 0; pass < p.passes; ++pass) {
+      const int base = row0 + pass * p.rows_per_pass;
+      if (base >= row_end) break;
+      const int limit = min(base + p.rows_per_pass, row_end);       // rows [base, limit) are this pass's output columns
+      // byte offset (inside a K block's factor slot) of this lane's weight-scale value, per sub-tile
+      uint32_t sb_off[S];
+#pragma unroll
+      for (int s = 0; s < S; ++s) {
+        const int n = base + s * BLOCK_M + quarter * 32 + lane;
+        sb_off[s] = 4u * uint32_t(NT) + 4u * uint32_t(min(n / 128 - base / 128, 3));
+      }
+      float accum[S][CW];
+#pragma unroll
+      for (int s = 0; s < S; ++s)
+#pragma unroll
+        for (int i = 0; i < CW; ++i) accum[s][i] = 0.0f;
+      for (int g = 0; g < num_groups; ++g) {
+        const int nb = min(G, num_kb - g * G);
+        ptx::mbar_wait(tfull_bar(slot), slot_phase);   // the hand-off's MMAs complete
+        ptx::tc_fence_after();
+        const uint32_t taddr = tmem_base + lane_base + uint32_t(slot * C::SLOT_COLS + t0);
+        const uint32_t fslot = scale_base + uint32_t(stage) * C::SCALE_SLOT;
+        uint32_t v[NBUF][IW];
+        // item i = (K block j, sub-tile s, column chunk c) with i = (j * S + s) * IPB + c
+        auto item_ld = [&](int i, uint32_t (&buf)[IW]) {
+          dptx::tmem_ld<IW>(taddr + uint32_t((i / IPB) * NT + (i % IPB) * IW), buf);
+        };
+        auto item_fma = [&](int i, const uint32_t (&buf)[IW]) {
+          const int j = i / (S * IPB), s = (i / IPB) % S, c = i % IPB;
+          const uint32_t kslot = fslot + uint32_t(j) * C::KB_SCALE_BYTES;
+          const float sbv = ptx::lds_f32(kslot + sb_off[s]);
+          const uint32_t fac = kslot + 4u * uint32_t(t0 + c * IW);
+#pragma unroll
+          for (int q = 0; q < IW / 4; ++q) {
+            const float4 f = dptx::lds_f32x4(fac + 16u * q);
+            float* a = &accum[s][c * IW + 4 * q];
+            dptx::fma2_scaled(a[0], a[1], buf[4 * q], buf[4 * q + 1], f.x, f.y, sbv);
+            dptx::fma2_scaled(a[2], a[3], buf[4 * q + 2], buf[4 * q + 3], f.z, f.w, sbv);
+          }
+        };
+        auto release_slot = [&]() {                    // every tcgen05.ld of this warp on the slot has completed
+          ptx::tc_fence_before();
+          if (lane == 0) ptx::mbar_arrive(tempty_bar(slot));
+        };
+        if constexpr (C::kOneBatch) {
+          // the whole hand-off in one go: all tcgen05.ld issued, one wait, slot handed back, then the FMAs
+#pragma unroll
+          for (int i = 0; i < ITEMS; ++i)
+            if (i / (S * IPB) < nb) item_ld(i, v[i]);
+          ptx::mbar_wait(sfull_bar(stage), phase);     // the factors of these K blocks are in smem (long since, normally)
+          asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+          release_slot();
+#pragma unroll
+          for (int i = 0; i < ITEMS; ++i) {
+            if (i / (S * IPB) < nb) {
+#pragma unroll
+              for (int r = 0; r < IW; ++r) asm volatile("" : "+r"(v[i][r]));   // consumers stay below the wait
+              item_fma(i, v[i]);
+            }
+          }
+        } else {
+          // item i+1 is in flight while item i is folded in; the slot goes back as soon as its last item is in registers
+          ptx::mbar_wait(sfull_bar(stage), phase);
+          const int last = nb * S * IPB - 1;
+          item_ld(0, v[0]);
+#pragma unroll
+          for (int i = 0; i < ITEMS; ++i) {
+            if (i <= last) {
+              dptx::tmem_ld_wait<IW>(v[i & 1]);
+              if (i < last) item_ld(i + 1, v[(i + 1) & 1]);
+              else release_slot();
+              item_fma(i, v[i & 1]);
+            }
+          }
+        }
+        __syncwarp();
+        if (lane == 0) ptx::mbar_arrive(sempty_bar(stage));     // every factor of this stage has been read
+        if (++stage == nstages) { stage = 0; phase ^= 1; }
+        if (++slot == kSlots) { slot = 0; slot_phase ^= 1; }
+      }
+      // ---------------- C^T out of the registers: lane = output column n, accum[s][j] = token t0 + j ----------------
+#pragma unroll
+      for (int s = 0; s < S; ++s) {
+        const int n = base + s * BLOCK_M + quarter * 32 + lane;
+        if (pair_ok) {
+          // neighbouring lanes swap one value each: the even lane ends up with (n, n+1) of token j, the odd lane with
+          // (n-1, n) of token j+1 — one 4-byte store per two values (base and limit are even: a pair is never split)
+          const int odd = lane & 1;
+          const int col = n - odd;
+#pragma unroll
+          for (int j = 0; j < CW; j += 2) {
+            const float send = odd ? accum[s][j] : accum[s][j + 1];
+            const float recv = __shfl_xor_sync(0xFFFFFFFFu, send, 1);
+            const uint32_t w = odd ? pack2<OutT>(recv, accum[s][j + 1]) : pack2<OutT>(accum[s][j], recv);
+            const int tok = t0 + j + odd;
+            if (tok < p.M && col < limit) *reinterpret_cast<uint32_t*>(Cp + int64_t(tok) * p.ldc + col) = w;
+          }
+        } else if (n < limit) {
+#pragma unroll
+          for (int j = 0; j < CW; ++j) {
+            if (t0 + j < p.M) {
+              const uint32_t w = pack2<OutT>(accum[s][j], 0.0f);
+              Cp[int64_t(t0 + j) * p.ldc + n] = *reinterpret_cast<const OutT*>(&w);
+            }
+          }
+        }
+      }
+    }
+    __syncwarp();
+  }
+
+  // =========================== teardown ===========================
+  ptx::tc_fence_before();
+  __syncthreads();
+  if (warp == 2) ptx::tmem_dealloc<1>(tmem_base, C::TMEM_COLS);
+}
+
+struct RowsPlan {
+  int nt, S, G, workers, rows_per_worker, passes, rows_per_pass, stages;
+  uint32_t sub_rows[2], x_rows, stage_bytes, sub1_off, x_off, kb_tx_bytes;
+};
+
+bool rows_supported(int64_t M, int64_t N, int64_t K) { return M >= 1 && M <= 128 && N >= 1 && K >= 1; }
+
+static RowsPlan make_rows_plan(int64_t M, int64_t N, int64_t K, int num_sms) {
+  (void)K;
+  RowsPlan pl;
+  pl.nt = decode_nt(M);
+  const int64_t W = num_sms < 1 ? 1 : num_sms;
+  int64_t R = ((N + W - 1) / W + 7) / 8 * 8;                  // rows per CTA, whole 8-row swizzle atoms
+  pl.passes = int((R + 255) / 256);
+  pl.rows_per_pass = int(((R + pl.passes - 1) / pl.passes + 7) / 8 * 8);
+  R = int64_t(pl.rows_per_pass) * pl.passes;
+  pl.rows_per_worker = int(R);
+  pl.workers = int((N + R - 1) / R);
+  pl.S = pl.rows_per_pass > BLOCK_M ? 2 : 1;
+  pl.sub_rows[0] = uint32_t(pl.rows_per_pass > BLOCK_M ? BLOCK_M : pl.rows_per_pass);
+  pl.sub_rows[1] = pl.S == 2 ? uint32_t(pl.rows_per_pass - BLOCK_M) : 0u;
+  pl.x_rows = uint32_t((M + 7) / 8 * 8);
+  // K blocks per ring stage / accumulator hand-off
+  // (more K blocks per stage = more independent MMA chains in flight and fewer hand-offs; bounded by TMEM — a hand-off
+  // is G x S x NT columns and two must fit — and by the ring: at least ~3 stages of G K blocks each)
+  pl.G = pl.S == 2 ? (pl.nt <= 32 ? 2 : 1) : (pl.nt == 16 ? 8 : (pl.nt <= 64 ? 4 : 2));
+  // tiles are box-rows x 128 B (multiples of 1 KB); the MMA reads 128 weight rows / NT activation rows from a tile's base
+  // whatever the box held: what lies behind (the next tile, the next stage, the 16 KB tail) is addressable smem
+  pl.sub1_off = uint32_t(pl.G) * pl.sub_rows[0] * BLOCK_K;
+  pl.x_off = pl.sub1_off + uint32_t(pl.G) * pl.sub_rows[1] * BLOCK_K;
+  pl.kb_tx_bytes = (pl.sub_rows[0] + pl.sub_rows[1] + pl.x_rows) * BLOCK_K;
+  pl.stage_bytes = uint32_t(pl.G) * pl.kb_tx_bytes;
+  int n = (kMaxDynSmem - kRowsTailBytes) / int(pl.stage_bytes);
+  if (n > kDecMaxStages) n = kDecMaxStages;
+  const int scale_slot = pl.G * (pl.nt + 4) * 4, bar_bytes = 8 * (4 * kDecMaxStages + 16) + 16;
+  while (n > 2 && n * scale_slot + bar_bytes > kRowsTailBytes) --n;
+  pl.stages = n;
+  return pl;
+}
+
+template <int NT, int S, int G, typename OutT>
+static int launch_rows(const CUtensorMap& tw0, const CUtensorMap& tw1, const CUtensorMap& tx, const RowsParams& p,
+                       int workers, cudaStream_t st) {
+  auto kern = fp8_blockwise_gemm_rows_kernel<NT, S, G, OutT>;
+  static std::atomic<uint64_t> configured{0};
+  if (int e = ensure_max_dyn_smem(kern, configured, kMaxDynSmem)) return e;
+  kern<<<dim3(unsigned(workers)), dim3(RowsCfg<NT, S, G>::kThreads), kMaxDynSmem, st>>>(tw0, tw1, tx, p);
+  return int(cudaGetLastError());
+}
+
+template <typename OutT>
+static int launch_rows_cfg(const RowsPlan& pl, const CUtensorMap& tw0, const CUtensorMap& tw1, const CUtensorMap& tx,
+                           const RowsParams& p, cudaStream_t st) {
+  const int key = pl.nt * 100 + pl.S * 10 + pl.G;
+  switch (key) {
+    case 1618: return launch_rows<16, 1, 8, OutT>(tw0, tw1, tx, p, pl.workers, st);
+    case 1622: return launch_rows<16, 2, 2, OutT>(tw0, tw1, tx, p, pl.workers, st);
+    case 3214: return launch_rows<32, 1, 4, OutT>(tw0, tw1, tx, p, pl.workers, st);
+    case 3222: return launch_rows<32, 2, 2, OutT>(tw0, tw1, tx, p, pl.workers, st);
+    case 6414: return launch_rows<64, 1, 4, OutT>(tw0, tw1, tx, p, pl.workers, st);
+    case 6421: return launch_rows<64, 2, 1, OutT>(tw0, tw1, tx, p, pl.workers, st);
+    case 12812: return launch_rows<128, 1, 2, OutT>(tw0, tw1, tx, p, pl.workers, st);
+    case 12821: return launch_rows<128, 2, 1, OutT>(tw0, tw1, tx, p, pl.workers, st);
+    default: return SGLK_E_VARIANT;
+  }
+}
+
+// Arguments were validated by gemm_entry (pointers, strides, alignment, dtype); M in [1, 128].
+int rows_entry(const void* A, const void* B, const float* sa, const float* sb, void* Cout, int64_t M, int64_t N, int64_t K,
+               int64_t lda, int64_t ldb, int64_t ldc, int64_t sa_sm, int64_t sa_sk, int64_t sb_sk, int64_t sb_sn,
+               int out_dtype, int num_sms, int flags, cudaStream_t st) {
+  if (num_sms <= 0) num_sms = device_sm_count();
+  const RowsPlan pl = make_rows_plan(M, N, K, num_sms);
+  if (pl.stages < 2) return SGLK_E_SHAPE;
+  RowsParams p;
+  memset(&p, 0, sizeof(p));
+  p.sa = sa; p.sb = sb; p.C = Cout;
+  p.M = M; p.N = N; p.K = K; p.ldc = ldc;
+  p.sa_sm = sa_sm; p.sa_sk = sa_sk; p.sb_sk = sb_sk; p.sb_sn = sb_sn;
+  p.num_k_blocks = int32_t((K + BLOCK_K - 1) / BLOCK_K);
+  p.num_sb_cols = int32_t((N + 127) / 128);
+  p.rows_per_worker = pl.rows_per_worker;
+  p.passes = pl.passes;
+  p.rows_per_pass = pl.rows_per_pass;
+  p.num_stages = pl.stages;
+  p.stage_bytes = pl.stage_bytes;
+  p.sub_tile_bytes[0] = pl.sub_rows[0] * BLOCK_K;
+  p.sub_tile_bytes[1] = pl.sub_rows[1] * BLOCK_K;
+  p.x_tile_bytes = pl.x_rows * BLOCK_K;
+  p.kb3d = (K % BLOCK_K == 0 && ldb % 16 == 0 && lda % 16 == 0 && !(flags & SGLK_GEMM_DECODE_2D_LOADS)) ? 1 : 0;
+  p.sub1_off = pl.sub1_off;
+  p.x_off = pl.x_off;
+  p.kb_tx_bytes = pl.kb_tx_bytes;
+  CUtensorMap tw0, tw1, tx;
+  if (p.kb3d) {
+    // (an encode failure here is not an error: the 2-D maps below serve every shape)
+    bool ok = make_tmap_kblocks(&tw0, B, uint64_t(N), uint64_t(K), uint64_t(ldb), pl.sub_rows[0], uint32_t(pl.G));
+    tw1 = tw0;
+    if (ok && pl.S == 2) ok = make_tmap_kblocks(&tw1, B, uint64_t(N), uint64_t(K), uint64_t(ldb), pl.sub_rows[1], uint32_t(pl.G));
+    if (ok) ok = make_tmap_kblocks(&tx, A, uint64_t(M), uint64_t(K), uint64_t(lda), pl.x_rows, uint32_t(pl.G));
+    if (!ok) p.kb3d = 0;
+  }
+  if (!p.kb3d) {
+    if (!make_tmap_2d(&tw0, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, B, uint64_t(N), uint64_t(K), uint64_t(ldb), pl.sub_rows[0], BLOCK_K))
+      return SGLK_E_DRIVER;
+    tw1 = tw0;
+    if (pl.S == 2 &&
+        !make_tmap_2d(&tw1, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, B, uint64_t(N), uint64_t(K), uint64_t(ldb), pl.sub_rows[1], BLOCK_K))
+      return SGLK_E_DRIVER;
+    if (!make_tmap_2d(&tx, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, A, uint64_t(M), uint64_t(K), uint64_t(lda), pl.x_rows, BLOCK_K))
+      return SGLK_E_DRIVER;
+  }
+  if (out_dtype == SGLK_BF16) return launch_rows_cfg<__nv_bfloat16>(pl, tw0, tw1, tx, p, st);
+  return launch_rows_cfg<__half>(pl, tw0, tw1, tx, p, st);
+}
+
 }  // namespace sglk

@@ -18,7 +18,7 @@ LIB_PATH = os.environ.get(
 BF16, F16, F32, E4M3, INT8 = 0, 1, 2, 3, 4
 SCALE_F32_ROW_MAJOR, SCALE_F32_COL_MAJOR, SCALE_UE8M0_ROW_MAJOR, SCALE_UE8M0_COL_PACKED = 0, 1, 2, 3
 ABI_VERSION = 2
-STREAMK_AUTO, STREAMK_FORCE, STREAMK_NEVER, GROUP_M_SHIFT, SPLIT_SHIFT = 0, 1, 2, 8, 16
+STREAMK_AUTO, STREAMK_FORCE, STREAMK_NEVER, GROUP_M_SHIFT, SPLIT_SHIFT, DECODE_2D_LOADS = 0, 1, 2, 8, 16, 1 << 24
 
 _i64, _i32, _f32, _vp = ctypes.c_int64, ctypes.c_int, ctypes.c_float, ctypes.c_void_p
 

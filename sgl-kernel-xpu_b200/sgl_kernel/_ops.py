@@ -285,7 +285,7 @@ def _sched_flags(stream_k=True, group_m: int = 0, split: int = 0) -> int:
 
 
 def _gemm(mat_a, mat_b, scales_a, scales_b, out_dtype, variant: int = -1, num_sms: int = 0, stream_k=True, group_m: int = 0,
-          split: int = 0):
+          split: int = 0, extra_flags: int = 0):
     """fp8_blockwise_scaled_mm, include/sgl_kernel_ops.h:581-586 (allocates and returns C).
     stream_k: True (cost model), "force", or False ("never": whole tiles, no workspace)."""
     _check(mat_a.is_cuda and mat_b.is_cuda and scales_a.is_cuda and scales_b.is_cuda,
@@ -299,7 +299,7 @@ def _gemm(mat_a, mat_b, scales_a, scales_b, out_dtype, variant: int = -1, num_sm
     _check(lda % 16 == 0 and ldb % 16 == 0 and mat_a.data_ptr() % 16 == 0 and mat_b.data_ptr() % 16 == 0,
            "mat_a / mat_b rows must be 16-byte aligned")
     lib = _lib.load()
-    flags = _sched_flags(stream_k, group_m, split)
+    flags = _sched_flags(stream_k, group_m, split) | int(extra_flags)
     with torch.cuda.device(mat_a.device):
         stream = _stream_ptr(mat_a)
         ws_ptr, ws_bytes = None, 0

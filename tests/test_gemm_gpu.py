@@ -22,8 +22,14 @@ def product_variants():
     return [v for v in range(lib.sglk_gemm_num_variants()) if lib.sglk_gemm_variant_is_product(v)]
 
 
-PRODUCT = [0, 1, 2, 3, 4, 5, 6, 13, 14, 23, 29, 30, 31]
-DECODE = [30, 31]                      # swap-AB decode kernel: single CTA / CTA pair (M <= 256)
+PRODUCT = [0, 1, 2, 3, 4, 5, 6, 13, 14, 23, 29, 30, 31, 32]
+DECODE = [30, 31, 32]                  # swap-AB decode kernels: single CTA / CTA pair tiles (M <= 256), row-balanced (M <= 128)
+DECODE_MAX_M = {30: 256, 31: 256, 32: 128}
+
+
+def skip_if_too_many_tokens(variant, M):
+    if variant in DECODE and M > DECODE_MAX_M[variant]:
+        pytest.skip(f"decode kernel {variant}: M <= {DECODE_MAX_M[variant]}")
 
 
 def test_product_variant_list_is_current():
@@ -74,8 +80,7 @@ SHAPES = [(1, 128, 512), (5, 512, 1024), (127, 256, 512), (128, 128, 7168), (129
 @pytest.mark.parametrize("variant", PRODUCT)
 @pytest.mark.parametrize("M,N,K", SHAPES)
 def test_every_variant(variant, M, N, K):
-    if variant in DECODE and M > 256:
-        pytest.skip("decode kernel: M <= 256")
+    skip_if_too_many_tokens(variant, M)
     a, b, sa, sb = O.make_gemm_inputs(M, N, K, seed=M + N + K)
     odt = torch.bfloat16 if (M + variant) % 2 == 0 else torch.float16
     ref = O.baseline_scaled_mm(a, b, sa, sb, odt)
@@ -168,13 +173,12 @@ def test_row_major_activation_scales():
 
 @pytest.mark.parametrize("M,N,K", [(1, 2112, 7168), (64, 24576, 2048), (200, 512, 1024), (300, 1280, 4096), (1024, 1024, 512),
                                    (129, 384, 1536), (16, 4096, 7168)])
-@pytest.mark.parametrize("variant", [-1, 0, 2, 3, 13, 23, 30, 31])
+@pytest.mark.parametrize("variant", [-1, 0, 2, 3, 13, 23, 30, 31, 32])
 def test_k_contiguous_scales_vector_path(M, N, K, variant, force_stream_k):
     """scales_a row-major (the quant op's default output) and scales_b contiguous along K blocks (the view of a
     [N/128, K/128] weight-scale tensor): the promotion warps' 16-byte-per-4-blocks path, incl. stream-K segments that
     start in the middle of a group of four (K=1536 has 12 blocks: vector path; the others too)."""
-    if variant in DECODE and M > 256:
-        pytest.skip("decode kernel: M <= 256")
+    skip_if_too_many_tokens(variant, M)
     a, b, sa, sb = O.make_gemm_inputs(M, N, K, seed=M + K)
     ref = O.baseline_scaled_mm(a, b, sa, sb, torch.bfloat16)
     sad = sa.contiguous().to(DEV)                           # [M, G] row-major
@@ -245,12 +249,11 @@ STREAMK = [(1, 2112, 7168), (16, 24576, 7168), (64, 2112, 7168), (130, 4096, 204
 
 
 @pytest.mark.parametrize("M,N,K", STREAMK)
-@pytest.mark.parametrize("variant", [-1, 0, 2, 3, 5, 6, 13, 14, 23, 29, 30, 31])
+@pytest.mark.parametrize("variant", [-1, 0, 2, 3, 5, 6, 13, 14, 23, 29, 30, 31, 32])
 def test_stream_k_matches_whole_tiles_and_oracle(M, N, K, variant, force_stream_k):
     """Stream-K scheduling (tiles cut across CTAs, summed through the workspace by the last arriver)
     gives the oracle's answer, is bit-reproducible, and leaves its counters zeroed for the next launch."""
-    if variant in DECODE and M > 256:
-        pytest.skip("decode kernel: M <= 256")
+    skip_if_too_many_tokens(variant, M)
     lib = _lib.load()
     need = lib.sglk_gemm_workspace_bytes(M, N, K, variant, 0, _lib.STREAMK_FORCE)
     a, b, sa, sb = O.make_gemm_inputs(M, N, K, seed=M * 7 + N)
@@ -266,8 +269,8 @@ def test_stream_k_matches_whole_tiles_and_oracle(M, N, K, variant, force_stream_
     assert torch.equal(out_sk, out_sk2), "stream-K result not reproducible"
     if need == 0:
         assert torch.equal(out_sk, out_dp)
-    if variant == -1 and M <= 256 and N >= 2048:
-        assert need > 0, "decode shapes are expected to take the stream-K path"
+    if variant == -1 and M <= 256 and N >= 2048 and lib.sglk_gemm_pick_variant(M, N, K) != 32:
+        assert need > 0, "decode shapes on the tile kernels are expected to take the stream-K path"
 
 
 def test_stream_k_odd_sm_counts(force_stream_k):
@@ -277,7 +280,7 @@ def test_stream_k_odd_sm_counts(force_stream_k):
     ad, bd = a.to(DEV), b.t().contiguous().to(DEV).t()
     sad, sbd = sa.t().contiguous().to(DEV).t(), sb.to(DEV)
     ref = O.baseline_scaled_mm(a, b, sa, sb, torch.bfloat16)
-    for variant in (0, 30, 31):
+    for variant in (0, 30, 31, 32):
         for sms in (148, 37, 24, 7, 100):
             out = _ops._gemm(ad, bd, sad, sbd, torch.bfloat16, variant, sms, True)
             torch.cuda.synchronize()
@@ -378,6 +381,7 @@ DECODE_SHAPES = [(1, 128, 512), (3, 512, 1024), (5, 1024, 4096), (15, 384, 256),
 @pytest.mark.parametrize("M,N,K", DECODE_SHAPES)
 @pytest.mark.parametrize("sched", ["auto", "force", "never"])
 def test_decode_kernel(variant, M, N, K, sched):
+    skip_if_too_many_tokens(variant, M)
     a, b, sa, sb = O.make_gemm_inputs(M, N, K, seed=3 * M + N + K)
     odt = torch.bfloat16 if (M + N // 64) % 2 == 0 else torch.float16
     ref = O.baseline_scaled_mm(a, b, sa, sb, odt)
@@ -393,19 +397,37 @@ def test_decode_kernel(variant, M, N, K, sched):
 
 
 def test_decode_is_the_default_for_small_m():
-    """the swap-AB kernel is the default exactly where it measured faster (M <= 16, gemm.cu pick_variant): single CTAs
-    when the weight has fewer 128-row tiles than SMs, CTA pairs otherwise; larger batches stay on the token-major tiles"""
+    """the row-balanced swap-AB kernel is the default exactly where it measured faster (gemm.cu pick_variant): up to 16
+    tokens always, beyond that while 2 * M <= rows per CTA (N=24576 on 148 SMs: 168 rows, so up to 84 tokens); larger
+    batches stay on the token-major tiles"""
     lib = _lib.load()
     for M in (1, 8, 16):
-        assert lib.sglk_gemm_pick_variant(M, 2112, 7168) == 30
-        assert lib.sglk_gemm_pick_variant(M, 24576, 7168) == 31
+        assert lib.sglk_gemm_pick_variant(M, 2112, 7168) == 32
+        assert lib.sglk_gemm_pick_variant(M, 24576, 7168) == 32
+    for M in (17, 32, 64, 84):
+        assert lib.sglk_gemm_pick_variant(M, 24576, 7168) == 32
+        assert lib.sglk_gemm_pick_variant(M, 2112, 7168) == 0
     for N in (2112, 24576):
-        for M in (17, 32, 64, 128):
+        for M in (85, 128):
             assert lib.sglk_gemm_pick_variant(M, N, 7168) == 0
     assert lib.sglk_gemm_pick_variant(256, 2112, 7168) == 0
     assert lib.sglk_gemm_pick_variant(256, 24576, 7168) == 29
     assert lib.sglk_gemm_pick_variant(257, 24576, 7168) == 29
     assert lib.sglk_gemm_pick_variant(16384, 18432, 7168) == 29
+
+
+def test_rows_kernel_load_forms_agree():
+    """one 3-D TMA box per operand per stage (K % 128 == 0) and one 2-D box per K block give the same bits"""
+    for M, N, K in [(16, 2112, 7168), (64, 24576, 1024), (5, 1000, 2048), (128, 4096, 1536)]:
+        a, b, sa, sb = O.make_gemm_inputs(M, N, K, seed=M + N)
+        ad, bd = a.to(DEV), b.t().contiguous().to(DEV).t()
+        sad, sbd = sa.contiguous().to(DEV), sb.to(DEV)
+        ref = O.baseline_scaled_mm(a, b, sa, sb, torch.bfloat16)
+        y3 = _ops._gemm(ad, bd, sad, sbd, torch.bfloat16, 32)
+        y2 = _ops._gemm(ad, bd, sad, sbd, torch.bfloat16, 32, extra_flags=_lib.DECODE_2D_LOADS)
+        torch.cuda.synchronize()
+        check(y3.cpu(), ref)
+        assert torch.equal(y3, y2)
 
 
 # K tails (K % 128 != 0: TMA zero-fills the last K block, scale index is ceil(K/128)), odd N, unaligned ldc — the
@@ -415,10 +437,9 @@ RAGGED = [(37, 130, 144), (300, 1000, 2064), (5, 77, 272), (129, 250, 400), (64,
 
 
 @pytest.mark.parametrize("M,N,K", RAGGED)
-@pytest.mark.parametrize("variant", [-1, 0, 1, 3, 4, 29, 30, 31])
+@pytest.mark.parametrize("variant", [-1, 0, 1, 3, 4, 29, 30, 31, 32])
 def test_ragged_k_and_n(M, N, K, variant):
-    if variant in DECODE and M > 256:
-        pytest.skip("decode kernel: M <= 256")
+    skip_if_too_many_tokens(variant, M)
     a, b, sa, sb = O.make_gemm_inputs(M, N, K, seed=M + N + K)
     ref = O.baseline_scaled_mm(a, b, sa, sb, torch.bfloat16)
     out = gpu_mm(a, b, sa, sb, torch.bfloat16, variant)
