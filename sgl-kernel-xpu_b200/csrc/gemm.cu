@@ -1067,7 +1067,7 @@ static const Variant kVariants[] = {
     {"swapab_rows", 128, 0, 1, false, false, true},                  // decode, row-balanced: one contiguous weight-row range per CTA, no split-K
 };
 constexpr int kDecodeVariant1 = 30, kDecodeVariant2 = 31, kRowsVariant = 32;
-constexpr int kDecodeMaxTokens = 16;   // the default dispatch uses the swap-AB kernel up to here (pick_variant)
+constexpr int kRowsMaxTokens = 64;     // the default dispatch uses the row-balanced swap-AB kernel up to here (pick_variant)
 constexpr int kFirstStampVariant = 15, kLastStampVariant = 22;
 constexpr int kNumVariants = int(sizeof(kVariants) / sizeof(kVariants[0]));
 
@@ -1171,19 +1171,20 @@ static bool tma_store_ok(const void* C, int64_t ldc, int out_bytes) {
 // gemm_decode.cu, single CTAs for a few tokens, CTA pairs (tokens split over the pair: half the L2 -> smem traffic of the
 // activation tile) from 33 tokens up.
 static int pick_variant(int64_t M, int64_t N, int64_t K, bool plain_output, int num_sms = 0) {
-  // Row-balanced swap-AB kernel (gemm_decode.cu, swapab_rows): every CTA streams one contiguous range of
-  // R = ceil8(N / #SMs) weight rows for all of K.  Measured in a CUDA graph on B200 with every launch streaming its
-  // weight from HBM (tools/decode_ab.py, K=7168), against the best of the tile kernels (swap-AB tiles 30/31, 128-row
-  // token-major tiles 0): N=24576 (R=168): 30.2 / 30.3 / 31.5 / 33.2 us at M = 1 / 16 / 32 / 64 against 36.1 / 36.6 /
-  // 38.0 / 38.7 (0.89 -> 0.83 of the measured copy bandwidth instead of 0.75 -> 0.71); at M = 128 it loses (49.3 against
-  // 40.9): every CTA re-reads the whole activation matrix from L2, M / R of its weight bytes.  N=2112 (R=16): equal to
-  // the 4-way split tiles at M <= 16 (11.8 us: launch + prologue + one DRAM round trip, not bytes), behind them above.
-  // Hence: up to 16 tokens always, beyond that while the activation re-reads stay under half of the weight bytes.
-  if (plain_output && rows_supported(M, N, K)) {
-    const int64_t W = num_sms > 0 ? num_sms : 148;
-    const int64_t R = ((N + W - 1) / W + 7) / 8 * 8;
-    if (M <= kDecodeMaxTokens || 2 * M <= R) return kRowsVariant;
-  }
+  // Row-balanced swap-AB kernel (gemm_decode.cu, swapab_rows): every CTA streams one contiguous range of weight rows —
+  // R = ceil8(N / #SMs) rows for all of K, or for narrow weights R = ceil8(N / #clusters) rows for a half / a quarter of K
+  // with the cluster's partials summed through distributed shared memory.  Measured in a CUDA graph on B200 with every
+  // launch streaming its weight from HBM (tools/decode_ab.py, K=7168, us; best tile kernel = min of the swap-AB tiles
+  // 30/31 and the 128-row token-major tiles 0):
+  //      M =          1      16      32      64      128
+  //   N=24576 rows  29.5    29.7    30.9    32.8    49.6        (0.91 .. 0.84 of the measured copy bandwidth up to 64)
+  //           tiles 36.1    36.6    37.1    38.1    40.8
+  //   N=2112  rows   8.6     9.1    10.0    12.7    17.6        (clusters of 4 over K)
+  //           tiles 11.7    11.7    13.2    15.0    15.4
+  //   N=7168  rows    -     13.9      -     16.5    20.7        (clusters of 2)
+  //           tiles   -     16.1      -     19.0    20.6
+  // Beyond 64 tokens every CTA re-reading its K range of the activations from L2 costs more than the balance gains.
+  if (plain_output && M <= kRowsMaxTokens && rows_supported(M, N, K)) return kRowsVariant;
   // a handful of wide tiles on a narrow weight (N=2112, 129 <= M <= 256: 9 pair tiles for 74 pairs): 128-wide single-CTA
   // tiles give stream-K twice the units to balance
   if (M > 128 && M <= 256 && N < 4096) return 0;

@@ -115,6 +115,19 @@ __device__ __forceinline__ void fma2_scaled(float& a0, float& a1, uint32_t v0, u
 __device__ __forceinline__ void cp_async_mbar_arrive_noinc(uint32_t bar) {
   asm volatile("cp.async.mbarrier.arrive.noinc.shared::cta.b64 [%0];" ::"r"(bar) : "memory");
 }
+// tcgen05.mma (cta_group::1, e4m3 x e4m3 -> f32) with the operand descriptors given as 32-bit halves: the low words
+// (start address >> 4; leading byte offset 0) differ per tile, the high word (stride offset, version, swizzle) is shared
+__device__ __forceinline__ void mma_f8_lohi(uint32_t tmem_d, uint32_t a_lo, uint32_t b_lo, uint32_t desc_hi, uint32_t idesc,
+                                            uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t.reg .b64 da, db;\n\t"
+      "setp.ne.b32 p, %5, 0;\n\t"
+      "mov.b64 da, {%1, %3};\n\t"
+      "mov.b64 db, {%2, %3};\n\t"
+      "tcgen05.mma.cta_group::1.kind::f8f6f4 [%0], da, db, %4, p;\n\t}"
+      ::"r"(tmem_d), "r"(a_lo), "r"(b_lo), "r"(desc_hi), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
 __device__ __forceinline__ float4 lds_f32x4(uint32_t addr) {
   float4 v;
   asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(addr) : "memory");
@@ -768,6 +781,8 @@ struct RowsParams {
   uint32_t kb_tx_bytes;      // bytes TMA delivers per K block (boxes are always delivered whole, out-of-bounds zero-filled)
   int32_t kb3d;              // K % 128 == 0: the tensor maps are the [kblock][row][128 B] views, one TMA instruction per
                              // operand per stage; else 2-D maps (which zero-fill the K tail), one per operand per K block
+  int32_t ksplit;            // 1, 2 or 4: CTAs of one CLUSTER share a row range and take one K range each; their partials
+                             // are summed through distributed shared memory by the cluster's first CTA, in rank order
 };
 
 template <int NT, int S, int G>
@@ -850,10 +865,14 @@ fp8_blockwise_gemm_rows_kernel(const __grid_constant__ CUtensorMap tmap_w0, cons
   ptx::tc_fence_after();
   const uint32_t tmem_base = *reinterpret_cast<volatile uint32_t*>(smem_raw + (tmem_slot - smem_base));
 
-  // this CTA's weight rows [row0, row_end), walked in `passes` passes of rows_per_pass rows; every role runs the same loop
-  const int num_kb = p.num_k_blocks;
+  // this CTA's weight rows [row0, row_end), walked in `passes` passes of rows_per_pass rows, and its K blocks
+  // [kb_begin, kb_begin + num_kb) (all of K unless the cluster splits it); every role runs the same loops
+  const int ksplit = p.ksplit;
+  const uint32_t kq = ksplit > 1 ? ptx::cluster_ctarank() : 0u;
+  const int kb_begin = int(int64_t(p.num_k_blocks) * kq / ksplit);
+  const int num_kb = int(int64_t(p.num_k_blocks) * (kq + 1) / ksplit) - kb_begin;
   const int num_groups = (num_kb + G - 1) / G;
-  const int row0 = int(blockIdx.x) * p.rows_per_worker;
+  const int row0 = (int(blockIdx.x) / ksplit) * p.rows_per_worker;
   const int row_end = min(row0 + p.rows_per_worker, int(p.N));
 
   if (warp == 0) {
@@ -872,15 +891,15 @@ fp8_blockwise_gemm_rows_kernel(const __grid_constant__ CUtensorMap tmap_w0, cons
         if (ptx::elect_one()) {
           const uint32_t dst = smem_base + uint32_t(stage) * stage_bytes;
           if (p.kb3d) {
-            // whole boxes of G K blocks (K blocks past the end are zero-filled and never multiplied)
+            // whole boxes of G K blocks (K blocks past this CTA's range — the next CTA's, or zero fill past K — are never multiplied)
             ptx::mbar_arrive_expect_tx(full_bar(stage), uint32_t(G) * p.kb_tx_bytes);
-            ptx::tma_load_3d(&tmap_w0, full_bar(stage), dst, 0, base, g * G, pol_w);
-            if constexpr (S == 2) ptx::tma_load_3d(&tmap_w1, full_bar(stage), dst + p.sub1_off, 0, base + BLOCK_M, g * G, pol_w);
-            ptx::tma_load_3d(&tmap_x, full_bar(stage), dst + p.x_off, 0, 0, g * G, pol_x);
+            ptx::tma_load_3d(&tmap_w0, full_bar(stage), dst, 0, base, kb_begin + g * G, pol_w);
+            if constexpr (S == 2) ptx::tma_load_3d(&tmap_w1, full_bar(stage), dst + p.sub1_off, 0, base + BLOCK_M, kb_begin + g * G, pol_w);
+            ptx::tma_load_3d(&tmap_x, full_bar(stage), dst + p.x_off, 0, 0, kb_begin + g * G, pol_x);
           } else {
             ptx::mbar_arrive_expect_tx(full_bar(stage), uint32_t(nb) * p.kb_tx_bytes);
             for (int j = 0; j < nb; ++j) {
-              const int kb = g * G + j;
+              const int kb = kb_begin + g * G + j;
               ptx::tma_load_2d(&tmap_w0, full_bar(stage), dst + uint32_t(j) * p.sub_tile_bytes[0], kb * BLOCK_K, base, pol_w);
               if constexpr (S == 2)
                 ptx::tma_load_2d(&tmap_w1, full_bar(stage), dst + p.sub1_off + uint32_t(j) * p.sub_tile_bytes[1], kb * BLOCK_K,
@@ -894,55 +913,61 @@ fp8_blockwise_gemm_rows_kernel(const __grid_constant__ CUtensorMap tmap_w0, cons
       }
     }
     __syncwarp();
-  } else if (warp == 1) {
-    // =========================== MMA issuer ===========================
+    if (ksplit > 1) ptx::cluster_sync();               // (1) the cluster's partials are in shared memory
+  } else if (warp == 1 || warp == 2) {
+    // =========================== MMA issuers ===========================
+    // Two warps (the second one also owns the TMEM allocation) take alternate stages: at these widths the tensor pipe
+    // needs 8-64 clk per MMA but one thread issues one only every ~35-40 clk (measured: ~175 clk per K block of four
+    // MMAs, whatever the stage depth, load form or issue order), which bounded the small-N shapes.  MMAs of different
+    // stages touch different smem and different TMEM columns, so the two issue streams need no ordering between them;
+    // each thread's commits cover its own MMAs.
     ptx::reg_dealloc<40>();
     constexpr uint32_t idesc = make_idesc(BLOCK_M, NT);
     const uint32_t tmem_base_u = __shfl_sync(0xFFFFFFFFu, tmem_base, 0);
-    const uint64_t desc_hi = make_smem_desc(0);
-    int stage = 0, slot = 0;
+    const uint32_t desc_hi = uint32_t(make_smem_desc(0) >> 32);
+    const uint32_t tile_lo[2] = {p.sub_tile_bytes[0] >> 4, p.sub_tile_bytes[1] >> 4};
+    const uint32_t x_tile_lo = p.x_tile_bytes >> 4, sub1_lo = p.sub1_off >> 4, x_lo = p.x_off >> 4;
+    int stage = 0, slot = 0, turn = warp - 1;          // this warp issues when turn == 0
     uint32_t phase = 0, slot_phase = 0;
     for (int pass = 0; pass < p.passes; ++pass) {
       if (row0 + pass * p.rows_per_pass >= row_end) break;
       for (int g = 0; g < num_groups; ++g) {
-        const int nb = min(G, num_kb - g * G);
-        ptx::mbar_wait(full_bar(stage), phase);
-        ptx::mbar_wait(tempty_bar(slot), slot_phase ^ 1);   // slot drained by every promotion warp?
-        ptx::tc_fence_after();
-        const uint32_t st_addr = smem_base + uint32_t(stage) * stage_bytes;
-        if (ptx::elect_one()) {
-          // The four K=32 MMAs of one (K block, sub-tile) accumulate into the same TMEM columns: a dependent chain, and at
-          // these widths (N = 16..128) an MMA is latency-, not throughput-bound (measured ~290 clk per chain of four at
-          // N=16, where the pipe time is 4 x 8 clk).  The G x S chains of a stage are independent, so they are issued
-          // round-robin: chain latency overlaps across chains.
+        if (turn == 0) {
+          const int nb = min(G, num_kb - g * G);
+          ptx::mbar_wait(full_bar(stage), phase);
+          ptx::mbar_wait(tempty_bar(slot), slot_phase ^ 1);   // slot drained by every promotion warp?
+          ptx::tc_fence_after();
+          const uint32_t st_lo = ((smem_base + uint32_t(stage) * stage_bytes) & 0x3FFFFu) >> 4;
+          const uint32_t d0 = tmem_base_u + uint32_t(slot * C::SLOT_COLS);
+          if (ptx::elect_one()) {
+            // The four K=32 MMAs of one (K block, sub-tile) accumulate into the same TMEM columns — a dependent chain;
+            // the G x S chains of a stage are independent and are issued round-robin.
 #pragma unroll
-          for (int k = 0; k < BLOCK_K / UMMA_K; ++k) {
+            for (int k = 0; k < BLOCK_K / UMMA_K; ++k) {
 #pragma unroll
-            for (int j = 0; j < G; ++j) {
-              if (j < nb) {
-                const uint64_t db = desc_hi | uint64_t(((st_addr + p.x_off + uint32_t(j) * p.x_tile_bytes) & 0x3FFFFu) >> 4);
+              for (int j = 0; j < G; ++j) {
+                if (j < nb) {
+                  const uint32_t b_lo = st_lo + x_lo + uint32_t(j) * x_tile_lo + uint32_t(k * (UMMA_K >> 4));
 #pragma unroll
-                for (int s = 0; s < S; ++s) {
-                  const uint32_t a_addr = st_addr + (s ? p.sub1_off : 0u) + uint32_t(j) * p.sub_tile_bytes[s];
-                  const uint64_t da = desc_hi | uint64_t((a_addr & 0x3FFFFu) >> 4);
-                  const uint32_t d_tmem = tmem_base_u + uint32_t(slot * C::SLOT_COLS + (j * S + s) * NT);
-                  ptx::mma_f8f6f4<1>(d_tmem, da + uint64_t(k * (UMMA_K >> 4)), db + uint64_t(k * (UMMA_K >> 4)), idesc,
-                                     k > 0 ? 1u : 0u);
+                  for (int s = 0; s < S; ++s) {
+                    const uint32_t a_lo = st_lo + (s ? sub1_lo : 0u) + uint32_t(j) * tile_lo[s] + uint32_t(k * (UMMA_K >> 4));
+                    dptx::mma_f8_lohi(d0 + uint32_t((j * S + s) * NT), a_lo, b_lo, desc_hi, idesc, k > 0 ? 1u : 0u);
+                  }
                 }
               }
             }
+            ptx::tc_commit<1>(empty_bar(stage));     // smem stage reusable once these MMAs have read it
+            ptx::tc_commit<1>(tfull_bar(slot));      // the hand-off's partials are complete
           }
-          ptx::tc_commit<1>(empty_bar(stage));     // smem stage reusable once these MMAs have read it
-          ptx::tc_commit<1>(tfull_bar(slot));      // the hand-off's partials are complete
+          __syncwarp();
         }
-        __syncwarp();
+        turn ^= 1;
         if (++stage == nstages) { stage = 0; phase ^= 1; }
         if (++slot == kSlots) { slot = 0; slot_phase ^= 1; }
       }
     }
     __syncwarp();
-  } else if (warp == 2) {
-    ptx::reg_dealloc<40>();                        // TMEM owner: only waits for the end
+    if (ksplit > 1) ptx::cluster_sync();               // (1)
   } else if (warp == 3) {
     // =========================== scale loader ===========================
     // per K block: sa[token, kb] for every token and the sb[kb, .] of the (up to three) 128-row scale blocks this pass
@@ -960,7 +985,7 @@ fp8_blockwise_gemm_rows_kernel(const __grid_constant__ CUtensorMap tmap_w0, cons
         ptx::mbar_wait(sempty_bar(stage), phase ^ 1);
         const uint32_t slot = scale_base + uint32_t(stage) * C::SCALE_SLOT;
         for (int j = 0; j < nb; ++j) {
-          const int kb = g * G + j;
+          const int kb = kb_begin + g * G + j;
           const uint32_t kslot = slot + uint32_t(j) * C::KB_SCALE_BYTES;
 #pragma unroll
           for (int q = 0; q < (NT + 31) / 32; ++q) {
@@ -976,9 +1001,11 @@ fp8_blockwise_gemm_rows_kernel(const __grid_constant__ CUtensorMap tmap_w0, cons
     ptx::cp_async_commit();
     ptx::cp_async_wait<0>();
     __syncwarp();
+    if (ksplit > 1) ptx::cluster_sync();               // (1)
   } else {
     // =========================== promotion + epilogue warps ===========================
     ptx::reg_alloc<232>();
+    bool synced = false;
     const int ew = warp - 4;
     const int quarter = warp & 3;                      // TMEM lanes this warp may touch: 32*quarter .. +31
     const int colgroup = ew >> 2;                      // which half of the token columns
@@ -1069,6 +1096,38 @@ fp8_blockwise_gemm_rows_kernel(const __grid_constant__ CUtensorMap tmap_w0, cons
         if (++stage == nstages) { stage = 0; phase ^= 1; }
         if (++slot == kSlots) { slot = 0; slot_phase ^= 1; }
       }
+      // ---------------- split K: the cluster's partials meet in the first CTA ----------------
+      if (ksplit > 1) {
+        // (one pass per CTA in this mode.)  Every MMA of this CTA has completed — this warp has seen the commit of
+        // every hand-off — so the operand ring is free and holds the partial: [warp][value][lane] as float4.
+        constexpr int V4 = S * CW / 4;
+        if (kq != 0) {
+          float4* red = reinterpret_cast<float4*>(smem_raw) + ew * V4 * 32 + lane;
+#pragma unroll
+          for (int s = 0; s < S; ++s)
+#pragma unroll
+            for (int j = 0; j < CW / 4; ++j)
+              red[(s * (CW / 4) + j) * 32] = make_float4(accum[s][4 * j], accum[s][4 * j + 1], accum[s][4 * j + 2], accum[s][4 * j + 3]);
+        }
+        ptx::cluster_sync();                           // (1): release / acquire at cluster scope
+        synced = true;
+        if (kq != 0) break;
+        // fixed order (bit-reproducible): own + rank 1 + rank 2 + ...
+        for (uint32_t q = 1; q < uint32_t(ksplit); ++q) {
+          const uint32_t peer = ptx::mapa(smem_base, q) + uint32_t(ew * V4 * 32 + lane) * 16u;
+#pragma unroll
+          for (int s = 0; s < S; ++s)
+#pragma unroll
+            for (int j = 0; j < CW / 4; ++j) {
+              float4 t;
+              asm volatile("ld.shared::cluster.v4.f32 {%0, %1, %2, %3}, [%4];"
+                           : "=f"(t.x), "=f"(t.y), "=f"(t.z), "=f"(t.w)
+                           : "r"(peer + uint32_t((s * (CW / 4) + j) * 32) * 16u)
+                           : "memory");
+              accum[s][4 * j] += t.x; accum[s][4 * j + 1] += t.y; accum[s][4 * j + 2] += t.z; accum[s][4 * j + 3] += t.w;
+            }
+        }
+      }
       // ---------------- C^T out of the registers: lane = output column n, accum[s][j] = token t0 + j ----------------
 #pragma unroll
       for (int s = 0; s < S; ++s) {
@@ -1098,27 +1157,53 @@ fp8_blockwise_gemm_rows_kernel(const __grid_constant__ CUtensorMap tmap_w0, cons
       }
     }
     __syncwarp();
+    if (ksplit > 1 && !synced) ptx::cluster_sync();    // (1) — a CTA without rows (the host never launches one)
   }
 
   // =========================== teardown ===========================
   ptx::tc_fence_before();
-  __syncthreads();
+  if (ksplit > 1) ptx::cluster_sync();                 // (2) nobody leaves while the first CTA may still read its shared memory
+  else __syncthreads();
   if (warp == 2) ptx::tmem_dealloc<1>(tmem_base, C::TMEM_COLS);
 }
 
 struct RowsPlan {
-  int nt, S, G, workers, rows_per_worker, passes, rows_per_pass, stages;
+  int nt, S, G, ksplit, workers, rows_per_worker, passes, rows_per_pass, stages;
   uint32_t sub_rows[2], x_rows, stage_bytes, sub1_off, x_off, kb_tx_bytes;
 };
 
 bool rows_supported(int64_t M, int64_t N, int64_t K) { return M >= 1 && M <= 128 && N >= 1 && K >= 1; }
 
-static RowsPlan make_rows_plan(int64_t M, int64_t N, int64_t K, int num_sms) {
-  (void)K;
+static int rows_max_clusters(int cs, int num_sms);
+
+static RowsPlan make_rows_plan(int64_t M, int64_t N, int64_t K, int num_sms, int flags) {
   RowsPlan pl;
   pl.nt = decode_nt(M);
   const int64_t W = num_sms < 1 ? 1 : num_sms;
-  int64_t R = ((N + W - 1) / W + 7) / 8 * 8;                  // rows per CTA, whole 8-row swizzle atoms
+  const int64_t num_kb = (K + BLOCK_K - 1) / BLOCK_K;
+  // K split over the CTAs of a cluster.  An MMA reads its whole 128-row A tile from shared memory whatever part of it
+  // holds rows of the range (measured: ~70 clk per K=32 MMA at these widths, i.e. ~0.14 us per K block per CTA), so a
+  // narrow weight spread over all SMs as 16-row ranges is bound by 56 K blocks of mostly empty MMAs (N=2112: 11.4 us).
+  // Splitting K four ways gives every CTA a quarter of the K blocks on four times the rows, and a quarter of the
+  // activation re-reads.  Used while there are fewer 128-row tiles than clusters; flags bits 16..23 override (1, 2, 4).
+  int ks = (flags >> 16) & 0xFF;
+  if (ks == 0) {
+    const int64_t tiles128 = (N + 127) / 128;
+    ks = (num_kb >= 8 && tiles128 * 4 <= W) ? 4 : ((num_kb >= 8 && tiles128 * 2 <= W) ? 2 : 1);
+  }
+  if (ks != 1 && ks != 2 && ks != 4) ks = 1;
+  if (ks > num_kb) ks = 1;
+  int64_t groups = W;
+  if (ks > 1) {
+    groups = rows_max_clusters(ks, int(W));
+    if (groups < 1) { ks = 1; groups = W; }
+  }
+  int64_t R = ((N + groups - 1) / groups + 7) / 8 * 8;        // rows per CTA (cluster), whole 8-row swizzle atoms
+  if (ks > 1 && R > 256) {                                    // split K runs one pass per CTA
+    ks = 1; groups = W;
+    R = ((N + groups - 1) / groups + 7) / 8 * 8;
+  }
+  pl.ksplit = ks;
   pl.passes = int((R + 255) / 256);
   pl.rows_per_pass = int(((R + pl.passes - 1) / pl.passes + 7) / 8 * 8);
   R = int64_t(pl.rows_per_pass) * pl.passes;
@@ -1128,15 +1213,19 @@ static RowsPlan make_rows_plan(int64_t M, int64_t N, int64_t K, int num_sms) {
   pl.sub_rows[0] = uint32_t(pl.rows_per_pass > BLOCK_M ? BLOCK_M : pl.rows_per_pass);
   pl.sub_rows[1] = pl.S == 2 ? uint32_t(pl.rows_per_pass - BLOCK_M) : 0u;
   pl.x_rows = uint32_t((M + 7) / 8 * 8);
-  // K blocks per ring stage / accumulator hand-off
-  // (more K blocks per stage = more independent MMA chains in flight and fewer hand-offs; bounded by TMEM — a hand-off
-  // is G x S x NT columns and two must fit — and by the ring: at least ~3 stages of G K blocks each)
-  pl.G = pl.S == 2 ? (pl.nt <= 32 ? 2 : 1) : (pl.nt == 16 ? 8 : (pl.nt <= 64 ? 4 : 2));
+  // K blocks per ring stage / accumulator hand-off: more of them = more independent MMA chains in flight and fewer
+  // hand-offs; bounded by TMEM (a hand-off is G x S x NT columns and two must fit) and by the ring (three stages at
+  // least, or the loads cannot run ahead of the MMAs).  Candidates are the instantiations launch_rows_cfg knows.
+  pl.kb_tx_bytes = (pl.sub_rows[0] + pl.sub_rows[1] + pl.x_rows) * BLOCK_K;
+  {
+    const int first = pl.S == 2 ? (pl.nt <= 32 ? 2 : 1) : (pl.nt == 16 ? 8 : (pl.nt <= 64 ? 4 : 2));
+    const int second = pl.S == 2 ? first : (pl.nt == 128 ? 1 : 2);
+    pl.G = (kMaxDynSmem - kRowsTailBytes) / int(uint32_t(first) * pl.kb_tx_bytes) >= 3 ? first : second;
+  }
   // tiles are box-rows x 128 B (multiples of 1 KB); the MMA reads 128 weight rows / NT activation rows from a tile's base
   // whatever the box held: what lies behind (the next tile, the next stage, the 16 KB tail) is addressable smem
   pl.sub1_off = uint32_t(pl.G) * pl.sub_rows[0] * BLOCK_K;
   pl.x_off = pl.sub1_off + uint32_t(pl.G) * pl.sub_rows[1] * BLOCK_K;
-  pl.kb_tx_bytes = (pl.sub_rows[0] + pl.sub_rows[1] + pl.x_rows) * BLOCK_K;
   pl.stage_bytes = uint32_t(pl.G) * pl.kb_tx_bytes;
   int n = (kMaxDynSmem - kRowsTailBytes) / int(pl.stage_bytes);
   if (n > kDecMaxStages) n = kDecMaxStages;
@@ -1152,8 +1241,55 @@ static int launch_rows(const CUtensorMap& tw0, const CUtensorMap& tw1, const CUt
   auto kern = fp8_blockwise_gemm_rows_kernel<NT, S, G, OutT>;
   static std::atomic<uint64_t> configured{0};
   if (int e = ensure_max_dyn_smem(kern, configured, kMaxDynSmem)) return e;
-  kern<<<dim3(unsigned(workers)), dim3(RowsCfg<NT, S, G>::kThreads), kMaxDynSmem, st>>>(tw0, tw1, tx, p);
-  return int(cudaGetLastError());
+  cudaLaunchConfig_t cfg;
+  memset(&cfg, 0, sizeof(cfg));
+  cfg.gridDim = dim3(unsigned(workers * p.ksplit));
+  cfg.blockDim = dim3(RowsCfg<NT, S, G>::kThreads);
+  cfg.dynamicSmemBytes = kMaxDynSmem;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = unsigned(p.ksplit);
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  return int(cudaLaunchKernelEx(&cfg, kern, tw0, tw1, tx, p));
+}
+
+// How many clusters of `cs` CTAs of this kernel (one CTA per SM: 227 KB of shared memory) the current device runs at
+// once — clusters are placed inside a GPC, so it is less than #SMs / cs.  Every instantiation has the same footprint;
+// one is asked, once per (device, cluster size).
+static int rows_max_clusters(int cs, int num_sms) {
+  static std::atomic<int> cache[64][5];
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64 || cs < 1 || cs > 4) return num_sms / (cs < 1 ? 1 : cs);
+  int n = cache[dev][cs].load(std::memory_order_acquire);
+  if (n == 0) {
+    auto kern = fp8_blockwise_gemm_rows_kernel<16, 1, 8, __nv_bfloat16>;
+    n = -1;
+    if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kMaxDynSmem) == cudaSuccess) {
+      cudaLaunchConfig_t cfg;
+      memset(&cfg, 0, sizeof(cfg));
+      cfg.gridDim = dim3(unsigned(cs * 64));
+      cfg.blockDim = dim3(RowsCfg<16, 1, 8>::kThreads);
+      cfg.dynamicSmemBytes = kMaxDynSmem;
+      cudaLaunchAttribute attr[1];
+      attr[0].id = cudaLaunchAttributeClusterDimension;
+      attr[0].val.clusterDim.x = unsigned(cs);
+      attr[0].val.clusterDim.y = 1;
+      attr[0].val.clusterDim.z = 1;
+      cfg.attrs = attr;
+      cfg.numAttrs = 1;
+      int got = 0;
+      if (cudaOccupancyMaxActiveClusters(&got, kern, &cfg) == cudaSuccess && got > 0) n = got;
+    }
+    (void)cudaGetLastError();
+    cache[dev][cs].store(n, std::memory_order_release);
+  }
+  if (n < 0) return 0;
+  const int cap = num_sms / cs;                       // a caller that restricts num_sms restricts the clusters too
+  return n < cap ? n : cap;
 }
 
 template <typename OutT>
@@ -1162,12 +1298,16 @@ static int launch_rows_cfg(const RowsPlan& pl, const CUtensorMap& tw0, const CUt
   const int key = pl.nt * 100 + pl.S * 10 + pl.G;
   switch (key) {
     case 1618: return launch_rows<16, 1, 8, OutT>(tw0, tw1, tx, p, pl.workers, st);
+    case 1612: return launch_rows<16, 1, 2, OutT>(tw0, tw1, tx, p, pl.workers, st);
     case 1622: return launch_rows<16, 2, 2, OutT>(tw0, tw1, tx, p, pl.workers, st);
     case 3214: return launch_rows<32, 1, 4, OutT>(tw0, tw1, tx, p, pl.workers, st);
+    case 3212: return launch_rows<32, 1, 2, OutT>(tw0, tw1, tx, p, pl.workers, st);
     case 3222: return launch_rows<32, 2, 2, OutT>(tw0, tw1, tx, p, pl.workers, st);
     case 6414: return launch_rows<64, 1, 4, OutT>(tw0, tw1, tx, p, pl.workers, st);
+    case 6412: return launch_rows<64, 1, 2, OutT>(tw0, tw1, tx, p, pl.workers, st);
     case 6421: return launch_rows<64, 2, 1, OutT>(tw0, tw1, tx, p, pl.workers, st);
     case 12812: return launch_rows<128, 1, 2, OutT>(tw0, tw1, tx, p, pl.workers, st);
+    case 12811: return launch_rows<128, 1, 1, OutT>(tw0, tw1, tx, p, pl.workers, st);
     case 12821: return launch_rows<128, 2, 1, OutT>(tw0, tw1, tx, p, pl.workers, st);
     default: return SGLK_E_VARIANT;
   }
@@ -1178,8 +1318,10 @@ int rows_entry(const void* A, const void* B, const float* sa, const float* sb, v
                int64_t lda, int64_t ldb, int64_t ldc, int64_t sa_sm, int64_t sa_sk, int64_t sb_sk, int64_t sb_sn,
                int out_dtype, int num_sms, int flags, cudaStream_t st) {
   if (num_sms <= 0) num_sms = device_sm_count();
-  const RowsPlan pl = make_rows_plan(M, N, K, num_sms);
+  const RowsPlan pl = make_rows_plan(M, N, K, num_sms, flags);
   if (pl.stages < 2) return SGLK_E_SHAPE;
+  // the split-K partial of a CTA (S * NT/2 KB) lives in the operand ring
+  if (pl.ksplit > 1 && int64_t(pl.S) * (pl.nt / 2) * 1024 > int64_t(pl.stages) * pl.stage_bytes) return SGLK_E_SHAPE;
   RowsParams p;
   memset(&p, 0, sizeof(p));
   p.sa = sa; p.sb = sb; p.C = Cout;
@@ -1195,6 +1337,7 @@ int rows_entry(const void* A, const void* B, const float* sa, const float* sb, v
   p.sub_tile_bytes[0] = pl.sub_rows[0] * BLOCK_K;
   p.sub_tile_bytes[1] = pl.sub_rows[1] * BLOCK_K;
   p.x_tile_bytes = pl.x_rows * BLOCK_K;
+  p.ksplit = pl.ksplit;
   p.kb3d = (K % BLOCK_K == 0 && ldb % 16 == 0 && lda % 16 == 0 && !(flags & SGLK_GEMM_DECODE_2D_LOADS)) ? 1 : 0;
   p.sub1_off = pl.sub1_off;
   p.x_off = pl.x_off;

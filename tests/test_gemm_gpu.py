@@ -397,23 +397,38 @@ def test_decode_kernel(variant, M, N, K, sched):
 
 
 def test_decode_is_the_default_for_small_m():
-    """the row-balanced swap-AB kernel is the default exactly where it measured faster (gemm.cu pick_variant): up to 16
-    tokens always, beyond that while 2 * M <= rows per CTA (N=24576 on 148 SMs: 168 rows, so up to 84 tokens); larger
-    batches stay on the token-major tiles"""
+    """the row-balanced swap-AB kernel is the default exactly where it measured faster (gemm.cu pick_variant): up to 64
+    tokens; larger batches stay on the token-major tiles"""
     lib = _lib.load()
-    for M in (1, 8, 16):
-        assert lib.sglk_gemm_pick_variant(M, 2112, 7168) == 32
-        assert lib.sglk_gemm_pick_variant(M, 24576, 7168) == 32
-    for M in (17, 32, 64, 84):
-        assert lib.sglk_gemm_pick_variant(M, 24576, 7168) == 32
-        assert lib.sglk_gemm_pick_variant(M, 2112, 7168) == 0
-    for N in (2112, 24576):
-        for M in (85, 128):
+    for N in (2112, 4096, 7168, 24576, 129280):
+        for M in (1, 8, 16, 17, 32, 64):
+            assert lib.sglk_gemm_pick_variant(M, N, 7168) == 32
+        for M in (65, 128):
             assert lib.sglk_gemm_pick_variant(M, N, 7168) == 0
     assert lib.sglk_gemm_pick_variant(256, 2112, 7168) == 0
     assert lib.sglk_gemm_pick_variant(256, 24576, 7168) == 29
     assert lib.sglk_gemm_pick_variant(257, 24576, 7168) == 29
     assert lib.sglk_gemm_pick_variant(16384, 18432, 7168) == 29
+
+
+@pytest.mark.parametrize("M,N,K", [(16, 2112, 7168), (64, 2112, 7168), (128, 4096, 7168), (5, 1000, 2048), (33, 7168, 1024),
+                                   (16, 4096, 7168), (1, 128, 1024), (128, 640, 8192)])
+def test_rows_kernel_cluster_split_k(M, N, K):
+    """K split over clusters of 1 / 2 / 4 CTAs (partials summed through distributed shared memory in rank order):
+    the oracle's answer for every split, reproducible, and the automatic choice is one of them"""
+    a, b, sa, sb = O.make_gemm_inputs(M, N, K, seed=M + N + K)
+    ad, bd = a.to(DEV), b.t().contiguous().to(DEV).t()
+    sad, sbd = sa.contiguous().to(DEV), sb.to(DEV)
+    ref = O.baseline_scaled_mm(a, b, sa, sb, torch.bfloat16)
+    outs = {ks: _ops._gemm(ad, bd, sad, sbd, torch.bfloat16, 32, split=ks) for ks in (1, 2, 4)}
+    auto = _ops._gemm(ad, bd, sad, sbd, torch.bfloat16, 32)
+    again = {ks: _ops._gemm(ad, bd, sad, sbd, torch.bfloat16, 32, split=ks) for ks in (2, 4)}
+    torch.cuda.synchronize()
+    for ks, y in outs.items():
+        check(y.cpu(), ref)
+    for ks, y in again.items():
+        assert torch.equal(y, outs[ks]), f"split {ks} not reproducible"
+    assert any(torch.equal(auto, y) for y in outs.values())
 
 
 def test_rows_kernel_load_forms_agree():

@@ -2,7 +2,8 @@
 """A/B of the decode GEMM variants with every launch streaming its weight from HBM: the launches of one CUDA graph
 rotate over enough weight copies to exceed 2 x L2 (bench.py's config-3 method), GPU-side time per launch.
 usage: decode_ab.py [variants=-1,0,30,31,32,32d] [Ms=1,16,32,64,128] [Ns=2112,24576] [Ks=7168]
-("32d" = variant 32 with one 2-D TMA load per K block instead of one 3-D load per stage)"""
+("32d" = variant 32 with one 2-D TMA load per K block instead of one 3-D load per stage; "32s4" / "32s2" / "32s1" =
+variant 32 with K split over clusters of 4 / 2 / not at all)"""
 import json, os, sys
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path[:0] = [ROOT, os.path.join(ROOT, "sgl-kernel-xpu_b200")]
@@ -18,6 +19,9 @@ peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json"))) if os.path.ex
 def run(a, bt, sa, sb, v):
     if v.endswith("d"):
         return _ops._gemm(a, bt, sa, sb, torch.bfloat16, int(v[:-1]), extra_flags=_lib.DECODE_2D_LOADS)
+    if "s" in v:                                     # "32s4": variant 32 with K split over clusters of 4 (1 = no split)
+        vid, ks = v.split("s")
+        return _ops._gemm(a, bt, sa, sb, torch.bfloat16, int(vid), split=int(ks))
     return _ops._gemm(a, bt, sa, sb, torch.bfloat16, int(v))
 
 
