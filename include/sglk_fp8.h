@@ -238,6 +238,42 @@ SGLK_API int sglk_fp8_blockwise_scaled_mm_allgather(const void* A, const void* B
                                            void* workspace, int64_t workspace_bytes, void* stream);
 
 /*
+ * Row-sharded activation quantisation for the N-sharded layer on several GPUs, and the GEMM that consumes it while it
+ * arrives (no reference counterpart: the reference has no communication layer).  Replicated activations
+ * make every rank quantise the whole batch; here rank r quantises only ITS rows — the same arithmetic as
+ * sglk_per_token_group_quant_8bit (group 128, e4m3, row-major fp32 scales; bit-identical, quantisation is row-local) —
+ * and the codes and scales land in EVERY rank's copy of a symmetric [M, hidden] / [M, hidden/128] buffer:
+ *   input            this rank's rows, [rows, hidden] bf16/f16 contiguous, 32-byte aligned
+ *   output_q/_s      where those rows live in the code / scale buffer (base + row offset); with multicast != 0 these
+ *                    are NVLS multicast addresses (one multimem.st reaches every GPU), else plain device pointers
+ *   ready_counters   the counter of the first of these rows' blocks (same addressing rule).  Every rows_per_counter rows
+ *                    share one uint32 counter; it is incremented (release, system scope) once per finished chunk of 16384
+ *                    elements, rows_per_counter * hidden / 16384 times per block and call.  Counters are never reset.
+ * Requirements: hidden % 128 == 0, rows % rows_per_counter == 0, rows_per_counter * hidden % 16384 == 0.
+ */
+SGLK_API int sglk_per_token_group_quant_fp8_bcast(const void* input, void* output_q, float* output_s,
+                                         uint32_t* ready_counters, int64_t rows, int64_t hidden,
+                                         int64_t rows_per_counter, int in_dtype, float eps, int multicast,
+                                         void* stream);
+
+/*
+ * sglk_fp8_blockwise_scaled_mm whose A rows (codes and row-major scales) ARRIVE WHILE THE KERNEL RUNS: one arrival
+ * counter per 256 rows (row_ready_counters[m / 256], as written by sglk_per_token_group_quant_fp8_bcast with
+ * rows_per_counter = 256); the 256-row tiles of a block are started once int32(counter - ready_target) >= 0, i.e. the
+ * caller passes (calls so far on this buffer + 1) * 256 * K / 16384.  The blocks are walked in arrival order: the
+ * panel of rank panel_rank first (rows [rank, rank + 1) * M / world), then the j-th block of every other panel, nearest
+ * rank first, for j = 0, 1, ...  Same result bits as sglk_fp8_blockwise_scaled_mm on the completed buffers.
+ * Requirements: M % (256 * panel_world) == 0, N >= 256, K-block-contiguous scales (sa_stride_k == sb_stride_k == 1,
+ * 16-byte aligned rows), C 16-byte aligned rows.  A counter that never arrives traps the kernel after ~4 s.
+ */
+SGLK_API int sglk_fp8_blockwise_scaled_mm_gated(const void* A, const void* B, const float* sa, const float* sb, void* C,
+                                       int64_t M, int64_t N, int64_t K, int64_t lda, int64_t ldb, int64_t ldc,
+                                       int64_t sa_stride_m, int64_t sa_stride_k, int64_t sb_stride_k,
+                                       int64_t sb_stride_n, int out_dtype, int num_sms,
+                                       const uint32_t* row_ready_counters, uint32_t ready_target, int panel_rank,
+                                       int panel_world, void* stream);
+
+/*
  * Replaces: void fp8_blockwise_scaled_grouped_mm(output, a_ptrs, ..., problem_sizes, expert_offsets, workspace)
  *   declared /root/reference/include/sgl_kernel_ops.h:660-678, wrapped python/sgl_kernel/moe.py:236-276, semantics
  *   pinned by tests/test_fp8_blockwise_moe.py:27-51,66-171 (the reference ships no kernel).

@@ -70,6 +70,16 @@ struct GemmParams {
   const int4* grp_tiles;          // one entry per 128-row m-tile: {first row in the stack, valid rows, expert, 0}
   const int32_t* grp_num_m_tiles; // how many entries (written on the device by build_group_tiles_kernel)
   int64_t grp_sb_expert_stride;   // floats between the experts' weight-scale matrices
+  // gated mode (kWaitA instantiation, sglk_fp8_blockwise_scaled_mm_gated): the rows of A (and of sa) arrive while the
+  // kernel runs — written by the row-sharded quantisation of every rank (quant_bcast.cu) — one arrival counter per
+  // 256-row m-block; a tile is started once int32(counter - a_ready_target) >= 0.  The m-blocks are walked own panel
+  // first, then one "slice" (the j-th m-block of every other rank's panel, nearest rank first) after the other: the
+  // order in which the panels, all sent at once, fill up.
+  const uint32_t* a_ready;
+  uint32_t a_ready_target;
+  int32_t panel_own;              // m-blocks per rank panel
+  int32_t panel_rank, panel_world;
+  int32_t panel_group;            // remote m-blocks per rasterisation group (a whole number of slices)
 };
 
 constexpr int kMaxDests = 8;
@@ -141,6 +151,47 @@ __device__ __forceinline__ void tile_coords(int tile, const GemmParams& p, int& 
   nb = in_g / rows;
 }
 
+// gated mode: tile index -> (physical m-block, n-block) in arrival order (see GemmParams::a_ready)
+__device__ __forceinline__ void tile_coords_panels(int tile, const GemmParams& p, int& mb, int& nb) {
+  const int own = p.panel_own, nn = p.num_n_blocks;
+  int L;                                                        // position in the walk order
+  if (tile < own * nn) {                                        // own panel: groups of group_m m-blocks, n-major
+    const int per_group = p.group_m * nn;
+    const int g = tile / per_group, first = g * p.group_m;
+    const int rows = min(p.group_m, own - first), in_g = tile - g * per_group;
+    L = first + in_g % rows;
+    nb = in_g / rows;
+  } else {                                                      // the other panels: groups of whole slices
+    const int t = tile - own * nn, per_group = p.panel_group * nn;
+    const int g = t / per_group, first = g * p.panel_group;
+    const int rows = min(p.panel_group, (p.num_m_blocks - own) - first), in_g = t - g * per_group;
+    L = own + first + in_g % rows;
+    nb = in_g / rows;
+  }
+  if (L < own) {
+    mb = p.panel_rank * own + L;
+  } else {
+    const int r = L - own, w1 = p.panel_world - 1;
+    const int j = r / w1, i = r - j * w1;
+    int panel = p.panel_rank + 1 + i;
+    if (panel >= p.panel_world) panel -= p.panel_world;
+    mb = panel * own + j;
+  }
+}
+// spin until the rows of an m-block have arrived (acquire at system scope: the writers are other GPUs).  A peer that
+// never delivers would hang the GPU: give up with a trap after ~4 s.
+__device__ __forceinline__ void wait_rows_ready(const uint32_t* counter, uint32_t target) {
+  long long t0 = 0;
+  for (uint32_t spins = 0;; ++spins) {
+    uint32_t v;
+    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(counter) : "memory");
+    if (int32_t(v - target) >= 0) return;
+    if (spins == 0) t0 = clock64();
+    else if ((spins & 255u) == 0 && clock64() - t0 > 8000000000LL) __trap();
+    __nanosleep(100);
+  }
+}
+
 // kDiag (diagnostics only, results are NOT the op's): 1 = skip the promotion arithmetic, 2 = accumulate all of K in
 // TMEM like an unscaled GEMM (one accumulator hand-off per tile) — both measure ceilings of the TMA/MMA pipeline.
 // kSplitN: each K block is issued as two N/2-wide MMA halves with their own full/empty barriers, so a half can be
@@ -149,7 +200,7 @@ __device__ __forceinline__ void tile_coords(int tile, const GemmParams& p, int& 
 // 1x128 group, bit-identical to GEMM -> sgl_per_token_group_quant_8bit); 2 = the same after silu(gate)*up, the tile's
 // first 128 columns being a gate block and its last 128 the matching up block (weights interleaved by 128-row blocks).
 template <int BLOCK_N, int kStages, int kCG, typename OutT, bool kTmaStore, int kDiag = 0, bool kSplitN = false,
-          bool kGrouped = false, int kEpi = 0, bool kMcB = false, int kPipe = 0>
+          bool kGrouped = false, int kEpi = 0, bool kMcB = false, int kPipe = 0, bool kWaitA = false>
 __global__ void __launch_bounds__(kNumThreads, 1)
 fp8_blockwise_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
                           const __grid_constant__ CMaps tmap_c, const GemmParams p) {
@@ -159,6 +210,7 @@ fp8_blockwise_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gr
   // but every accumulator hand-off (tcgen05.commit -> promotion warps -> issuer) stays inside one CTA.
   constexpr int kCl = kMcB ? 2 : kCG;                  // CTAs per cluster = per 256-row (kCl == 2) tile slot
   static_assert(!kMcB || (kCG == 1 && !kSplitN && !kGrouped && kDiag == 0), "multicast-B mode: cta_group::1 MMAs");
+  static_assert(!kWaitA || (kCG == 2 && !kGrouped && kDiag == 0 && kEpi == 0 && !kMcB), "gated mode: the paired prefill tiles");
   constexpr int NC = C::NC;
   constexpr int kAccStages = C::kAccStages;
   constexpr int kHalves = kSplitN ? 2 : 1;             // accumulator hand-off granularity: whole stage or column half
@@ -256,7 +308,15 @@ fp8_blockwise_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gr
           n0 = ti.z * int(p.N) + nb * BLOCK_N;                  // B is the experts' [N, K] matrices stacked
           mb = 0; (void)mb;
         } else {
-          tile_coords(tile, p, mb, nb);
+          if constexpr (kWaitA) {
+            tile_coords_panels(tile, p, mb, nb);
+            // the codes of this m-block were written by another GPU's generic-proxy stores; the loads below are async-proxy reads
+            if (lane == 0) wait_rows_ready(p.a_ready + mb, p.a_ready_target);
+            __syncwarp();
+            asm volatile("fence.proxy.async;" ::: "memory");
+          } else {
+            tile_coords(tile, p, mb, nb);
+          }
           m0 = mb * (BLOCK_M * kCl) + int(cta_rank) * BLOCK_M;
           n0 = nb * BLOCK_N + int(cta_rank) * (kMcB ? BLOCK_N / 2 : C::LOAD_N);
         }
@@ -425,7 +485,14 @@ fp8_blockwise_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gr
         sb_base += int64_t(ti.z) * p.grp_sb_expert_stride;
         mb = 0;
       } else {
-        tile_coords(tile, p, mb, nb);
+        if constexpr (kWaitA) {
+          tile_coords_panels(tile, p, mb, nb);
+          // this warp reads the m-block's activation scales itself (ahead of the tile's first accumulator hand-off)
+          if (lane == 0) wait_rows_ready(p.a_ready + mb, p.a_ready_target);
+          __syncwarp();
+        } else {
+          tile_coords(tile, p, mb, nb);
+        }
         m0 = mb * (BLOCK_M * kCl) + int(cta_rank) * BLOCK_M;
         row_ok = m0 + quarter * 32 + lane < p.M;
       }
@@ -443,7 +510,12 @@ fp8_blockwise_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gr
       // of the iteration that uses it, so no instruction ever waits on an in-flight global load
       // (an in-order warp that multiplies right after the load stalls ~1 us per K block — measured).
       const int64_t sa_sk = p.sa_sk, sb_sk = p.sb_sk;
-      auto ld_sa = [&](int kb) { return (row_ok && kb < kb1) ? __ldg(sa_ptr + int64_t(kb) * sa_sk) : 0.0f; };
+      // (gated mode: the scales were written by other GPUs during this launch — read them at L2, never through the
+      // non-coherent path)
+      auto ld_sa = [&](int kb) {
+        return (row_ok && kb < kb1) ? (kWaitA ? __ldcg(sa_ptr + int64_t(kb) * sa_sk) : __ldg(sa_ptr + int64_t(kb) * sa_sk)) : 0.0f;
+      };
+      auto ld_sa4 = [&](const float4* ptr) { return kWaitA ? __ldcg(ptr) : __ldg(ptr); };
       auto ld_sb = [&](int kb) { return kb < kb1 ? __ldg(sb_ptr + int64_t(kb) * sb_sk) : 0.0f; };
       float sa0 = ld_sa(kb0), sb0 = ld_sb(kb0), sa1 = ld_sa(kb0 + 1), sb1 = ld_sb(kb0 + 1);
       constexpr int NCH = NC / 32;           // 32-column TMEM chunks per K block for this warp
@@ -559,7 +631,7 @@ fp8_blockwise_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gr
             ready = ptx::mbar_try_wait(tfull_bar(acc * kHalves + hb), acc_phase);
           }
           if (fetch) {
-            a_nx = __ldg(sa4n);
+            a_nx = ld_sa4(sa4n);
             b_nx = __ldg(sb4n);
           }
           fma_chunk(2, v[0], s);
@@ -584,7 +656,7 @@ fp8_blockwise_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gr
             ready = ptx::mbar_try_wait(tfull_bar(acc * kHalves + hb), acc_phase);
           }
           if (fetch) {
-            a_nx = __ldg(sa4n);
+            a_nx = ld_sa4(sa4n);
             b_nx = __ldg(sb4n);
           }
           fma_chunk(0, v[0], s);
@@ -621,7 +693,7 @@ fp8_blockwise_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gr
               // the next group's scales are requested here, in the shadow of the hand-off wait, not at the group's
               // loop top where the issue sits between this warp's first tcgen05.ld and its FMAs
               if (fetch) {
-                a_nx = __ldg(sa4n);
+                a_nx = ld_sa4(sa4n);
                 b_nx = __ldg(sb4n);
               }
               if (kDiag != 6 && !(kDiag == 8 && (warp & 3) == 1))
@@ -664,7 +736,7 @@ fp8_blockwise_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gr
           // every group boundary under this register pressure (S2R + LDCU + 64-bit IMAD chain, ~200 clk measured)
           sa4n = sa4 + g;
           sb4n = sb4 + g;
-          a_nx = __ldg(sa4n);
+          a_nx = ld_sa4(sa4n);
           b_nx = __ldg(sb4n);
           ptx::mbar_wait(tfull_bar(acc * kHalves + hb), acc_phase);
           ptx::tc_fence_after();
@@ -1072,11 +1144,11 @@ constexpr int kFirstStampVariant = 15, kLastStampVariant = 22;
 constexpr int kNumVariants = int(sizeof(kVariants) / sizeof(kVariants[0]));
 
 template <int BLOCK_N, int kStages, int kCG, typename OutT, bool kTmaStore, int kDiag = 0, bool kSplitN = false,
-          bool kGrouped = false, int kEpi = 0, bool kMcB = false, int kPipe = 0>
+          bool kGrouped = false, int kEpi = 0, bool kMcB = false, int kPipe = 0, bool kWaitA = false>
 static int launch_variant(const CUtensorMap& ta, const CUtensorMap& tb, const CMaps& tc, const GemmParams& p,
                           int workers, cudaStream_t st) {
   using C = Cfg<BLOCK_N, kCG>;
-  auto kern = fp8_blockwise_gemm_kernel<BLOCK_N, kStages, kCG, OutT, kTmaStore, kDiag, kSplitN, kGrouped, kEpi, kMcB, kPipe>;
+  auto kern = fp8_blockwise_gemm_kernel<BLOCK_N, kStages, kCG, OutT, kTmaStore, kDiag, kSplitN, kGrouped, kEpi, kMcB, kPipe, kWaitA>;
   constexpr int smem = kMaxDynSmem;
   (void)sizeof(C);
   static std::atomic<uint64_t> configured{0};   // per instantiation, one bit per device ordinal
@@ -1258,11 +1330,18 @@ struct QuantOut {
   int silu_mul;
 };
 
+// Gated request (sglk_fp8_blockwise_scaled_mm_gated): one arrival counter per 256 rows of A, see GemmParams::a_ready.
+struct GateIn {
+  const uint32_t* counters;
+  uint32_t target;
+  int rank, world;
+};
+
 static int gemm_entry(const void* A, const void* B, const float* sa, const float* sb, void* Cout, int64_t M,
                       int64_t N, int64_t K, int64_t lda, int64_t ldb, int64_t ldc, int64_t sa_sm, int64_t sa_sk,
                       int64_t sb_sk, int64_t sb_sn, int out_dtype, int variant, int num_sms, int flags, void* workspace,
                       int64_t workspace_bytes, void* stream, void* const* extra_dests = nullptr, int num_extra = 0,
-                      void* mc_ptr = nullptr, const QuantOut* qo = nullptr) {
+                      void* mc_ptr = nullptr, const QuantOut* qo = nullptr, const GateIn* gate = nullptr) {
   if (M < 0 || N < 0 || K < 0) return SGLK_E_SHAPE;
   if (out_dtype != SGLK_BF16 && out_dtype != SGLK_F16) return SGLK_E_DTYPE;
   if (M == 0 || N == 0) return SGLK_OK;
@@ -1286,7 +1365,14 @@ static int gemm_entry(const void* A, const void* B, const float* sa, const float
   if (K % 16 != 0 || lda % 16 != 0 || ldb % 16 != 0 || lda < K || ldb < K || ldc < N) return SGLK_E_STRIDE;
   if ((reinterpret_cast<uintptr_t>(A) & 15) || (reinterpret_cast<uintptr_t>(B) & 15)) return SGLK_E_STRIDE;
   if (M >= (int64_t(1) << 31) || N >= (int64_t(1) << 31) || K >= (int64_t(1) << 31)) return SGLK_E_SHAPE;
-  const bool plain_output = !qo && num_extra == 0 && !mc_ptr;
+  const bool plain_output = !qo && num_extra == 0 && !mc_ptr && !gate;
+  if (gate) {
+    // the paired 256-row tiles, one counter per m-block, equal whole panels per rank, whole tiles (no stream-K)
+    if (!gate->counters || gate->world < 1 || gate->rank < 0 || gate->rank >= gate->world) return SGLK_E_ARG;
+    if (M % (int64_t(2 * BLOCK_M) * gate->world) != 0 || N < 256 || qo || num_extra != 0 || mc_ptr) return SGLK_E_SHAPE;
+    variant = 29;
+    flags = (flags & ~3) | SGLK_GEMM_STREAMK_NEVER;
+  }
   if (variant < 0) variant = pick_variant(M, N, K, plain_output, num_sms);
   if (!variant_available(variant)) return SGLK_E_VARIANT;
   if (variant == kRowsVariant) {
@@ -1303,6 +1389,7 @@ static int gemm_entry(const void* A, const void* B, const float* sa, const float
   for (int d = 0; d < num_extra; ++d)
     if (!extra_dests[d] || !tma_store_ok(extra_dests[d], ldc, 2)) return SGLK_E_STRIDE;
   if (!qo && v.tma_store && !tma_store_ok(Cout, ldc, 2)) {
+    if (gate) return SGLK_E_STRIDE;
     // same tile shape, predicated-store epilogue
     variant = (v.cg == 2) ? 4 : 1;
     v = kVariants[variant];
@@ -1311,6 +1398,7 @@ static int gemm_entry(const void* A, const void* B, const float* sa, const float
 
   GemmParams p;
   p.grp_tiles = nullptr; p.grp_num_m_tiles = nullptr; p.grp_sb_expert_stride = 0;
+  p.a_ready = nullptr; p.a_ready_target = 0; p.panel_own = p.panel_rank = 0; p.panel_world = 1; p.panel_group = 1;
   p.sa = sa; p.sb = sb; p.C = Cout;
   p.M = M; p.N = N; p.K = K; p.ldc = ldc;
   p.sa_sm = sa_sm; p.sa_sk = sa_sk; p.sb_sk = sb_sk; p.sb_sn = sb_sn;
@@ -1342,6 +1430,7 @@ static int gemm_entry(const void* A, const void* B, const float* sa, const float
     const bool vec_layout = sa_sk == 1 && sb_sk == 1 && sa_sm % 4 == 0 && sb_sn % 4 == 0 &&
                             (reinterpret_cast<uintptr_t>(sa) & 15) == 0 && (reinterpret_cast<uintptr_t>(sb) & 15) == 0;
     const int64_t base = pl.stream_k ? pl.counter_bytes + pl.partial_bytes : kCounterAreaBytes;
+    if (gate && !vec_layout) return SGLK_E_STRIDE;   // the scales arrive during the launch: they cannot be re-laid-out first
     if (!vec_layout && pl.scale_bytes > 0 && workspace && workspace_bytes >= base + pl.scale_bytes &&
         (reinterpret_cast<uintptr_t>(workspace) & 15) == 0 && (variant < kFirstStampVariant || variant > kLastStampVariant)) {
       const int G = pl.num_k_blocks, NB = p.num_sb_cols;
@@ -1415,6 +1504,20 @@ static int gemm_entry(const void* A, const void* B, const float* sa, const float
   } else {
     if (num_extra > 0) return SGLK_E_STRIDE;   // multi-destination output needs the TMA-store epilogue
     for (int d = 0; d < kMaxDests; ++d) tc.m[d] = ta;   // unused by the kernel
+  }
+  if (gate) {
+    if (!p.scale_vec) return SGLK_E_STRIDE;
+    p.a_ready = gate->counters;
+    p.a_ready_target = gate->target;
+    p.panel_world = gate->world;
+    p.panel_rank = gate->rank;
+    p.panel_own = p.num_m_blocks / gate->world;
+    if (p.group_m > p.panel_own) p.group_m = p.panel_own;
+    const int w1 = gate->world - 1;
+    p.panel_group = w1 > 0 ? w1 * (8 / w1 > 0 ? 8 / w1 : 1) : 1;
+    if (out_dtype == SGLK_BF16)
+      return launch_variant<256, 5, 2, __nv_bfloat16, true, 0, true, false, 0, false, 3, true>(ta, tb, tc, p, pl.workers, st);
+    return launch_variant<256, 5, 2, __half, true, 0, true, false, 0, false, 3, true>(ta, tb, tc, p, pl.workers, st);
   }
   if (out_dtype == SGLK_BF16) return launch_by_id<__nv_bfloat16>(variant, ta, tb, tc, p, pl.workers, st);
   return launch_by_id<__half>(variant, ta, tb, tc, p, pl.workers, st);
@@ -1526,6 +1629,17 @@ extern "C" int sglk_fp8_blockwise_scaled_mm_quant(const void* A, const void* B, 
   sglk::QuantOut qo{out_q, ldq, out_s, os_stride_m, os_stride_g, eps, silu_mul ? 1 : 0};
   return sglk::gemm_entry(A, B, sa, sb, nullptr, M, N, K, lda, ldb, N, sa_stride_m, sa_stride_k, sb_stride_k, sb_stride_n,
                           round_dtype, -1, num_sms, flags, workspace, workspace_bytes, stream, nullptr, 0, nullptr, &qo);
+}
+
+extern "C" int sglk_fp8_blockwise_scaled_mm_gated(const void* A, const void* B, const float* sa, const float* sb, void* C,
+                                                  int64_t M, int64_t N, int64_t K, int64_t lda, int64_t ldb, int64_t ldc,
+                                                  int64_t sa_stride_m, int64_t sa_stride_k, int64_t sb_stride_k,
+                                                  int64_t sb_stride_n, int out_dtype, int num_sms,
+                                                  const uint32_t* row_ready_counters, uint32_t ready_target,
+                                                  int panel_rank, int panel_world, void* stream) {
+  const sglk::GateIn gate{row_ready_counters, ready_target, panel_rank, panel_world};
+  return sglk::gemm_entry(A, B, sa, sb, C, M, N, K, lda, ldb, ldc, sa_stride_m, sa_stride_k, sb_stride_k, sb_stride_n,
+                          out_dtype, 29, num_sms, 0, nullptr, 0, stream, nullptr, 0, nullptr, nullptr, &gate);
 }
 
 extern "C" int64_t sglk_gemm_workspace_bytes(int64_t M, int64_t N, int64_t K, int variant, int num_sms, int flags) {

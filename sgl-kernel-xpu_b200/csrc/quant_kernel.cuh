@@ -168,7 +168,19 @@ struct QuantCfg {
 // One chunk of 256*U slots.  kFull (CTA-uniform, chosen by the caller): every slot of the chunk exists, so the
 // per-slot bounds predicates compile away — the kernel is sensitive to issue pressure (tools/quant_exp.py: the trimmed
 // variant 13 gains ~3 % over the predicated body, an inexact multiply-only variant ~2 % more).
-template <typename T, int GROUP, bool kInt8, int kLayout, bool kFuse, bool kV2, bool kFull>
+// NVLS multicast stores (kSt == 1 instantiations of ptgq_chunk: the broadcast form of quant_bcast.cu): one store lands
+// in the same place of every GPU's copy of a symmetric buffer, replicated by the NVSwitch
+__device__ __forceinline__ void mc_store_f32(float* p, float v) {
+  asm volatile("multimem.st.relaxed.sys.global.f32 [%0], %1;" ::"l"(p), "f"(v) : "memory");
+}
+__device__ __forceinline__ void mc_store_v4(void* p, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
+  asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};"
+               ::"l"(p), "f"(__uint_as_float(a)), "f"(__uint_as_float(b)), "f"(__uint_as_float(c)), "f"(__uint_as_float(d))
+               : "memory");
+}
+
+// kSt: 0 = plain stores; 1 = multimem.st to an NVLS multicast address (row-major fp32 scales, 16-byte code vectors)
+template <typename T, int GROUP, bool kInt8, int kLayout, bool kFuse, bool kV2, bool kFull, int kSt = 0>
 __device__ __forceinline__ void ptgq_chunk(const T* __restrict__ x, uint8_t* __restrict__ q, void* __restrict__ s_out,
                                            const QuantParams& p, const int64_t chunk0, const int64_t total_slots,
                                            const int tid) {
@@ -254,7 +266,8 @@ __device__ __forceinline__ void ptgq_chunk(const T* __restrict__ x, uint8_t* __r
       }
       if (valid && l == 0) {
         if constexpr (kLayout == SGLK_SCALE_F32_ROW_MAJOR) {
-          reinterpret_cast<float*>(s_out)[gid] = scale;
+          if constexpr (kSt == 1) mc_store_f32(reinterpret_cast<float*>(s_out) + gid, scale);
+          else reinterpret_cast<float*>(s_out)[gid] = scale;
         } else if constexpr (kLayout == SGLK_SCALE_UE8M0_ROW_MAJOR) {
           reinterpret_cast<uint8_t*>(s_out)[gid] = uint8_t(exp2s + 127);
         } else {
@@ -323,7 +336,10 @@ __device__ __forceinline__ void ptgq_chunk(const T* __restrict__ x, uint8_t* __r
         }
         if (valid) {
           uint8_t* dst = q + gid * GROUP + (j * LPG + l) * EPV;
-          if constexpr (EPV == 16) *reinterpret_cast<uint4*>(dst) = make_uint4(packed[0], packed[1], packed[2], packed[3]);
+          if constexpr (kSt == 1) {
+            static_assert(kSt != 1 || (EPV == 16 && kLayout == SGLK_SCALE_F32_ROW_MAJOR && !kFuse && !kV2), "broadcast form");
+            mc_store_v4(dst, packed[0], packed[1], packed[2], packed[3]);
+          } else if constexpr (EPV == 16) *reinterpret_cast<uint4*>(dst) = make_uint4(packed[0], packed[1], packed[2], packed[3]);
           else *reinterpret_cast<uint2*>(dst) = make_uint2(packed[0], packed[1]);
         }
       }

@@ -356,6 +356,55 @@ def _gemm_allgather(mat_a, mat_b, scales_a, scales_b, out_full, col_lo: int, pee
     return out_full
 
 
+ROWS_PER_COUNTER = 256     # one arrival counter per 256-row m-block of the paired prefill tiles
+
+
+def counter_increments(hidden: int) -> int:
+    """How much one call of `_quant_bcast` adds to the counter of every 256-row block it covers."""
+    return ROWS_PER_COUNTER * hidden // 16384
+
+
+def _quant_bcast(x, q_ptr: int, s_ptr: int, counters_ptr: int, multicast: bool, eps: float = 1e-10):
+    """Row-sharded group quantisation (include/sglk_fp8.h: sglk_per_token_group_quant_fp8_bcast): quantise `x`
+    ([rows, hidden] bf16/f16, this rank's rows) to e4m3 codes + row-major fp32 scales written at the raw addresses
+    `q_ptr` / `s_ptr` (NVLS multicast addresses when `multicast`), and bump the arrival counters at `counters_ptr`."""
+    _check(x.is_cuda and x.dim() == 2 and x.is_contiguous(), "x must be a contiguous [rows, hidden] CUDA tensor")
+    _check(x.dtype in (torch.bfloat16, torch.float16), "x must be bf16 or f16")
+    rows, hidden = x.shape
+    if rows == 0:
+        return
+    lib = _lib.load()
+    with torch.cuda.device(x.device):
+        rc = lib.sglk_per_token_group_quant_fp8_bcast(
+            x.data_ptr(), int(q_ptr), int(s_ptr), int(counters_ptr), rows, hidden, ROWS_PER_COUNTER,
+            _lib.BF16 if x.dtype == torch.bfloat16 else _lib.F16, float(eps), 1 if multicast else 0, _stream_ptr(x))
+    _lib.check(rc, "per_token_group_quant_fp8 (row-sharded broadcast)")
+
+
+def _gemm_gated(mat_a, mat_b, scales_a, scales_b, out_dtype, counters, target: int, panel_rank: int, panel_world: int,
+                num_sms: int = 0):
+    """fp8_blockwise_scaled_mm whose activation rows arrive during the launch (include/sglk_fp8.h:
+    sglk_fp8_blockwise_scaled_mm_gated).  `counters`: uint32/int32 tensor, one entry per 256 rows of mat_a."""
+    _check(mat_a.is_cuda and mat_b.is_cuda and scales_a.is_cuda and scales_b.is_cuda and counters.is_cuda,
+           "fp8_blockwise_scaled_mm: tensors must be CUDA tensors")
+    M, N, K = _gemm_checks(mat_a, mat_b, scales_a, scales_b, out_dtype)
+    _check(counters.element_size() == 4 and counters.numel() >= -(M // -ROWS_PER_COUNTER), "one 32-bit counter per 256 rows")
+    out = torch.empty((M, N), dtype=out_dtype, device=mat_a.device)
+    if M == 0 or N == 0:
+        return out
+    lda = mat_a.stride(0) if M > 1 else max(K, 16)
+    ldb = mat_b.stride(1) if N > 1 else max(K, 16)
+    lib = _lib.load()
+    with torch.cuda.device(mat_a.device):
+        rc = lib.sglk_fp8_blockwise_scaled_mm_gated(
+            mat_a.data_ptr(), mat_b.data_ptr(), scales_a.data_ptr(), scales_b.data_ptr(), out.data_ptr(), M, N, K, lda, ldb,
+            out.stride(0), scales_a.stride(0), scales_a.stride(1), scales_b.stride(0), scales_b.stride(1),
+            _GEMM_OUT[out_dtype], num_sms, counters.data_ptr(), int(target) & 0xFFFFFFFF, int(panel_rank), int(panel_world),
+            _stream_ptr(mat_a))
+    _lib.check(rc, "fp8_blockwise_scaled_mm (gated)")
+    return out
+
+
 def _gemm_quant(mat_a, mat_b, scales_a, scales_b, round_dtype, eps, fuse_silu_and_mul, column_major_scales):
     """fp8_blockwise_scaled_mm followed by sgl_per_token_group_quant_8bit (group 128, e4m3; optionally silu(gate)*up in
     between, gate/up interleaved by 128-column blocks) as ONE kernel: the bf16 intermediate never reaches HBM.

@@ -100,6 +100,62 @@ class ColumnShardedFp8Linear:
         self._hdl.barrier(channel=1)
         return out
 
+    # ---- row-sharded activation quantisation, broadcast over NVLink while the GEMM runs ------------------------
+    def sharded_quant_supported(self, tokens: int) -> bool:
+        """whole 256-row blocks per rank (one arrival counter per block of the paired GEMM tiles)"""
+        return self.world >= 1 and tokens > 0 and tokens % (256 * self.world) == 0 and self.local.out_features >= 256
+
+    def enable_sharded_quant(self, max_tokens: int) -> bool:
+        """Allocate the symmetric activation buffers (two sets: codes [M, K] e4m3, scales [M, K/128] fp32, one arrival
+        counter per 256 rows) and exchange the mappings (collective).  Returns False when the NVLS multicast mapping
+        is not available (the replicated path stays in use)."""
+        import torch.distributed._symmetric_memory as symm_mem
+
+        dev = self.local.weight_q.device
+        k = self.local.in_features
+        assert k % 128 == 0 and max_tokens % 256 == 0
+        al = lambda v: -(-v // 256) * 256
+        self._sq_codes, self._sq_scales, self._sq_cnt = al(max_tokens * k), al(max_tokens * (k // 128) * 4), al((max_tokens // 256) * 4)
+        per_set = self._sq_codes + self._sq_scales + self._sq_cnt
+        self._sq_buf = symm_mem.empty((2 * per_set,), dtype=torch.uint8, device=dev)
+        self._sq_buf.zero_()
+        self._sq_hdl = symm_mem.rendezvous(self._sq_buf, self.group if self.group is not None else dist.group.WORLD)
+        self._sq_per_set, self._sq_tokens, self._sq_step = per_set, max_tokens, 0
+        self._sq_hdl.barrier(channel=0)                      # everybody's counters are zero before anybody adds to them
+        mc = getattr(self._sq_hdl, "multicast_ptr", 0)
+        self._sq_mc = int(mc) if mc else 0
+        return self._sq_mc != 0
+
+    def forward_sharded_quant(self, x: torch.Tensor) -> torch.Tensor:
+        """This rank's [M, N/g] panel from REPLICATED bf16 activations `x` [M, K] — like forward_local, but rank r
+        quantises only rows [r, r+1) * M/g: the quant kernel writes codes and scales into every rank's buffer with
+        multimem.st and bumps per-256-row arrival counters, and the GEMM starts on its own rows at once and on the
+        others' as they arrive.  Two buffer sets alternate, so no cross-GPU barrier is needed: a rank can only start
+        step t+2 (which overwrites set t % 2) after its GEMM of step t+1, which needed every rank's step-t+1 rows, which
+        every rank sends after its own step-t GEMM.  Collective: every rank calls it with the same batch, in the same
+        order.  Bit-identical to forward_local (quantisation is row-local)."""
+        from . import _ops
+
+        m, k = x.shape
+        # (one batch size per enable_sharded_quant: every block's counter then advances by the same amount per call)
+        assert self.sharded_quant_supported(m) and m == self._sq_tokens and self._sq_mc
+        b = self._sq_step & 1
+        calls = self._sq_step // 2 + 1                       # calls on this buffer set, this one included
+        base = b * self._sq_per_set
+        off_s, off_c = base + self._sq_codes, base + self._sq_codes + self._sq_scales
+        rows = m // self.world
+        lo = self.rank * rows
+        g = k // 128
+        _ops._quant_bcast(x[lo:lo + rows], self._sq_mc + base + lo * k, self._sq_mc + off_s + lo * g * 4,
+                          self._sq_mc + off_c + (lo // 256) * 4, multicast=True)
+        xq = self._sq_buf[base:base + m * k].view(torch.float8_e4m3fn).view(m, k)
+        xs = self._sq_buf[off_s:off_s + m * g * 4].view(torch.float32).view(m, g)
+        cnt = self._sq_buf[off_c:off_c + (m // 256) * 4].view(torch.int32)
+        out = _ops._gemm_gated(xq, self.local.weight_q.t(), xs, self.local.weight_scale.t(), self.local.out_dtype, cnt,
+                               calls * _ops.counter_increments(k), self.rank, self.world)
+        self._sq_step += 1
+        return out
+
     def forward(self, x: torch.Tensor, gather_output: bool = True) -> torch.Tensor:
         y = self.forward_local(x)
         return self.gather(y) if gather_output else y
