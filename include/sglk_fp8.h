@@ -261,8 +261,10 @@ SGLK_API int sglk_per_token_group_quant_fp8_bcast(const void* input, void* outpu
  * counter per 256 rows (row_ready_counters[m / 256], as written by sglk_per_token_group_quant_fp8_bcast with
  * rows_per_counter = 256); the 256-row tiles of a block are started once int32(counter - ready_target) >= 0, i.e. the
  * caller passes (calls so far on this buffer + 1) * 256 * K / 16384.  The blocks are walked in arrival order: the
- * panel of rank panel_rank first (rows [rank, rank + 1) * M / world), then the j-th block of every other panel, nearest
- * rank first, for j = 0, 1, ...  Same result bits as sglk_fp8_blockwise_scaled_mm on the completed buffers.
+ * panel of rank panel_rank first (rows [rank, rank + 1) * M / world), then either (whole_panels == 0: every rank
+ * broadcasts at once) the j-th block of every other panel, nearest rank first, for j = 0, 1, ..., or (whole_panels != 0:
+ * ring schedule, one sender per receiver at a time) the panels of ranks rank+1, rank+2, ... one after the other.
+ * Same result bits as sglk_fp8_blockwise_scaled_mm on the completed buffers.
  * Requirements: M % (256 * panel_world) == 0, N >= 256, K-block-contiguous scales (sa_stride_k == sb_stride_k == 1,
  * 16-byte aligned rows), C 16-byte aligned rows.  A counter that never arrives traps the kernel after ~4 s.
  */
@@ -271,7 +273,7 @@ SGLK_API int sglk_fp8_blockwise_scaled_mm_gated(const void* A, const void* B, co
                                        int64_t sa_stride_m, int64_t sa_stride_k, int64_t sb_stride_k,
                                        int64_t sb_stride_n, int out_dtype, int num_sms,
                                        const uint32_t* row_ready_counters, uint32_t ready_target, int panel_rank,
-                                       int panel_world, void* stream);
+                                       int panel_world, int whole_panels, void* stream);
 
 /*
  * Replaces: void fp8_blockwise_scaled_grouped_mm(output, a_ptrs, ..., problem_sizes, expert_offsets, workspace)

@@ -80,6 +80,7 @@ struct GemmParams {
   int32_t panel_own;              // m-blocks per rank panel
   int32_t panel_rank, panel_world;
   int32_t panel_group;            // remote m-blocks per rasterisation group (a whole number of slices)
+  int32_t panel_whole;            // 1: the other panels arrive one after the other (nearest rank first) instead of slice by slice
 };
 
 constexpr int kMaxDests = 8;
@@ -153,45 +154,26 @@ __device__ __forceinline__ void tile_coords(int tile, const GemmParams& p, int& 
 
 // gated mode: tile index -> (physical m-block, n-block) in arrival order (see GemmParams::a_ready)
 __device__ __forceinline__ void tile_coords_panels(int tile, const GemmParams& p, int& mb, int& nb) {
+  // straight-line on purpose (selects, no branches): with branches here ptxas kept the producer's loop state out of the
+  // uniform registers
   const int own = p.panel_own, nn = p.num_n_blocks;
-  int L;                                                        // position in the walk order
-  if (tile < own * nn) {                                        // own panel: groups of group_m m-blocks, n-major
-    const int per_group = p.group_m * nn;
-    const int g = tile / per_group, first = g * p.group_m;
-    const int rows = min(p.group_m, own - first), in_g = tile - g * per_group;
-    L = first + in_g % rows;
-    nb = in_g / rows;
-  } else {                                                      // the other panels: groups of whole slices
-    const int t = tile - own * nn, per_group = p.panel_group * nn;
-    const int g = t / per_group, first = g * p.panel_group;
-    const int rows = min(p.panel_group, (p.num_m_blocks - own) - first), in_g = t - g * per_group;
-    L = own + first + in_g % rows;
-    nb = in_g / rows;
-  }
-  if (L < own) {
-    mb = p.panel_rank * own + L;
-  } else {
-    const int r = L - own, w1 = p.panel_world - 1;
-    const int j = r / w1, i = r - j * w1;
-    int panel = p.panel_rank + 1 + i;
-    if (panel >= p.panel_world) panel -= p.panel_world;
-    mb = panel * own + j;
-  }
+  const bool is_own = tile < own * nn;
+  const int t = is_own ? tile : tile - own * nn;                  // own panel: groups of group_m m-blocks, n-major;
+  const int gsz = is_own ? p.group_m : p.panel_group;             // the other panels: groups of panel_group
+  const int span = is_own ? own : p.num_m_blocks - own;
+  const int per_group = gsz * nn;
+  const int g = t / per_group, first = g * gsz;
+  const int rows = min(gsz, span - first), in_g = t - g * per_group;
+  nb = in_g / rows;
+  const int r = first + (in_g - nb * rows);                       // position inside the own / the remote part of the walk
+  // remote part: whole panels one after the other (i = peer index, j = block in panel), or slice by slice
+  const int d = p.panel_whole ? own : max(p.panel_world - 1, 1);
+  const int q = r / d, m = r - q * d;
+  const int i = p.panel_whole ? q : m, j = p.panel_whole ? m : q;
+  int panel = p.panel_rank + 1 + i;
+  panel -= panel >= p.panel_world ? p.panel_world : 0;
+  mb = is_own ? p.panel_rank * own + r : panel * own + j;
 }
-// spin until the rows of an m-block have arrived (acquire at system scope: the writers are other GPUs).  A peer that
-// never delivers would hang the GPU: give up with a trap after ~4 s.
-__device__ __forceinline__ void wait_rows_ready(const uint32_t* counter, uint32_t target) {
-  long long t0 = 0;
-  for (uint32_t spins = 0;; ++spins) {
-    uint32_t v;
-    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(counter) : "memory");
-    if (int32_t(v - target) >= 0) return;
-    if (spins == 0) t0 = clock64();
-    else if ((spins & 255u) == 0 && clock64() - t0 > 8000000000LL) __trap();
-    __nanosleep(100);
-  }
-}
-
 // kDiag (diagnostics only, results are NOT the op's): 1 = skip the promotion arithmetic, 2 = accumulate all of K in
 // TMEM like an unscaled GEMM (one accumulator hand-off per tile) — both measure ceilings of the TMA/MMA pipeline.
 // kSplitN: each K block is issued as two N/2-wide MMA halves with their own full/empty barriers, so a half can be
@@ -242,6 +224,7 @@ fp8_blockwise_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gr
   const uint32_t tmem_slot = bar_base + 8u * (2 * kMaxStages + 2 * kAccBars);
   // scale staging for the promotion warps (filled with cp.async so no long-latency LDG sits in their
   // in-order instruction stream): 2 x fp32 per warp for sb at bar_base + 512, 2 x fp32 per thread for sa after the KB of barriers
+  const uint32_t ready_word = bar_base + 400u;   // gated mode: the producer's mask of arrived m-blocks, published for the promotion warps
   const uint32_t sb_slots = bar_base + 512u;
   const uint32_t sa_slots = bar_base + 1024u;
   uint8_t* smem_gen = smem_raw + (smem_base - ptx::smem_u32(smem_raw));   // generic pointer to smem_base
@@ -266,6 +249,7 @@ fp8_blockwise_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gr
       ptx::mbar_init(tfull_bar(s), 1);                             // one tcgen05.commit
       ptx::mbar_init(tempty_bar(s), kCG * kNumEpiWarps / kHalves); // one arrive per epilogue warp (of that half) of every CTA
     }
+    if constexpr (kWaitA) asm volatile("st.shared.u64 [%0], %1;" ::"r"(ready_word), "l"(0ull) : "memory");
     ptx::fence_mbar_init();
   }
   if (warp == 2) {
@@ -310,10 +294,38 @@ fp8_blockwise_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gr
         } else {
           if constexpr (kWaitA) {
             tile_coords_panels(tile, p, mb, nb);
-            // the codes of this m-block were written by another GPU's generic-proxy stores; the loads below are async-proxy reads
-            if (lane == 0) wait_rows_ready(p.a_ready + mb, p.a_ready_target);
-            __syncwarp();
-            asm volatile("fence.proxy.async;" ::: "memory");
+            // Wait until this tile's m-block has arrived.  Fast path: one LDS + warp vote on the mask of arrived blocks;
+            // refresh: ONE warp-wide round of system-scope acquire loads over all (<= 64) counters — such a load costs
+            // ~1-2 us, so it must not run per tile once everything is there — then the proxy fence (the rows were written
+            // by another GPU's generic-proxy stores, the loads below are async-proxy reads) and the mask is published for
+            // the promotion warps.  Everything here is warp-CONVERGENT (all lanes, vote-controlled loops) and lives in the
+            // producer: a lane-0 spin, a non-inlined helper, or a fourth warp role with its own tile loop each made
+            // ptxas drop the uniform-register form of the MMA issuer's loop (7 R2UR per K block half: +12 % kernel time).
+            if (p.num_m_blocks <= 64) {
+              unsigned long long seen;
+              asm volatile("ld.shared.u64 %0, [%1];" : "=l"(seen) : "r"(ready_word) : "memory");
+              for (uint32_t spins = 0; !__all_sync(0xFFFFFFFFu, int((seen >> mb) & 1ull)); ++spins) {
+                uint32_t v0 = p.a_ready_target - 1u, v1 = p.a_ready_target - 1u;
+                if (lane < p.num_m_blocks)
+                  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v0) : "l"(p.a_ready + lane) : "memory");
+                if (lane + 32 < p.num_m_blocks)
+                  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v1) : "l"(p.a_ready + lane + 32) : "memory");
+                const uint32_t w0 = __ballot_sync(0xFFFFFFFFu, int32_t(v0 - p.a_ready_target) >= 0);
+                const uint32_t w1 = __ballot_sync(0xFFFFFFFFu, int32_t(v1 - p.a_ready_target) >= 0);
+                seen = uint64_t(w0) | (uint64_t(w1) << 32);
+                asm volatile("fence.proxy.async;" ::: "memory");
+                if (ptx::elect_one()) asm volatile("st.release.cta.shared.u64 [%0], %1;" ::"r"(ready_word), "l"(seen) : "memory");
+                if (spins > 4000000u) __trap();            // a peer that never delivers: give up after a few seconds
+              }
+            } else {                                       // more than 64 m-blocks: this tile's own counter, every tile
+              const uint32_t* cp = p.a_ready + mb;
+              uint32_t v, spins = 0;
+              do {
+                asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(cp) : "memory");
+                if (++spins > 4000000u) __trap();
+              } while (__any_sync(0xFFFFFFFFu, int32_t(v - p.a_ready_target) < 0));
+              asm volatile("fence.proxy.async;" ::: "memory");
+            }
           } else {
             tile_coords(tile, p, mb, nb);
           }
@@ -486,10 +498,9 @@ fp8_blockwise_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gr
         mb = 0;
       } else {
         if constexpr (kWaitA) {
+          // (no poll here: this warp's first read of the m-block's scales comes after the tile's first accumulator
+          // hand-off, i.e. after the producer saw the counter — the writer made its rows visible before the counter)
           tile_coords_panels(tile, p, mb, nb);
-          // this warp reads the m-block's activation scales itself (ahead of the tile's first accumulator hand-off)
-          if (lane == 0) wait_rows_ready(p.a_ready + mb, p.a_ready_target);
-          __syncwarp();
         } else {
           tile_coords(tile, p, mb, nb);
         }
@@ -510,12 +521,17 @@ fp8_blockwise_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gr
       // of the iteration that uses it, so no instruction ever waits on an in-flight global load
       // (an in-order warp that multiplies right after the load stalls ~1 us per K block — measured).
       const int64_t sa_sk = p.sa_sk, sb_sk = p.sb_sk;
-      // (gated mode: the scales were written by other GPUs during this launch — read them at L2, never through the
-      // non-coherent path)
+      // (gated mode: the scales were written by other GPUs during this launch, so not through the non-coherent path; a
+      // plain L1-cached load is safe — L1 starts every launch empty and nothing of an m-block is read before its counter
+      // has been seen — and needed: the next group's scales are requested ~300 clk before their use, an L1 hit makes
+      // that, an L2 round trip does not: ld.cg cost 7 % of the kernel)
       auto ld_sa = [&](int kb) {
-        return (row_ok && kb < kb1) ? (kWaitA ? __ldcg(sa_ptr + int64_t(kb) * sa_sk) : __ldg(sa_ptr + int64_t(kb) * sa_sk)) : 0.0f;
+        return (row_ok && kb < kb1) ? (kWaitA ? *(sa_ptr + int64_t(kb) * sa_sk) : __ldg(sa_ptr + int64_t(kb) * sa_sk)) : 0.0f;
       };
-      auto ld_sa4 = [&](const float4* ptr) { return kWaitA ? __ldcg(ptr) : __ldg(ptr); };
+      auto ld_sa4 = [&](const float4* ptr) {
+        if constexpr (kWaitA) return *ptr;      // (a plain load the compiler may schedule, like the __ldg of the other form)
+        else return __ldg(ptr);
+      };
       auto ld_sb = [&](int kb) { return kb < kb1 ? __ldg(sb_ptr + int64_t(kb) * sb_sk) : 0.0f; };
       float sa0 = ld_sa(kb0), sb0 = ld_sb(kb0), sa1 = ld_sa(kb0 + 1), sb1 = ld_sb(kb0 + 1);
       constexpr int NCH = NC / 32;           // 32-column TMEM chunks per K block for this warp
@@ -736,9 +752,18 @@ fp8_blockwise_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gr
           // every group boundary under this register pressure (S2R + LDCU + 64-bit IMAD chain, ~200 clk measured)
           sa4n = sa4 + g;
           sb4n = sb4 + g;
-          a_nx = ld_sa4(sa4n);
+          // gated mode: the scales may be requested ahead of the tile's first hand-off only if the producer has already
+          // published the m-block as arrived; otherwise after the hand-off (which the producer's own wait precedes)
+          bool early = true;
+          if constexpr (kWaitA) {
+            unsigned long long seen;
+            asm volatile("ld.acquire.cta.shared.u64 %0, [%1];" : "=l"(seen) : "r"(ready_word) : "memory");
+            early = p.num_m_blocks <= 64 && ((seen >> mb) & 1ull);
+          }
+          if (early) a_nx = ld_sa4(sa4n);
           b_nx = __ldg(sb4n);
           ptx::mbar_wait(tfull_bar(acc * kHalves + hb), acc_phase);
+          if (!early) a_nx = ld_sa4(sa4n);
           ptx::tc_fence_after();
           taddr = stage_addr();
           ptx::tmem_ld_32x32(taddr, v[0]);
@@ -1335,6 +1360,7 @@ struct GateIn {
   const uint32_t* counters;
   uint32_t target;
   int rank, world;
+  int whole_panels;   // arrival order of the other ranks' panels: 0 = all at once, slice by slice; 1 = one panel after the other
 };
 
 static int gemm_entry(const void* A, const void* B, const float* sa, const float* sb, void* Cout, int64_t M,
@@ -1398,7 +1424,7 @@ static int gemm_entry(const void* A, const void* B, const float* sa, const float
 
   GemmParams p;
   p.grp_tiles = nullptr; p.grp_num_m_tiles = nullptr; p.grp_sb_expert_stride = 0;
-  p.a_ready = nullptr; p.a_ready_target = 0; p.panel_own = p.panel_rank = 0; p.panel_world = 1; p.panel_group = 1;
+  p.a_ready = nullptr; p.a_ready_target = 0; p.panel_own = p.panel_rank = 0; p.panel_world = 1; p.panel_group = 1; p.panel_whole = 0;
   p.sa = sa; p.sb = sb; p.C = Cout;
   p.M = M; p.N = N; p.K = K; p.ldc = ldc;
   p.sa_sm = sa_sm; p.sa_sk = sa_sk; p.sb_sk = sb_sk; p.sb_sn = sb_sn;
@@ -1514,7 +1540,9 @@ static int gemm_entry(const void* A, const void* B, const float* sa, const float
     p.panel_own = p.num_m_blocks / gate->world;
     if (p.group_m > p.panel_own) p.group_m = p.panel_own;
     const int w1 = gate->world - 1;
-    p.panel_group = w1 > 0 ? w1 * (8 / w1 > 0 ? 8 / w1 : 1) : 1;
+    p.panel_whole = gate->whole_panels ? 1 : 0;
+    // rasterisation groups of the remote part: whole slices (all-at-once arrival) or up to 8 m-blocks of one panel
+    p.panel_group = p.panel_whole ? (p.panel_own < 8 ? p.panel_own : 8) : (w1 > 0 ? w1 * (8 / w1 > 0 ? 8 / w1 : 1) : 1);
     if (out_dtype == SGLK_BF16)
       return launch_variant<256, 5, 2, __nv_bfloat16, true, 0, true, false, 0, false, 3, true>(ta, tb, tc, p, pl.workers, st);
     return launch_variant<256, 5, 2, __half, true, 0, true, false, 0, false, 3, true>(ta, tb, tc, p, pl.workers, st);
@@ -1636,8 +1664,8 @@ extern "C" int sglk_fp8_blockwise_scaled_mm_gated(const void* A, const void* B, 
                                                   int64_t sa_stride_m, int64_t sa_stride_k, int64_t sb_stride_k,
                                                   int64_t sb_stride_n, int out_dtype, int num_sms,
                                                   const uint32_t* row_ready_counters, uint32_t ready_target,
-                                                  int panel_rank, int panel_world, void* stream) {
-  const sglk::GateIn gate{row_ready_counters, ready_target, panel_rank, panel_world};
+                                                  int panel_rank, int panel_world, int whole_panels, void* stream) {
+  const sglk::GateIn gate{row_ready_counters, ready_target, panel_rank, panel_world, whole_panels};
   return sglk::gemm_entry(A, B, sa, sb, C, M, N, K, lda, ldb, ldc, sa_stride_m, sa_stride_k, sb_stride_k, sb_stride_n,
                           out_dtype, 29, num_sms, 0, nullptr, 0, stream, nullptr, 0, nullptr, nullptr, &gate);
 }

@@ -382,7 +382,7 @@ def _quant_bcast(x, q_ptr: int, s_ptr: int, counters_ptr: int, multicast: bool, 
 
 
 def _gemm_gated(mat_a, mat_b, scales_a, scales_b, out_dtype, counters, target: int, panel_rank: int, panel_world: int,
-                num_sms: int = 0):
+                num_sms: int = 0, whole_panels: bool = False):
     """fp8_blockwise_scaled_mm whose activation rows arrive during the launch (include/sglk_fp8.h:
     sglk_fp8_blockwise_scaled_mm_gated).  `counters`: uint32/int32 tensor, one entry per 256 rows of mat_a."""
     _check(mat_a.is_cuda and mat_b.is_cuda and scales_a.is_cuda and scales_b.is_cuda and counters.is_cuda,
@@ -400,7 +400,7 @@ def _gemm_gated(mat_a, mat_b, scales_a, scales_b, out_dtype, counters, target: i
             mat_a.data_ptr(), mat_b.data_ptr(), scales_a.data_ptr(), scales_b.data_ptr(), out.data_ptr(), M, N, K, lda, ldb,
             out.stride(0), scales_a.stride(0), scales_a.stride(1), scales_b.stride(0), scales_b.stride(1),
             _GEMM_OUT[out_dtype], num_sms, counters.data_ptr(), int(target) & 0xFFFFFFFF, int(panel_rank), int(panel_world),
-            _stream_ptr(mat_a))
+            1 if whole_panels else 0, _stream_ptr(mat_a))
     _lib.check(rc, "fp8_blockwise_scaled_mm (gated)")
     return out
 

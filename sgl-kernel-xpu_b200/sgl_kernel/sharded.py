@@ -107,8 +107,7 @@ class ColumnShardedFp8Linear:
 
     def enable_sharded_quant(self, max_tokens: int) -> bool:
         """Allocate the symmetric activation buffers (two sets: codes [M, K] e4m3, scales [M, K/128] fp32, one arrival
-        counter per 256 rows) and exchange the mappings (collective).  Returns False when the NVLS multicast mapping
-        is not available (the replicated path stays in use)."""
+        counter per 256 rows) and exchange the mappings (collective)."""
         import torch.distributed._symmetric_memory as symm_mem
 
         dev = self.local.weight_q.device
@@ -124,21 +123,37 @@ class ColumnShardedFp8Linear:
         self._sq_hdl.barrier(channel=0)                      # everybody's counters are zero before anybody adds to them
         mc = getattr(self._sq_hdl, "multicast_ptr", 0)
         self._sq_mc = int(mc) if mc else 0
-        return self._sq_mc != 0
+        # copy-engine transport: every peer's buffer as a tensor of this process, a side stream for the sends
+        self._sq_peer = [self._sq_buf if r == self.rank else self._sq_hdl.get_buffer(r, (2 * per_set,), torch.uint8, 0)
+                         for r in range(self.world)]
+        self._sq_copy_stream = torch.cuda.Stream(dev)
+        self._sq_ev = torch.cuda.Event()
+        return True
 
-    def forward_sharded_quant(self, x: torch.Tensor) -> torch.Tensor:
+    def forward_sharded_quant(self, x: torch.Tensor, transport: str = "copy") -> torch.Tensor:
         """This rank's [M, N/g] panel from REPLICATED bf16 activations `x` [M, K] — like forward_local, but rank r
-        quantises only rows [r, r+1) * M/g: the quant kernel writes codes and scales into every rank's buffer with
-        multimem.st and bumps per-256-row arrival counters, and the GEMM starts on its own rows at once and on the
-        others' as they arrive.  Two buffer sets alternate, so no cross-GPU barrier is needed: a rank can only start
-        step t+2 (which overwrites set t % 2) after its GEMM of step t+1, which needed every rank's step-t+1 rows, which
-        every rank sends after its own step-t GEMM.  Collective: every rank calls it with the same batch, in the same
-        order.  Bit-identical to forward_local (quantisation is row-local)."""
+        quantises only rows [r, r+1) * M/g; the codes, scales and per-256-row arrival counters reach every other
+        rank's buffers over NVLink while the GEMM (sglk_fp8_blockwise_scaled_mm_gated) already runs: it starts on its own
+        rows at once and on the others' as their counters arrive.  Bit-identical to forward_local (quantisation is
+        row-local).  Collective: every rank calls it with the same batch, in the same order.
+
+        transport "copy" (default): the quant kernel writes locally; the copy engines then push the panel to the peers
+          on a side stream, nearest consumer first (rank r-1 walks panel r right after its own, rank r-2 after that,
+          ...), each peer's data followed by its counters — at any time every rank sends to one peer and receives from
+          one, and no SM is involved, so the sends overlap the GEMM completely;
+        transport "multicast": the quant kernel itself stores to the NVLS multicast mapping (multimem.st) — one pass,
+          but the kernel then lasts as long as its stores take to leave the GPU, and the GEMM queues behind it.
+
+        Two buffer sets alternate, so no cross-GPU barrier is needed: a rank can only start step t+2 (which overwrites
+        set t % 2 everywhere) after its GEMM of step t+1, which needed every rank's step-t+1 rows, which every rank sends
+        after its own step-t GEMM."""
         from . import _ops
 
         m, k = x.shape
         # (one batch size per enable_sharded_quant: every block's counter then advances by the same amount per call)
-        assert self.sharded_quant_supported(m) and m == self._sq_tokens and self._sq_mc
+        assert self.sharded_quant_supported(m) and m == self._sq_tokens
+        multicast = transport == "multicast"
+        assert not multicast or self._sq_mc, "no NVLS multicast mapping on this system"
         b = self._sq_step & 1
         calls = self._sq_step // 2 + 1                       # calls on this buffer set, this one included
         base = b * self._sq_per_set
@@ -146,13 +161,26 @@ class ColumnShardedFp8Linear:
         rows = m // self.world
         lo = self.rank * rows
         g = k // 128
-        _ops._quant_bcast(x[lo:lo + rows], self._sq_mc + base + lo * k, self._sq_mc + off_s + lo * g * 4,
-                          self._sq_mc + off_c + (lo // 256) * 4, multicast=True)
+        dst = self._sq_mc if multicast else self._sq_buf.data_ptr()
+        _ops._quant_bcast(x[lo:lo + rows], dst + base + lo * k, dst + off_s + lo * g * 4, dst + off_c + (lo // 256) * 4,
+                          multicast=multicast)
+        if not multicast and self.world > 1:
+            # after the quant kernel the local counters of the own blocks hold exactly this step's target: they are
+            # what is sent behind the data
+            spans = [(base + lo * k, rows * k), (off_s + lo * g * 4, rows * g * 4), (off_c + (lo // 256) * 4, (rows // 256) * 4)]
+            cur = torch.cuda.current_stream()
+            self._sq_ev.record(cur)
+            with torch.cuda.stream(self._sq_copy_stream):
+                self._sq_copy_stream.wait_event(self._sq_ev)
+                for i in range(1, self.world):
+                    peer = self._sq_peer[(self.rank - i) % self.world]
+                    for off, nbytes in spans:                # codes, scales, then the counters (stream order)
+                        peer[off:off + nbytes].copy_(self._sq_buf[off:off + nbytes], non_blocking=True)
         xq = self._sq_buf[base:base + m * k].view(torch.float8_e4m3fn).view(m, k)
         xs = self._sq_buf[off_s:off_s + m * g * 4].view(torch.float32).view(m, g)
         cnt = self._sq_buf[off_c:off_c + (m // 256) * 4].view(torch.int32)
         out = _ops._gemm_gated(xq, self.local.weight_q.t(), xs, self.local.weight_scale.t(), self.local.out_dtype, cnt,
-                               calls * _ops.counter_increments(k), self.rank, self.world)
+                               calls * _ops.counter_increments(k), self.rank, self.world, whole_panels=not multicast)
         self._sq_step += 1
         return out
 

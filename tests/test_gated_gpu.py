@@ -58,9 +58,10 @@ def test_gated_gemm_matches_plain(M, N, K, world):
     inc = _ops.counter_increments(K)
     cnt = torch.full((M // 256,), 3 * inc, dtype=torch.int32, device=DEV)     # "third call on this buffer"
     for rank in range(world):
-        out = _ops._gemm_gated(xq, wq.t(), xs, ws.t(), torch.bfloat16, cnt, 3 * inc, rank, world)
-        torch.cuda.synchronize()
-        assert torch.equal(out, ref), f"rank {rank} of {world}"
+        for whole in (False, True):                      # both arrival orders of the other ranks' panels
+            out = _ops._gemm_gated(xq, wq.t(), xs, ws.t(), torch.bfloat16, cnt, 3 * inc, rank, world, whole_panels=whole)
+            torch.cuda.synchronize()
+            assert torch.equal(out, ref), f"rank {rank} of {world}, whole_panels={whole}"
     out = _ops._gemm_gated(xq, wq.t(), xs, ws.t(), torch.bfloat16, cnt, 2 * inc, 0, world)   # counters ahead of the target
     torch.cuda.synchronize()
     assert torch.equal(out, ref)

@@ -1,3 +1,4 @@
 mkdir -p gpurun_out
-timeout 600 python -m pytest tests/test_gated_gpu.py -x -q > gpurun_out/r7_pytest.log 2>&1; echo "rc=$?" >> gpurun_out/r7_pytest.log
-tail -30 gpurun_out/r7_pytest.log
+timeout 120 python -m pytest tests/test_gated_gpu.py -x -q 2>&1 | tail -2
+(timeout 300 python tools/gated_ab.py 8,4,2) > gpurun_out/r18_gated.log 2>&1; echo "rc=$?" >> gpurun_out/r18_gated.log
+cat gpurun_out/r18_gated.log

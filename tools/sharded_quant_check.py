@@ -21,6 +21,7 @@ wq = ((torch.rand(hi - lo, K, generator=gw, device=dev) - 0.5) * 896).to(torch.f
 ws = (torch.rand(-((hi - lo) // -128), K // 128, generator=gw, device=dev) + 0.5) * 1e-3
 layer = ColumnShardedFp8Linear(sgl_kernel.Fp8BlockLinear(wq, ws), N)
 ok = layer.sharded_quant_supported(M) and layer.enable_sharded_quant(M)
+TRANSPORTS = ["copy", "multicast"] if (ok and layer._sq_mc) else ["copy"]
 res = {"world": world, "M": M, "N": N, "K": K, "multicast_available": bool(ok)}
 same = True
 if ok:
@@ -29,9 +30,12 @@ if ok:
         g = torch.Generator(device=dev).manual_seed(1000 + step)
         x = torch.randn(M, K, generator=g, device=dev).to(torch.bfloat16)
         ref = layer.forward_local(x)
-        out = layer.forward_sharded_quant(x)
+        tr = TRANSPORTS[step % len(TRANSPORTS)]
+        out = layer.forward_sharded_quant(x, transport=tr)
         torch.cuda.synchronize()
-        same = same and bool(torch.equal(out, ref))
+        eq = bool(torch.equal(out, ref))
+        res[f"step{step}_{tr}"] = eq
+        same = same and eq
     flush = torch.zeros(256 << 20, dtype=torch.uint8, device=dev).view(torch.int64)
 
     def timeit(fn, n=20):
@@ -49,8 +53,15 @@ if ok:
 
     t_rep = timeit(lambda: layer.forward_local(x))
     t_shq = timeit(lambda: layer.forward_sharded_quant(x))
+    if "multicast" in TRANSPORTS:
+        res["ms_sharded_quant_step_multicast"] = timeit(lambda: layer.forward_sharded_quant(x, transport="multicast"))
     xq, xs = layer.local.quantize_input(x)
     t_gemm = timeit(lambda: layer.local.forward_quantized(xq, xs))
+    from sgl_kernel import _ops
+    zero = torch.zeros(M // 256, dtype=torch.int32, device=dev)
+    for whole in (False, True):      # the gated kernel alone, every counter already at its target: cost of the walk order + polls
+        res["ms_gated_gemm_alone_" + ("panels" if whole else "slices")] = timeit(
+            lambda: _ops._gemm_gated(xq, wq.t(), xs, ws.t(), torch.bfloat16, zero, 0, rank, world, whole_panels=whole))
     res.update({"bitwise_equal_to_replicated": same, "ms_replicated_quant_step": t_rep, "ms_sharded_quant_step": t_shq,
                 "ms_gemm_alone": t_gemm, "tflops_replicated": 2.0 * M * N * K / t_rep / 1e9,
                 "tflops_sharded_quant": 2.0 * M * N * K / t_shq / 1e9})
