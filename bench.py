@@ -478,6 +478,40 @@ def main():
             with_gather["fused_error"] = str(e)[:200]
         del full
 
+    # ---- row-sharded activation quantisation + gated GEMM (sgl_kernel/sharded.py forward_sharded_quant): each rank
+    # quantises M/g rows, the copy engines push them to the peers behind the GEMM, which starts on its own rows at once.
+    # Reported next to `value` (whose step quantises everything on every rank); bitwise equality with that step's
+    # output is checked on every rank.
+    sharded_quant = None
+    if world > 1:
+        try:
+            if sharded.sharded_quant_supported(M):
+                sharded.enable_sharded_quant(M)
+                ref_panel = step()
+                ok_sq = True
+                for _ in range(3):
+                    ok_sq = ok_sq and bool(torch.equal(sharded.forward_sharded_quant(x), ref_panel))
+                flag = torch.tensor([1 if ok_sq else 0], device=dev, dtype=torch.int32)
+                dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+                ok_sq = bool(flag.item())
+                gather_mismatch |= not ok_sq
+                barrier()
+                evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+                for i in range(args.steps):
+                    flush_l2()
+                    evs[i][0].record()
+                    sharded.forward_sharded_quant(x)
+                    evs[i][1].record()
+                barrier()
+                tsq = torch.tensor([sum(a.elapsed_time(b) for a, b in evs) / args.steps], device=dev, dtype=torch.float64)
+                dist.all_reduce(tsq, op=dist.ReduceOp.MAX)
+                sharded_quant = {"matches_replicated": ok_sq, "ms_per_step": float(tsq.item()),
+                                 "value": 2.0 * M * N * K / (float(tsq.item()) * 1e-3) / 1e12, "unit": "TFLOPS",
+                                 "transport": "copy engines, ring schedule, per-256-row arrival counters; gated GEMM",
+                                 "nvlink_bytes_in_per_rank": int((M - M // world) * (K + (K // 128) * 4))}
+        except Exception as e:  # noqa: BLE001
+            sharded_quant = {"error": str(e)[:200]}
+
     # ---- end to end through the public API with HOST buffers (pinned), copies inside the timed region ----
     e2e = None
     if not args.no_e2e:
@@ -622,7 +656,7 @@ def main():
                            "traffic": quant_traffic, "traffic_source": quant_traffic_src, "kernel": "ptgq_kernel",
                            "algorithmic_bytes_per_launch": quant_bytes,
                            "peak_source": f"{peaks['source']} copy bandwidth; frac of nominal 8000 GB/s = {quant_gbs / HBM_NOMINAL_GBS:.3f}"},
-        "cpu_baseline": cpu_baseline, "e2e": e2e, "with_all_gather": with_gather,
+        "cpu_baseline": cpu_baseline, "e2e": e2e, "with_all_gather": with_gather, "sharded_quant": sharded_quant,
         "gpu_launches": 2 * args.steps * world, "clocks": clocks, "wall_s_timed_region": t_wall,
     }
     if world == 1 and not args.no_configs and M == M_FULL:
@@ -635,7 +669,7 @@ def main():
     if world > 1:
         dist.destroy_process_group()
     if gather_mismatch:
-        raise SystemExit("fused gather result differs from the NCCL-gathered result (see with_all_gather.*.matches_nccl)")
+        raise SystemExit("a fused multi-GPU form differs from its reference (see with_all_gather.*.matches_nccl, sharded_quant.matches_replicated)")
 
 
 if __name__ == "__main__":

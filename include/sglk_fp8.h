@@ -275,6 +275,12 @@ SGLK_API int sglk_fp8_blockwise_scaled_mm_gated(const void* A, const void* B, co
                                        const uint32_t* row_ready_counters, uint32_t ready_target, int panel_rank,
                                        int panel_world, int whole_panels, void* stream);
 
+/* Host-side copy of the gated kernel's walk, for tests and schedulers: out[2t] / out[2t+1] = the 256-row m-block and the
+ * 256-column n-block of the t-th tile in launch order (tile t goes to CTA pair t mod #pairs).  Returns the number of
+ * tiles (out may be NULL to ask for it), -1 for shapes the gated entry point rejects.  No device is touched. */
+SGLK_API int64_t sglk_gated_walk_order(int32_t* out, int64_t M, int64_t N, int64_t K, int panel_rank, int panel_world,
+                              int whole_panels);
+
 /*
  * Replaces: void fp8_blockwise_scaled_grouped_mm(output, a_ptrs, ..., problem_sizes, expert_offsets, workspace)
  *   declared /root/reference/include/sgl_kernel_ops.h:660-678, wrapped python/sgl_kernel/moe.py:236-276, semantics

@@ -153,7 +153,7 @@ __device__ __forceinline__ void tile_coords(int tile, const GemmParams& p, int& 
 }
 
 // gated mode: tile index -> (physical m-block, n-block) in arrival order (see GemmParams::a_ready)
-__device__ __forceinline__ void tile_coords_panels(int tile, const GemmParams& p, int& mb, int& nb) {
+__host__ __device__ __forceinline__ void tile_coords_panels(int tile, const GemmParams& p, int& mb, int& nb) {
   // straight-line on purpose (selects, no branches): with branches here ptxas kept the producer's loop state out of the
   // uniform registers
   const int own = p.panel_own, nn = p.num_n_blocks;
@@ -163,11 +163,11 @@ __device__ __forceinline__ void tile_coords_panels(int tile, const GemmParams& p
   const int span = is_own ? own : p.num_m_blocks - own;
   const int per_group = gsz * nn;
   const int g = t / per_group, first = g * gsz;
-  const int rows = min(gsz, span - first), in_g = t - g * per_group;
+  const int rows = gsz < span - first ? gsz : span - first, in_g = t - g * per_group;
   nb = in_g / rows;
   const int r = first + (in_g - nb * rows);                       // position inside the own / the remote part of the walk
   // remote part: whole panels one after the other (i = peer index, j = block in panel), or slice by slice
-  const int d = p.panel_whole ? own : max(p.panel_world - 1, 1);
+  const int d = p.panel_whole ? own : (p.panel_world > 2 ? p.panel_world - 1 : 1);
   const int q = r / d, m = r - q * d;
   const int i = p.panel_whole ? q : m, j = p.panel_whole ? m : q;
   int panel = p.panel_rank + 1 + i;
@@ -1355,6 +1355,18 @@ struct QuantOut {
   int silu_mul;
 };
 
+// The gated kernel's walk over the m-blocks (GemmParams::a_ready): num_m_blocks, num_n_blocks and group_m are set.
+static void set_panel_walk(GemmParams& p, int rank, int world, int whole_panels) {
+  p.panel_world = world;
+  p.panel_rank = rank;
+  p.panel_own = p.num_m_blocks / world;
+  if (p.group_m > p.panel_own) p.group_m = p.panel_own;
+  const int w1 = world - 1;
+  p.panel_whole = whole_panels ? 1 : 0;
+  // rasterisation groups of the remote part: whole slices (all-at-once arrival) or up to 8 m-blocks of one panel
+  p.panel_group = p.panel_whole ? (p.panel_own < 8 ? p.panel_own : 8) : (w1 > 0 ? w1 * (8 / w1 > 0 ? 8 / w1 : 1) : 1);
+}
+
 // Gated request (sglk_fp8_blockwise_scaled_mm_gated): one arrival counter per 256 rows of A, see GemmParams::a_ready.
 struct GateIn {
   const uint32_t* counters;
@@ -1535,14 +1547,7 @@ static int gemm_entry(const void* A, const void* B, const float* sa, const float
     if (!p.scale_vec) return SGLK_E_STRIDE;
     p.a_ready = gate->counters;
     p.a_ready_target = gate->target;
-    p.panel_world = gate->world;
-    p.panel_rank = gate->rank;
-    p.panel_own = p.num_m_blocks / gate->world;
-    if (p.group_m > p.panel_own) p.group_m = p.panel_own;
-    const int w1 = gate->world - 1;
-    p.panel_whole = gate->whole_panels ? 1 : 0;
-    // rasterisation groups of the remote part: whole slices (all-at-once arrival) or up to 8 m-blocks of one panel
-    p.panel_group = p.panel_whole ? (p.panel_own < 8 ? p.panel_own : 8) : (w1 > 0 ? w1 * (8 / w1 > 0 ? 8 / w1 : 1) : 1);
+    set_panel_walk(p, gate->rank, gate->world, gate->whole_panels);
     if (out_dtype == SGLK_BF16)
       return launch_variant<256, 5, 2, __nv_bfloat16, true, 0, true, false, 0, false, 3, true>(ta, tb, tc, p, pl.workers, st);
     return launch_variant<256, 5, 2, __half, true, 0, true, false, 0, false, 3, true>(ta, tb, tc, p, pl.workers, st);
@@ -1668,6 +1673,29 @@ extern "C" int sglk_fp8_blockwise_scaled_mm_gated(const void* A, const void* B, 
   const sglk::GateIn gate{row_ready_counters, ready_target, panel_rank, panel_world, whole_panels};
   return sglk::gemm_entry(A, B, sa, sb, C, M, N, K, lda, ldb, ldc, sa_stride_m, sa_stride_k, sb_stride_k, sb_stride_n,
                           out_dtype, 29, num_sms, 0, nullptr, 0, stream, nullptr, 0, nullptr, nullptr, &gate);
+}
+
+extern "C" int64_t sglk_gated_walk_order(int32_t* out, int64_t M, int64_t N, int64_t K, int panel_rank, int panel_world,
+                                         int whole_panels) {
+  using namespace sglk;
+  if (M <= 0 || N < 256 || K <= 0 || panel_world < 1 || panel_rank < 0 || panel_rank >= panel_world ||
+      M % (int64_t(2 * BLOCK_M) * panel_world) != 0) return -1;
+  GemmParams p;
+  memset(&p, 0, sizeof(p));
+  p.num_m_blocks = int32_t(M / (2 * BLOCK_M));
+  p.num_n_blocks = int32_t((N + 255) / 256);
+  int64_t gm = (int64_t(32) << 20) / (int64_t(2 * BLOCK_M) * K);        // as gemm_entry
+  p.group_m = int32_t(gm < 4 ? 4 : (gm > 16 ? 16 : gm));
+  set_panel_walk(p, panel_rank, panel_world, whole_panels);
+  const int64_t tiles = int64_t(p.num_m_blocks) * p.num_n_blocks;
+  if (out)
+    for (int64_t t = 0; t < tiles; ++t) {
+      int mb, nb;
+      tile_coords_panels(int(t), p, mb, nb);
+      out[2 * t] = mb;
+      out[2 * t + 1] = nb;
+    }
+  return tiles;
 }
 
 extern "C" int64_t sglk_gemm_workspace_bytes(int64_t M, int64_t N, int64_t K, int variant, int num_sms, int flags) {

@@ -48,6 +48,7 @@ SYMBOLS = {
     "sglk_per_token_group_quant_fp8_bcast": (_i32, [_vp, _vp, _vp, _vp, _i64, _i64, _i64, _i32, _f32, _i32, _vp]),
     "sglk_fp8_blockwise_scaled_mm_gated": (
         _i32, [_vp, _vp, _vp, _vp, _vp] + [_i64] * 10 + [_i32, _i32, _vp, ctypes.c_uint32, _i32, _i32, _i32, _vp]),
+    "sglk_gated_walk_order": (_i64, [_vp, _i64, _i64, _i64, _i32, _i32, _i32]),
     "sglk_gemm_num_variants": (_i32, []),
     "sglk_gemm_variant_name": (ctypes.c_char_p, [_i32]),
     "sglk_gemm_variant_is_product": (_i32, [_i32]),

@@ -1,4 +1,3 @@
 mkdir -p gpurun_out
-timeout 120 python -m pytest tests/test_gated_gpu.py -x -q 2>&1 | tail -2
-(timeout 300 python tools/gated_ab.py 8,4,2) > gpurun_out/r18_gated.log 2>&1; echo "rc=$?" >> gpurun_out/r18_gated.log
-cat gpurun_out/r18_gated.log
+timeout 200 python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29519 tools/peer_copy_bw.py > gpurun_out/r21_copybw.log 2>&1; echo "rc=$?" >> gpurun_out/r21_copybw.log
+tail -2 gpurun_out/r21_copybw.log

@@ -38,33 +38,36 @@ if ok:
         same = same and eq
     flush = torch.zeros(256 << 20, dtype=torch.uint8, device=dev).view(torch.int64)
 
-    def timeit(fn, n=20):
-        for _ in range(3):
-            fn()
-        torch.cuda.synchronize(); dist.barrier()
-        ts = []
-        for _ in range(n):
-            flush.sum()
-            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            e0.record(); fn(); e1.record(); e1.synchronize()
-            ts.append(e0.elapsed_time(e1))
-        t = torch.tensor([sum(ts) / n], device=dev); dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        return float(t.item())
+    def step_ms(fn):
+        flush.sum()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(); fn(); e1.record(); e1.synchronize()
+        return e0.elapsed_time(e1)
 
-    t_rep = timeit(lambda: layer.forward_local(x))
-    t_shq = timeit(lambda: layer.forward_sharded_quant(x))
-    if "multicast" in TRANSPORTS:
-        res["ms_sharded_quant_step_multicast"] = timeit(lambda: layer.forward_sharded_quant(x, transport="multicast"))
-    xq, xs = layer.local.quantize_input(x)
-    t_gemm = timeit(lambda: layer.local.forward_quantized(xq, xs))
     from sgl_kernel import _ops
+    xq, xs = layer.local.quantize_input(x)
     zero = torch.zeros(M // 256, dtype=torch.int32, device=dev)
-    for whole in (False, True):      # the gated kernel alone, every counter already at its target: cost of the walk order + polls
-        res["ms_gated_gemm_alone_" + ("panels" if whole else "slices")] = timeit(
-            lambda: _ops._gemm_gated(xq, wq.t(), xs, ws.t(), torch.bfloat16, zero, 0, rank, world, whole_panels=whole))
-    res.update({"bitwise_equal_to_replicated": same, "ms_replicated_quant_step": t_rep, "ms_sharded_quant_step": t_shq,
-                "ms_gemm_alone": t_gemm, "tflops_replicated": 2.0 * M * N * K / t_rep / 1e9,
-                "tflops_sharded_quant": 2.0 * M * N * K / t_shq / 1e9})
+    fns = {"replicated_quant_step": lambda: layer.forward_local(x),
+           "sharded_quant_step": lambda: layer.forward_sharded_quant(x),
+           "gemm_alone": lambda: layer.local.forward_quantized(xq, xs),
+           "gated_gemm_alone": lambda: _ops._gemm_gated(xq, wq.t(), xs, ws.t(), torch.bfloat16, zero, 0, rank, world, whole_panels=True)}
+    if "multicast" in TRANSPORTS:
+        fns["sharded_quant_step_multicast"] = lambda: layer.forward_sharded_quant(x, transport="multicast")
+    # interleaved rounds (the clocks drift under the power cap); every configuration is a collective or rank-local, and
+    # every rank runs them in the same order
+    for f in fns.values():
+        f(); f()
+    torch.cuda.synchronize(); dist.barrier()
+    ts = {k: [] for k in fns}
+    for _ in range(15):
+        for k, f in fns.items():
+            ts[k].append(step_ms(f))
+    for k, v in ts.items():
+        t = torch.tensor([sorted(v)[len(v) // 2]], device=dev); dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        res["ms_" + k] = round(float(t.item()), 4)
+    res["bitwise_equal_to_replicated"] = same
+    res["tflops_replicated"] = round(2.0 * M * N * K / res["ms_replicated_quant_step"] / 1e9, 1)
+    res["tflops_sharded_quant"] = round(2.0 * M * N * K / res["ms_sharded_quant_step"] / 1e9, 1)
 flag = torch.tensor([int(same)], device=dev); dist.all_reduce(flag, op=dist.ReduceOp.MIN)
 if rank == 0:
     res["bitwise_equal_on_all_ranks"] = bool(flag.item())
