@@ -311,6 +311,23 @@ def other_configs(torch, sgl_kernel, dev, peaks, flush):
                  "timing": "cuda events, L2 flushed between launches, median of 7",
                  "roofline": {"bound": "tensor", "achieved": fl / us / 1e6, "peak": fp8_peak, "unit": "TFLOP/s",
                               "frac": fl / us / 1e6 / fp8_peak, "algorithmic_flops": fl}})
+    # ---- §8 f4: grouped (MoE) blockwise GEMM, DeepSeek-V3 expert shapes, uneven routing (tools/grouped_bench.py) ----
+    try:
+        sys.path.insert(0, os.path.join(ROOT, "tools"))
+        import grouped_bench
+
+        grouped_bench.Es, grouped_bench.avg = [8, 32], 512
+        for r in grouped_bench.records():
+            fl = 2.0 * r["sum_m"] * r["N"] * r["K"]
+            recs.append({"config": f"f4 grouped MoE GEMM E={r['experts']} {r['proj']} sum_m={r['sum_m']} N={r['N']} K={r['K']}",
+                         "op": "fp8_blockwise_scaled_grouped_mm", "us": round(r["ms"] * 1e3, 1), "value": r["tflops"],
+                         "unit": "TFLOPS", "dense_op_same_flops_tflops": r["dense_tflops"],
+                         "expert0_equals_dense_op": r["expert0_equals_dense_op"],
+                         "timing": "cuda events, L2 flushed between launches, median of 9",
+                         "roofline": {"bound": "tensor", "achieved": r["tflops"], "peak": fp8_peak, "unit": "TFLOP/s",
+                                      "frac": r["tflops"] / fp8_peak, "algorithmic_flops": fl}})
+    except Exception as e:  # noqa: BLE001
+        recs.append({"config": "f4 grouped MoE GEMM", "error": str(e)[:200]})
     return recs
 
 

@@ -204,6 +204,9 @@ SGLK_API int sglk_fp8_blockwise_scaled_mm_ex(const void* A, const void* B, const
  *               [256j+128, 256j+256) (scales_b columns likewise); out_q [M, N/2], out_s (row, g) for g < N/256.
  *               silu in fp32 rounded to round_dtype, product rounded to round_dtype — the v2 quant op's fused mode
  *               (/root/reference/src/sycl/per_token_group_quant_8bit_v2.cpp:255-262).            Needs N % 256 == 0.
+ *               LABORATORY BUILD ONLY (libsglk_diag.so): correct but slower than the separate ops (the exact expf +
+ *               division chain runs in the epilogue while the tensor pipe waits); the product library answers
+ *               SGLK_E_VARIANT.
  * out_q row stride ldq (bytes, multiple of 16); out_s element (row, g) at row*os_stride_m + g*os_stride_g floats.
  * Other arguments as sglk_fp8_blockwise_scaled_mm_ex.
  */

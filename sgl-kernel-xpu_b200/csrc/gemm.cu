@@ -1245,17 +1245,23 @@ static bool variant_available(int v) {
 }
 
 // fused output quantisation: the paired 256x256 tiles for prefill, the single-CTA 128x256 tiles below that
+// The silu(gate)*up mode (kEpi == 2) is a LABORATORY form: correct (bit-identical to GEMM -> v2 quant op) but slower than
+// the separate ops (3.26 against 2.07 ms at 16384 x 18432 x 7168 — the exact expf + IEEE division of silu_mul is a ~60-
+// instruction dependent chain per element, run by 4 of the 12 warps while the tensor pipe waits).  It is compiled only
+// into libsglk_diag.so; the product library answers SGLK_E_VARIANT.
 template <typename OutT>
 static int launch_quant_epilogue(int v, int mode, const CUtensorMap& ta, const CUtensorMap& tb, const CMaps& tc,
                                  const GemmParams& p, int workers, cudaStream_t st) {
-  if (v == 13) {   // split-N pair tiles, like the plain GEMM's prefill default
-    return mode == 2 ? launch_variant<256, 6, 2, OutT, true, 0, true, false, 2>(ta, tb, tc, p, workers, st)
-                     : launch_variant<256, 6, 2, OutT, true, 0, true, false, 1>(ta, tb, tc, p, workers, st);
+#ifdef SGLK_DIAG
+  if (mode == 2) {
+    if (v == 13) return launch_variant<256, 6, 2, OutT, true, 0, true, false, 2>(ta, tb, tc, p, workers, st);
+    if (v == 2) return launch_variant<256, 4, 1, OutT, true, 0, false, false, 2>(ta, tb, tc, p, workers, st);
+    return SGLK_E_VARIANT;
   }
-  if (v == 2) {
-    return mode == 2 ? launch_variant<256, 4, 1, OutT, true, 0, false, false, 2>(ta, tb, tc, p, workers, st)
-                     : launch_variant<256, 4, 1, OutT, true, 0, false, false, 1>(ta, tb, tc, p, workers, st);
-  }
+#endif
+  if (mode != 1) return SGLK_E_VARIANT;
+  if (v == 13) return launch_variant<256, 6, 2, OutT, true, 0, true, false, 1>(ta, tb, tc, p, workers, st);   // split-N pair tiles
+  if (v == 2) return launch_variant<256, 4, 1, OutT, true, 0, false, false, 1>(ta, tb, tc, p, workers, st);
   return SGLK_E_VARIANT;
 }
 
