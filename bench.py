@@ -322,7 +322,7 @@ def other_configs(torch, sgl_kernel, dev, peaks, flush):
             recs.append({"config": f"f4 grouped MoE GEMM E={r['experts']} {r['proj']} sum_m={r['sum_m']} N={r['N']} K={r['K']}",
                          "op": "fp8_blockwise_scaled_grouped_mm", "us": round(r["ms"] * 1e3, 1), "value": r["tflops"],
                          "unit": "TFLOPS", "dense_op_same_flops_tflops": r["dense_tflops"],
-                         "expert0_equals_dense_op": r["expert0_equals_dense_op"],
+                         "expert0_matches_dense_op": r["expert0_matches_dense_op"],
                          "timing": "cuda events, L2 flushed between launches, median of 9",
                          "roofline": {"bound": "tensor", "achieved": r["tflops"], "peak": fp8_peak, "unit": "TFLOP/s",
                                       "frac": r["tflops"] / fp8_peak, "algorithmic_flops": fl}})

@@ -199,7 +199,8 @@ fp8_blockwise_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gr
   constexpr int kAccBars = kAccStages * kHalves;
   static_assert(!kSplitN || (BLOCK_N == 256 && (kDiag == 0 || kDiag == 4)), "split-N is for the 256-wide product tiles");
   static_assert(!kTmaStore || C::kCanTmaStore, "TMA-store epilogue needs >= 64 columns per warp");
-  static_assert(!kGrouped || (kCG == 1 && !kTmaStore && kDiag == 0 && !kSplitN), "grouped mode: single-CTA tiles, predicated stores");
+  static_assert(!kGrouped || (kDiag == 0 && ((kCG == 1 && !kTmaStore && !kSplitN) || (kCG == 2 && kTmaStore && kSplitN))),
+                "grouped mode: single-CTA 128-row tiles with direct stores, or split-N pair tiles (256 rows) staged through smem");
   static_assert(kEpi == 0 || (BLOCK_N == 256 && kTmaStore && kDiag == 0 && !kGrouped),
                 "fused output quantisation: 256-wide tiles (one 128-column group per epilogue warp), TMA-store epilogue");
 
@@ -285,11 +286,12 @@ fp8_blockwise_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gr
       WorkIter it(p, worker, num_workers, num_tiles);
       int tile, kb0, kb1;
       while (it.next(tile, kb0, kb1)) {
-        int mb, nb, m0, n0;
+        int mb, nb, m0, n0, n_tile;
         if constexpr (kGrouped) {
           const int4 ti = grouped_tile(tile, nb);
-          m0 = ti.x;                                            // rows past the expert's range are loaded but never stored
-          n0 = ti.z * int(p.N) + nb * BLOCK_N;                  // B is the experts' [N, K] matrices stacked
+          m0 = ti.x + int(cta_rank) * BLOCK_M;                  // rows past the expert's range are loaded but never stored
+          n_tile = ti.z * int(p.N) + nb * BLOCK_N;              // B is the experts' [N, K] matrices stacked
+          n0 = n_tile + int(cta_rank) * C::LOAD_N;
           mb = 0; (void)mb;
         } else {
           if constexpr (kWaitA) {
@@ -330,7 +332,8 @@ fp8_blockwise_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gr
             tile_coords(tile, p, mb, nb);
           }
           m0 = mb * (BLOCK_M * kCl) + int(cta_rank) * BLOCK_M;
-          n0 = nb * BLOCK_N + int(cta_rank) * (kMcB ? BLOCK_N / 2 : C::LOAD_N);
+          n_tile = nb * BLOCK_N;
+          n0 = n_tile + int(cta_rank) * (kMcB ? BLOCK_N / 2 : C::LOAD_N);
         }
         for (int kb = kb0; kb < kb1; ++kb) {
           ptx::mbar_wait(empty_bar(stage), phase ^ 1);
@@ -354,7 +357,7 @@ fp8_blockwise_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gr
               ptx::tma_load_2d_pair(&tmap_a, leader_full, sa_addr, kb * BLOCK_K, m0, pol_a);
               if constexpr (kSplitN) {
                 // column half h of the pair's tile = [n_tile + h*128, +128): this CTA contributes 64 rows of each half
-                const int nt = nb * BLOCK_N + int(cta_rank) * (BLOCK_N / 4);
+                const int nt = n_tile + int(cta_rank) * (BLOCK_N / 4);
                 ptx::tma_load_2d_pair(&tmap_b, leader_full, sb_addr, kb * BLOCK_K, nt, pol_b);
                 ptx::tma_load_2d_pair(&tmap_b, leader_full, sb_addr + (BLOCK_N / 4) * BLOCK_K, kb * BLOCK_K, nt + BLOCK_N / 2, pol_b);
               } else {
@@ -488,12 +491,14 @@ fp8_blockwise_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gr
     bool first_segment = true;
     while (it.next(tile, kb0, kb1)) {
       int mb, nb, m0;
+      int row_limit = int(p.M);       // first row this tile must not write (grouped: the next expert's first row)
       bool row_ok;
       const float* sb_base = p.sb;
       if constexpr (kGrouped) {
         const int4 ti = grouped_tile(tile, nb);
-        m0 = ti.x;
-        row_ok = quarter * 32 + lane < ti.y;                    // rows of this expert in the tile
+        m0 = ti.x + int(cta_rank) * BLOCK_M;
+        row_ok = int(cta_rank) * BLOCK_M + quarter * 32 + lane < ti.y;   // rows of this expert in the tile
+        row_limit = ti.x + ti.y;
         sb_base += int64_t(ti.z) * p.grp_sb_expert_stride;
         mb = 0;
       } else {
@@ -990,10 +995,12 @@ fp8_blockwise_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gr
               const uint32_t dst = my_store + uint32_t(lane * 128 + ((j ^ (lane & 7)) << 4));
               asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(dst), "r"(w0), "r"(w1), "r"(w2), "r"(w3) : "memory");
             }
-            if (p.mc_ptr != nullptr) {
+            if (kGrouped || p.mc_ptr != nullptr) {
               // NVLS multicast form of the fused all-gather: one multimem.st per 16 bytes lands in EVERY GPU's
               // buffer (the NVSwitch replicates), so a rank sends its panel once instead of once per peer.
-              // Read the staged box back row-contiguously: 8 lanes cover one 128-byte row segment.
+              // Grouped (MoE) form: plain 16-byte stores, rows cut at the expert's last row (a TMA box would run into
+              // the next expert's rows).  Both read the staged box back row-contiguously: 8 lanes cover one 128-byte
+              // row segment.
               __syncwarp();
 #pragma unroll
               for (int i = 0; i < 8; ++i) {
@@ -1004,11 +1011,15 @@ fp8_blockwise_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gr
                 asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(w0), "=r"(w1), "=r"(w2), "=r"(w3) : "r"(src));
                 const int grow = m0 + quarter * 32 + r;
                 const int gcol = col0 + cb * kStoreBoxCols + ch * 8;
-                if (grow < p.M && gcol + 8 <= p.N) {
-                  OutT* dst = reinterpret_cast<OutT*>(p.mc_ptr) + int64_t(grow) * p.ldc + gcol;
-                  asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};"
-                               ::"l"(dst), "f"(__uint_as_float(w0)), "f"(__uint_as_float(w1)), "f"(__uint_as_float(w2)),
-                                 "f"(__uint_as_float(w3)) : "memory");
+                if (grow < row_limit && gcol + 8 <= p.N) {
+                  if constexpr (kGrouped) {
+                    *reinterpret_cast<uint4*>(reinterpret_cast<OutT*>(p.C) + int64_t(grow) * p.ldc + gcol) = make_uint4(w0, w1, w2, w3);
+                  } else {
+                    OutT* dst = reinterpret_cast<OutT*>(p.mc_ptr) + int64_t(grow) * p.ldc + gcol;
+                    asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};"
+                                 ::"l"(dst), "f"(__uint_as_float(w0)), "f"(__uint_as_float(w1)), "f"(__uint_as_float(w2)),
+                                   "f"(__uint_as_float(w3)) : "memory");
+                  }
                 }
               }
               __syncwarp();
@@ -1085,17 +1096,17 @@ __global__ void __launch_bounds__(256) relayout_scales_kernel(RelayoutJob ja, Re
 }
 
 // Grouped (MoE) GEMM: the m-tile table.  Expert e owns rows [offsets[e], offsets[e] + sizes[e][0]) of the stacked A;
-// it contributes ceil(m_e / 128) entries {first row, valid rows, expert, 0}.  One block, one thread per expert,
+// it contributes ceil(m_e / tile_rows) entries {first row, valid rows, expert, 0} (tile_rows = 128, or 256 for pair tiles).  One block, one thread per expert,
 // an inclusive scan of the tile counts in shared memory; everything stays on the device (no host sync, capturable).
 __global__ void __launch_bounds__(1024)
 build_group_tiles_kernel(const int32_t* __restrict__ offsets, const int32_t* __restrict__ sizes, int num_experts,
-                         int4* __restrict__ table, int32_t* __restrict__ count, int max_tiles) {
+                         int4* __restrict__ table, int32_t* __restrict__ count, int max_tiles, int tile_rows) {
   __shared__ int scan[1024];
   int base = 0;                                           // tiles of the experts handled in earlier rounds
   for (int e0 = 0; e0 < num_experts; e0 += 1024) {
     const int e = e0 + int(threadIdx.x);
     const int m = e < num_experts ? max(sizes[e * 3], 0) : 0;
-    const int nt = (m + BLOCK_M - 1) / BLOCK_M;
+    const int nt = (m + tile_rows - 1) / tile_rows;
     scan[threadIdx.x] = nt;
     __syncthreads();
     for (int d = 1; d < 1024; d <<= 1) {
@@ -1109,7 +1120,7 @@ build_group_tiles_kernel(const int32_t* __restrict__ offsets, const int32_t* __r
       const int off = offsets[e];
       for (int t = 0; t < nt; ++t)
         if (first + t < max_tiles)
-          table[first + t] = make_int4(off + t * BLOCK_M, min(BLOCK_M, m - t * BLOCK_M), e, 0);
+          table[first + t] = make_int4(off + t * tile_rows, min(tile_rows, m - t * tile_rows), e, 0);
     }
     base += scan[1023];
     __syncthreads();
@@ -1582,7 +1593,14 @@ static int grouped_entry(const void* A, const void* B, const float* sa, const fl
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   int32_t* count = static_cast<int32_t*>(workspace);
   int4* table = reinterpret_cast<int4*>(static_cast<char*>(workspace) + 16);
-  build_group_tiles_kernel<<<1, 1024, 0, st>>>(expert_offsets, problem_sizes, int(num_experts), table, count, int(max_tiles));
+  // Tile shape.  Prefill-sized expert batches (>= 256 tokens per expert on average, whole 256-column blocks, 16-byte
+  // aligned output rows) take the dense prefill kernel's tiles: 256-row CTA-pair tiles, split-N hand-offs, two staging
+  // boxes per epilogue warp — the finished boxes are read back row-contiguously and stored with the rows cut at the
+  // expert's end.  Everything else: single-CTA 128-row tiles with per-thread predicated stores.
+  const bool pair = (total_m / num_experts >= 256) && N % 256 == 0 && tma_store_ok(Cout, ldc, 2) && num_sms >= 2;
+  const int tile_rows = pair ? 2 * BLOCK_M : BLOCK_M;
+  build_group_tiles_kernel<<<1, 1024, 0, st>>>(expert_offsets, problem_sizes, int(num_experts), table, count, int(max_tiles),
+                                               tile_rows);
 
   GemmParams p;
   memset(&p, 0, sizeof(p));
@@ -1612,6 +1630,22 @@ static int grouped_entry(const void* A, const void* B, const float* sa, const fl
   for (int d = 0; d < kMaxDests; ++d) tc.m[d] = ta;   // unused by the predicated-store epilogue
   int64_t workers = max_tiles * p.num_n_blocks;
   if (workers > num_sms) workers = num_sms;
+  if (pair) {
+    // operand ring as gemm_entry sets it up for variant 29: per CTA 128 rows of A and two 64-row boxes of B per stage
+    p.num_n_blocks = int32_t(N / 256);
+    const uint32_t bb = 128u * BLOCK_K;
+    p.stage_tx_bytes = 2u * (BLOCK_M * BLOCK_K + bb);
+    p.a_slot_bytes = BLOCK_M * BLOCK_K;
+    p.stage_bytes = p.a_slot_bytes + bb;
+    p.num_stages = 5;
+    if (!make_tmap_2d(&tb, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, B, uint64_t(num_experts * N), uint64_t(K), uint64_t(ldb), 64, BLOCK_K))
+      return SGLK_E_DRIVER;
+    int64_t w = max_tiles * p.num_n_blocks;
+    if (w > num_sms / 2) w = num_sms / 2;
+    if (out_dtype == SGLK_BF16)
+      return launch_variant<256, 5, 2, __nv_bfloat16, true, 0, true, true, 0, false, 3>(ta, tb, tc, p, int(w), st);
+    return launch_variant<256, 5, 2, __half, true, 0, true, true, 0, false, 3>(ta, tb, tc, p, int(w), st);
+  }
   if (out_dtype == SGLK_BF16)
     return launch_variant<128, 6, 1, __nv_bfloat16, false, 0, false, true>(ta, tb, tc, p, int(workers), st);
   return launch_variant<128, 6, 1, __half, false, 0, false, true>(ta, tb, tc, p, int(workers), st);

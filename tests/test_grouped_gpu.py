@@ -105,6 +105,28 @@ def test_gaps_between_experts_are_untouched():
         assert torch.isnan(out[off + m:end].float()).all()
 
 
+@pytest.mark.parametrize("m_list,n,k", [([300, 16, 700, 513], 512, 1024), ([257, 255, 256, 1024], 256, 7168),
+                                         ([1000, 0, 40], 768, 512)])
+def test_pair_tiles_for_prefill_sized_experts(m_list, n, k):
+    """>= 256 tokens per expert on average and N % 256 == 0: 256-row CTA-pair tiles whose boxes are stored with the rows
+    cut at the expert's end.  Same bits as the dense op per expert; rows between experts keep their contents."""
+    E = len(m_list)
+    a, bt, sa, sbt, _, _, odt = make_case(E, n, k, [m + 24 for m in m_list], sum(m_list) + k)
+    offs = torch.tensor([sum(m + 24 for m in m_list[:i]) for i in range(E)], dtype=torch.int32)     # 24 unused rows after every expert
+    sizes = torch.tensor([[m, n, k] for m in m_list], dtype=torch.int32)
+    out = run_grouped(a, bt, sa, sbt, offs, sizes, odt)
+    for e, m in enumerate(m_list):
+        off = int(offs[e])
+        assert torch.isnan(out[off + m:off + m + 24].float()).all(), f"rows behind expert {e} were written"
+        if m == 0:
+            continue
+        dense = sgl_kernel._ops._gemm(a[off:off + m].to(DEV), bt[e].to(DEV).t(), sa[off:off + m].to(DEV), sbt[e].to(DEV).t(),
+                                      odt, 29 if m > 128 else 1, 0, False)
+        assert torch.equal(dense.cpu(), out[off:off + m]), f"expert {e}"
+    e0 = O.baseline_scaled_mm(a[:m_list[0]], bt[0].t(), sa[:m_list[0]], sbt[0].t(), odt)
+    check(out[:m_list[0]], e0)
+
+
 def test_errors_and_graph_capture():
     a, bt, sa, sbt, offs, sizes, odt = make_case(4, 256, 512, [32, 64, 16, 48], 9)
     with pytest.raises(RuntimeError, match="workspace too small"):

@@ -52,14 +52,14 @@ def records():
             t = med(lambda: sgl_kernel.fp8_blockwise_scaled_grouped_mm(*args))
             # parity spot check: expert 0 against the dense op
             ref0 = sgl_kernel.fp8_blockwise_scaled_mm(a[:ms[0]], bt[0].t(), sa[:ms[0]], sbt[0].t(), torch.bfloat16)
-            same = bool(torch.equal(o[:ms[0]], ref0))
+            same = float((o[:ms[0]].float() - ref0.float()).norm() / ref0.float().norm()) <= 1e-3   # (summation orders differ)
             td = med(lambda: sgl_kernel.fp8_blockwise_scaled_mm(a, bt[0].t(), sa, sbt[0].t(), torch.bfloat16))
             fl = 2.0 * sum_m * N * K
             by = sum_m * K + E * N * K + 2 * sum_m * N
             out.append({"experts": E, "proj": name, "sum_m": sum_m, "N": N, "K": K, "ms": round(t, 4),
                         "tflops": round(fl / t / 1e9, 1), "GBps": round(by / t / 1e6, 1),
                         "dense_same_flops_ms": round(td, 4), "dense_tflops": round(fl / td / 1e9, 1),
-                        "expert0_equals_dense_op": same})
+                        "expert0_matches_dense_op": same})
             del a, bt, o
     return out
 
