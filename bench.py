@@ -64,8 +64,8 @@ def profile_traffic(kernel, want=None):
 
 # template arguments of fp8_blockwise_gemm_kernel per product variant id (csrc/gemm.cu launch_by_id): what the
 # kernel name in an ncu capture must contain for its traffic to be reported against that variant
-GEMM_TEMPLATE_ARGS = {13: "<256, 6, 2, __nv_bfloat16, 1, 0, 1, 0, 0, 0, 0>", 29: "<256, 5, 2, __nv_bfloat16, 1, 0, 1, 0, 0, 0, 3>",
-                      0: "<128, 6, 1, __nv_bfloat16, 1, 0, 0, 0, 0, 0, 0>"}
+GEMM_TEMPLATE_ARGS = {13: "<256, 6, 2, __nv_bfloat16, 1, 0, 1, 0, 0, 0, 0", 29: "<256, 5, 2, __nv_bfloat16, 1, 0, 1, 0, 0, 0, 3",
+                      0: "<128, 6, 1, __nv_bfloat16, 1, 0, 0, 0, 0, 0, 0"}   # (prefixes: later template parameters have defaults)
 FP8_NOMINAL_TFLOPS = 4500.0
 HBM_NOMINAL_GBS = 8000.0
 

@@ -13,9 +13,10 @@ $CMD > gpurun_out/plain_bench3.log 2>&1 && \
 ncu --set full --clock-control none --import-source on -k regex:ptgq_kernel -s 3 -c 1 -o gpurun_out/quant_$R $CMD > gpurun_out/ncu_quant.log 2>&1
 tail -2 gpurun_out/ncu_quant.log
 ls -la gpurun_out | grep $R
-# decode shapes (weight streaming): one full capture each of the swap-AB kernel the default dispatch picks at M=16 —
-# CTA pairs, whole tiles at N=24576; single CTAs, 4 workers per tile at N=2112 — and of the 128-row tile kernel at M=64
-for T in "decode 16 24576" "decoden 16 2112" "decode64 64 24576"; do
+# decode shapes (weight streaming): one full capture each of the row-balanced swap-AB kernel the default dispatch picks —
+# N=24576 at 16 and 64 tokens (one 168-row range per CTA), N=2112 at 16 tokens (clusters of 4 over K) — and of the 128-row
+# tile kernel at M=128
+for T in "decode 16 24576" "decoden 16 2112" "decode64 64 24576" "decode128 128 24576"; do
   set -- $T
   DCMD="python tools/ncu_target.py gemm $2 $3 7168"
   $DCMD > gpurun_out/plain_$1.log 2>&1 && \

@@ -84,5 +84,6 @@ dump_kernel("quant")
 dump_kernel("decode")
 dump_kernel("decoden")
 dump_kernel("decode64")
+dump_kernel("decode128")
 dump_kernel("tokenquant")
 print(sorted(os.listdir(P)))
