@@ -25,3 +25,8 @@ for T in "decode 16 24576" "decoden 16 2112" "decode64 64 24576" "decode128 128 
 done
 ls -la gpurun_out | grep $R
 # (per-token quant kernel unchanged since r01d: profiles/r01d_tokenquant_*)
+# the reports together exceed what gpurun copies back (64 MiB): summarise here, ship the summaries, drop the reports
+python tools/summarize_profiles.py $R > gpurun_out/summarize_$R.log 2>&1
+mkdir -p gpurun_out/prof_$R && cp profiles/${R}_* gpurun_out/prof_$R/
+rm -f gpurun_out/*_$R.ncu-rep
+ls gpurun_out/prof_$R
