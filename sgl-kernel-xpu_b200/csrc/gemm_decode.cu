@@ -1069,11 +1069,32 @@ fp8_blockwise_gemm_rows_kernel(const __grid_constant__ CUtensorMap tmap_w0, cons
           asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
           release_slot();
 #pragma unroll
-          for (int i = 0; i < ITEMS; ++i) {
-            if (i / (S * IPB) < nb) {
+          for (int i = 0; i < ITEMS; ++i)
 #pragma unroll
-              for (int r = 0; r < IW; ++r) asm volatile("" : "+r"(v[i][r]));   // consumers stay below the wait
-              item_fma(i, v[i]);
+            for (int r = 0; r < IW; ++r) asm volatile("" : "+r"(v[i][r]));     // consumers stay below the wait
+          // per (K block, column chunk): the activation factors are read from smem ONCE and applied to both sub-tiles
+#pragma unroll
+          for (int j = 0; j < G; ++j) {
+            if (j < nb) {
+              const uint32_t kslot = fslot + uint32_t(j) * C::KB_SCALE_BYTES;
+              float sbv[S];
+#pragma unroll
+              for (int s = 0; s < S; ++s) sbv[s] = ptx::lds_f32(kslot + sb_off[s]);
+#pragma unroll
+              for (int c = 0; c < IPB; ++c) {
+                const uint32_t fac = kslot + 4u * uint32_t(t0 + c * IW);
+#pragma unroll
+                for (int q = 0; q < IW / 4; ++q) {
+                  const float4 f = dptx::lds_f32x4(fac + 16u * q);
+#pragma unroll
+                  for (int s = 0; s < S; ++s) {
+                    const uint32_t* buf = v[(j * S + s) * IPB + c];
+                    float* a = &accum[s][c * IW + 4 * q];
+                    dptx::fma2_scaled(a[0], a[1], buf[4 * q], buf[4 * q + 1], f.x, f.y, sbv[s]);
+                    dptx::fma2_scaled(a[2], a[3], buf[4 * q + 2], buf[4 * q + 3], f.z, f.w, sbv[s]);
+                  }
+                }
+              }
             }
           }
         } else {
