@@ -172,7 +172,8 @@ enum {
   SGLK_GEMM_STREAMK_FORCE = 1,  /* cut whenever the shape allows it (tests exercise the fix-up on small shapes)      */
   SGLK_GEMM_STREAMK_NEVER = 2,  /* whole tiles only                                                                 */
   SGLK_GEMM_GROUP_M_SHIFT = 8,  /* bits 8..15: m-blocks per rasterisation group of the prefill kernel, 0 = built-in */
-  SGLK_GEMM_SPLIT_SHIFT = 16,   /* bits 16..23: decode kernel, workers per tile when there are fewer tiles than SMs, 0 = built-in */
+  SGLK_GEMM_SPLIT_SHIFT = 16,   /* bits 16..23: decode kernels, how K is split when there are fewer tiles than SMs — workers per tile
+                                   (swap-AB tile kernels) / CTAs per cluster, 1, 2 or 4 (row-balanced kernel); 0 = built-in */
   SGLK_GEMM_DECODE_2D_LOADS = 1 << 24   /* row-balanced decode kernel: one TMA load per K block even where one per stage would do (A/B hook) */
 };
 

@@ -1,4 +1,8 @@
-// Decode-shaped fp8 blockwise-scaled GEMM for sm_100a (M <= 256 tokens): the "swap-AB" kernel.
+// Decode-shaped fp8 blockwise-scaled GEMMs for sm_100a (M <= 256 tokens): two "swap-AB" kernels.
+//   1. fp8_blockwise_gemm_decode_kernel (first half of this file): 128 / 256-row weight TILES, stream-K hybrid schedule with a
+//      workspace fix-up — variants swapab_cta1 / swapab_cta2, the default of early round 2, kept as explicit variants;
+//   2. fp8_blockwise_gemm_rows_kernel (second half): one contiguous weight-ROW RANGE per CTA for all of K (or per cluster
+//      for a K range), no workspace, no atomics — variant swapab_rows, the default up to 64 tokens (gemm.cu pick_variant).
 //
 //   C[m, n] = sum_kb sa[m, kb] * sb[kb, n / 128] * sum_{k in kb} A[m, k] * B[k, n]
 //
