@@ -1173,8 +1173,11 @@ static const Variant kVariants[] = {
     {"swapab_cta1", 128, 0, 1, false, false, true},                  // decode (gemm_decode.cu): weights are the MMA M side
     {"swapab_cta2", 128, 0, 2, false, false, true},                  // decode, CTA pair: 256 weight rows, tokens split over the pair
     {"swapab_rows", 128, 0, 1, false, false, true},                  // decode, row-balanced: one contiguous weight-row range per CTA, no split-K
+    {"lab_rows_tokmajor", 128, 0, 1, false, false, false},           // laboratory: row-balanced with the tokens on the MMA M side (gemm_trows.cu);
+                                                                     // correct, but epilogue-bound with two 256-column TMEM stages: 58 us against the
+                                                                     // tile kernel's 41 at 128 x 24576 x 7168
 };
-constexpr int kDecodeVariant1 = 30, kDecodeVariant2 = 31, kRowsVariant = 32;
+constexpr int kDecodeVariant1 = 30, kDecodeVariant2 = 31, kRowsVariant = 32, kTRowsVariant = 33;
 constexpr int kRowsMaxTokens = 64;     // the default dispatch uses the row-balanced swap-AB kernel up to here (pick_variant)
 constexpr int kFirstStampVariant = 15, kLastStampVariant = 22;
 constexpr int kNumVariants = int(sizeof(kVariants) / sizeof(kVariants[0]));
@@ -1430,6 +1433,12 @@ static int gemm_entry(const void* A, const void* B, const float* sa, const float
   }
   if (variant < 0) variant = pick_variant(M, N, K, plain_output, num_sms);
   if (!variant_available(variant)) return SGLK_E_VARIANT;
+#ifdef SGLK_DIAG
+  if (variant == kTRowsVariant) {
+    if (!plain_output || !trows_supported(M, N, K)) return SGLK_E_VARIANT;
+    return trows_entry(A, B, sa, sb, Cout, M, N, K, lda, ldb, ldc, sa_sm, sa_sk, sb_sk, sb_sn, out_dtype, num_sms, st);
+  }
+#endif
   if (variant == kRowsVariant) {
     if (!plain_output || !rows_supported(M, N, K)) return SGLK_E_VARIANT;
     return rows_entry(A, B, sa, sb, Cout, M, N, K, lda, ldb, ldc, sa_sm, sa_sk, sb_sk, sb_sn, out_dtype, num_sms, flags, st);
@@ -1743,7 +1752,7 @@ extern "C" int64_t sglk_gemm_workspace_bytes(int64_t M, int64_t N, int64_t K, in
   if (variant < 0) variant = sglk::pick_variant(M, N, K, true, num_sms);
   if (!sglk::variant_available(variant)) return 0;
   if (num_sms <= 0) num_sms = sglk::device_sm_count();
-  if (variant == sglk::kRowsVariant) return 0;   // no split-K, no workspace
+  if (variant == sglk::kRowsVariant || variant == sglk::kTRowsVariant) return 0;   // no split-K through global memory, no workspace
   if (variant == sglk::kDecodeVariant1 || variant == sglk::kDecodeVariant2)
     return sglk::decode_workspace_bytes(M, N, K, variant == sglk::kDecodeVariant2 ? 2 : 1, num_sms, flags);
   const sglk::Plan pl = sglk::make_plan(M, N, K, variant, num_sms, true, flags);

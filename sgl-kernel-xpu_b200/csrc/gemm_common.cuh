@@ -130,5 +130,10 @@ int rows_entry(const void* A, const void* B, const float* sa, const float* sb, v
                int64_t lda, int64_t ldb, int64_t ldc, int64_t sa_sm, int64_t sa_sk, int64_t sb_sk, int64_t sb_sn,
                int out_dtype, int num_sms, int flags, cudaStream_t st);
 bool rows_supported(int64_t M, int64_t N, int64_t K);
+// row-balanced token-major kernel (gemm_trows.cu): the same split with the tokens on the MMA's M side, for 65..128 tokens
+int trows_entry(const void* A, const void* B, const float* sa, const float* sb, void* Cout, int64_t M, int64_t N, int64_t K,
+                int64_t lda, int64_t ldb, int64_t ldc, int64_t sa_sm, int64_t sa_sk, int64_t sb_sk, int64_t sb_sn,
+                int out_dtype, int num_sms, cudaStream_t st);
+bool trows_supported(int64_t M, int64_t N, int64_t K);
 
 }  // namespace sglk
