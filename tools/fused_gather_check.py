@@ -45,6 +45,6 @@ if rank == 0:
     print(json.dumps({"world": world, "M": M, "N": N, "K": K, "bitwise_equal_to_nccl_path": same, "ms_fused": t_fused, "ms_fused_multicast": t_mc, "multicast_bitwise_equal": same_mc,
                       "ms_nccl_gather": t_nccl, "ms_no_gather": t_local,
                       "tflops_fused": 2.0 * M * N * K / t_fused / 1e9, "tflops_nccl": 2.0 * M * N * K / t_nccl / 1e9}))
-all_same = torch.tensor([int(same)], device=dev); dist.all_reduce(all_same, op=dist.ReduceOp.MIN)
+all_same = torch.tensor([int(same and same_mc)], device=dev); dist.all_reduce(all_same, op=dist.ReduceOp.MIN)
 dist.destroy_process_group()
 sys.exit(0 if int(all_same.item()) == 1 else 1)
