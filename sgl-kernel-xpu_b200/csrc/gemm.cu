@@ -1302,9 +1302,21 @@ static int pick_variant(int64_t M, int64_t N, int64_t K, bool plain_output, int 
   //           tiles   -     16.1      -     19.0    20.6
   // Beyond 64 tokens every CTA re-reading its K range of the activations from L2 costs more than the balance gains.
   if (plain_output && M <= kRowsMaxTokens && rows_supported(M, N, K)) return kRowsVariant;
+  // 65..256 tokens are still weight streams; what matters is how the tile count fits the SMs (tools/decode_ab.py, K=7168,
+  // GPU-side in a CUDA graph, us):
+  //   M=128: N=24576: 128x256 single-CTA split-N tiles (14) 36.1 — 96 tiles, ONE wave — against 40.9 for 128x128 tiles
+  //          (0: 192 tiles, stream-K) and 48.4 for pair tiles (29); N=7168: 0 19.4-20.7, 14 22.5-24.6 (28 tiles only)
+  //   M=256: N=7168: 256x128 pair tiles (5) 19.8 — 56 tiles, one wave — against 27.5 (29) and 21.2 (0);
+  //          N=24576: 29 52.5, 5 55.7, 0 71.2; N=2112: 0 16.4, 5 16.5, 29 22.2
+  const int64_t sms = num_sms > 0 ? num_sms : 148;
+  if (plain_output && M > kRowsMaxTokens && M <= 128) {
+    const int64_t t256 = (N + 255) / 256;
+    if (t256 <= sms && 5 * t256 >= 3 * sms) return 14;      // one wave of 256-wide tiles that fills >= 60 % of the SMs
+  }
   // a handful of wide tiles on a narrow weight (N=2112, 129 <= M <= 256: 9 pair tiles for 74 pairs): 128-wide single-CTA
   // tiles give stream-K twice the units to balance
   if (M > 128 && M <= 256 && N < 4096) return 0;
+  if (plain_output && M > 128 && M <= 256 && (N + 127) / 128 <= sms / 2) return 5;   // one wave of 256x128 pair tiles
   // paired 256x256 tiles (one pair covers 256 rows), each K block issued as two 128-column MMA halves with their own
   // hand-off barriers: a half's stage has three half-MMAs (768 clk) of slack before it is needed again instead of one
   // whole MMA (512) — +5-10 % over the unsplit pair tile at every prefill shape measured

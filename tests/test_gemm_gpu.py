@@ -403,9 +403,10 @@ def test_decode_is_the_default_for_small_m():
     for N in (2112, 4096, 7168, 24576, 129280):
         for M in (1, 8, 16, 17, 32, 64):
             assert lib.sglk_gemm_pick_variant(M, N, 7168) == 32
-        for M in (65, 128):
-            assert lib.sglk_gemm_pick_variant(M, N, 7168) == 0
+        for M in (65, 128):      # one wave of 256-wide single-CTA tiles where that fills the SMs, else 128-wide + stream-K
+            assert lib.sglk_gemm_pick_variant(M, N, 7168) == (14 if N == 24576 else 0)
     assert lib.sglk_gemm_pick_variant(256, 2112, 7168) == 0
+    assert lib.sglk_gemm_pick_variant(256, 7168, 7168) == 5          # one wave of 256x128 pair tiles
     assert lib.sglk_gemm_pick_variant(256, 24576, 7168) == 29
     assert lib.sglk_gemm_pick_variant(257, 24576, 7168) == 29
     assert lib.sglk_gemm_pick_variant(16384, 18432, 7168) == 29
