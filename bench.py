@@ -636,7 +636,7 @@ def main():
     # over the same K steps above): activations quantised on every rank, or row-sharded and exchanged over NVLink under the
     # GEMM.  `value` is the faster one where the sharded form wins by more than 2 % (4 GPUs on this hardware); both are
     # reported.  gemm_ms / quant_ms / the rooflines always describe the replicated form's kernels.
-    value_form = "activations quantised on every rank (no collective)"
+    value_form = "activations quantised on every rank (no collective)" if world > 1 else "single GPU: quant + GEMM"
     replicated = {"value": value, "ms_per_step": t_step}
     if (sharded_quant and sharded_quant.get("matches_replicated") and
             sharded_quant.get("ms_per_step", 1e30) < 0.98 * t_step):
