@@ -265,8 +265,16 @@ fp8_blockwise_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gr
   // m-blocks of 128*kCG rows; grouped: the m-tile table was built on the device from the expert offsets
   const int num_m_tiles = kGrouped ? __ldg(p.grp_num_m_tiles) : p.num_m_blocks;
   const int num_tiles = num_m_tiles * p.num_n_blocks;
-  // grouped: tile -> (m-tile, n-block) with the m-tile fastest, so CTAs running together share an expert's B panel
-  auto grouped_tile = [&](int tile, int& nb) { nb = tile / num_m_tiles; return __ldg(p.grp_tiles + (tile - nb * num_m_tiles)); };
+  // grouped: tile -> (m-tile, n-block).  p.group_m == 0: the n-block fastest — the CTAs running together work on a few
+  // m-tiles (a few experts): an m-tile's A panel is read once, and an expert's B panel is still in L2 when its next m-tile
+  // comes by.  Otherwise (p.group_m != 0) the m-tile fastest: every wave touches every m-tile, and with more activations
+  // than L2 holds they are re-read from HBM once per n-block.
+  auto grouped_tile = [&](int tile, int& nb) {
+    int mt;
+    if (p.group_m == 0) { mt = tile / p.num_n_blocks; nb = tile - mt * p.num_n_blocks; }
+    else { nb = tile / num_m_tiles; mt = tile - nb * num_m_tiles; }
+    return __ldg(p.grp_tiles + mt);
+  };
   (void)grouped_tile;
   const int num_workers = gridDim.x / kCl;
   const int worker = blockIdx.x / kCl;
@@ -1632,7 +1640,7 @@ static int grouped_entry(const void* A, const void* B, const float* sa, const fl
   p.num_n_blocks = int32_t((N + 127) / 128);
   p.num_k_blocks = int32_t((K + BLOCK_K - 1) / BLOCK_K);
   p.num_sb_cols = int32_t((N + 127) / 128);
-  p.group_m = 8;
+  p.group_m = 0;     // grouped mode: tile order switch (see grouped_tile in the kernel): n-block fastest
   p.num_dests = 1;
   p.grp_tiles = table; p.grp_num_m_tiles = count; p.grp_sb_expert_stride = sb_se;
   const uint32_t b_bytes = 128u * BLOCK_K;
