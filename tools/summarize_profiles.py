@@ -85,5 +85,7 @@ dump_kernel("decode")
 dump_kernel("decoden")
 dump_kernel("decode64")
 dump_kernel("decode128")
+dump_kernel("grouped")
+dump_kernel("gated")
 dump_kernel("tokenquant")
 print(sorted(os.listdir(P)))
