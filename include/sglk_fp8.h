@@ -67,7 +67,8 @@ enum {
   SGLK_E_LAYOUT = -6,      /* unknown scale layout                           */
   SGLK_E_ARG = -7,         /* other invalid argument                         */
   SGLK_E_DRIVER = -8,      /* cuTensorMapEncodeTiled unavailable / failed    */
-  SGLK_E_VARIANT = -9      /* unknown kernel variant                         */
+  SGLK_E_VARIANT = -9,     /* unknown kernel variant                         */
+  SGLK_E_CAPACITY = -10    /* problem larger than a fixed built-in buffer    */
 };
 
 SGLK_API int sglk_abi_version(void);
@@ -307,6 +308,45 @@ SGLK_API int sglk_fp8_blockwise_scaled_grouped_mm(const void* A, const void* B, 
                                          int64_t sb_stride_e, int64_t sb_stride_k, int64_t sb_stride_n, int out_dtype,
                                          int num_sms, void* workspace, int64_t workspace_bytes, void* stream);
 SGLK_API int64_t sglk_grouped_mm_workspace_bytes(int64_t num_experts, int64_t total_m);
+
+/*
+ * The grouped GEMM above for callers that have no way to give it a workspace.  No counterpart in the reference (this is
+ * an addition of this library, not a replacement for anything there).
+ *
+ * Who needs it: hosts that may not create device memory at the point of the call — a plugin that runs inside someone
+ * else's memory pool and is forbidden to call cudaMalloc, a serving loop that has handed all of HBM to its KV cache and
+ * must not fragment it, a thin FFI binding (cgo / JNI / ctypes) that receives input and output pointers from its
+ * runtime but owns no allocator of its own.  The caller passes exactly the inputs and the output; the m-tile table the
+ * kernel needs is built in an array that is part of the library image (SGLK_GROUPED_STATIC_SCRATCH_BYTES, on every GPU
+ * that loads the library, from load until the process exits).  The function and everything under it call no cudaMalloc,
+ * cudaFree or other allocating routine.
+ *
+ * Limit: ceil(total_m / 128) + num_experts <= sglk_grouped_mm_static_max_tiles() (4095 with the 64 KiB array: e.g. 256
+ * experts and up to 491 392 stacked rows).  Anything larger is refused with SGLK_E_CAPACITY before any launch — use the
+ * workspace form for it.
+ *
+ * First call on each device: the library asks the CUDA runtime where that device's copy of the array lives (once per
+ * device, with that device current, i.e. the device of `stream`).  Make that first call outside any stream capture;
+ * every later call on the device only reads the remembered address.
+ *
+ * Sharing: all calls on a device use the SAME array, and it keeps what the last call wrote.  Nothing in it has to be
+ * zero on entry — each call rebuilds the tile count and every table entry it reads, in stream order, before its GEMM
+ * kernel starts — so back-to-back calls on one stream are fine.  Two calls that can run on the GPU at the same time
+ * (different streams without an event between them, or several host threads each on their own stream) would overwrite
+ * each other's table: that is a race the library does not guard against.  Serialise such calls, or use the workspace
+ * form with one workspace per stream.
+ *
+ * Arguments and result bits are those of sglk_fp8_blockwise_scaled_grouped_mm (same kernels, same tile order).
+ */
+#define SGLK_GROUPED_STATIC_SCRATCH_BYTES 65536
+SGLK_API int sglk_fp8_blockwise_scaled_grouped_mm_static(const void* A, const void* B, const float* sa, const float* sb,
+                                                void* C, const int32_t* expert_offsets, const int32_t* problem_sizes,
+                                                int64_t num_experts, int64_t total_m, int64_t N, int64_t K, int64_t lda,
+                                                int64_t ldb, int64_t ldc, int64_t sa_stride_m, int64_t sa_stride_k,
+                                                int64_t sb_stride_e, int64_t sb_stride_k, int64_t sb_stride_n,
+                                                int out_dtype, int num_sms, void* stream);
+/* largest ceil(total_m / 128) + num_experts the call above accepts */
+SGLK_API int64_t sglk_grouped_mm_static_max_tiles(void);
 
 /* bytes of workspace the call above can make use of (0: none): [1 MiB tile counters][stream-K partials, if the
  * scheduler would cut tiles][K-block-contiguous copies of sa / sb, for prefill-sized problems whose scales are not

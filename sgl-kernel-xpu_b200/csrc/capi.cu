@@ -18,6 +18,7 @@ extern "C" const char* sglk_error_string(int code) {
     case SGLK_E_ARG: return "invalid argument";
     case SGLK_E_DRIVER: return "cuTensorMapEncodeTiled unavailable or failed (needs an sm_100 CUDA driver)";
     case SGLK_E_VARIANT: return "unknown GEMM kernel variant";
+    case SGLK_E_CAPACITY: return "problem exceeds the fixed capacity of the library's built-in scratch array (use the entry point that takes a workspace)";
     default: break;
   }
   if (code > 0) return cudaGetErrorString(static_cast<cudaError_t>(code));

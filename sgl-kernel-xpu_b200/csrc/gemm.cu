@@ -1701,6 +1701,70 @@ extern "C" int64_t sglk_grouped_mm_workspace_bytes(int64_t num_experts, int64_t 
   return 16 + ((total_m + sglk::BLOCK_M - 1) / sglk::BLOCK_M + num_experts) * 16;
 }
 
+// --------------------------------------------------------------------------------------------
+// Grouped GEMM for hosts that cannot allocate device memory (see include/sglk_fp8.h).
+// The m-tile table of the grouped kernel normally lives in a caller-supplied workspace.  Here it lives in a fixed array
+// that is part of the library image: every GPU that loads libsglk holds SGLK_GROUPED_STATIC_SCRATCH_BYTES of it until
+// the process exits.  In HOST code the identifier below is only a handle for the runtime's symbol table — it is not a
+// device address and must never be handed to a kernel; the address the GPU sees is asked for once per device with
+// cudaGetSymbolAddress (each device has its own copy of the array at its own address).
+// --------------------------------------------------------------------------------------------
+namespace sglk {
+
+static __device__ __align__(256) unsigned char g_grouped_static_scratch[SGLK_GROUPED_STATIC_SCRATCH_BYTES];
+
+constexpr int kMaxStaticScratchDevices = 64;
+
+// Device address of the CURRENT device's copy of the array.  The first call on a device asks the runtime (which may load
+// the module there — do it outside stream capture); later calls read the cached pointer.  No allocation anywhere.
+static int grouped_static_scratch(void** out) {
+  static std::mutex mu;
+  static void* addr[kMaxStaticScratchDevices] = {};
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return int(e);
+  if (dev < 0 || dev >= kMaxStaticScratchDevices) return SGLK_E_ARG;
+  std::lock_guard<std::mutex> lock(mu);
+  if (!addr[dev]) {
+    void* p = nullptr;
+    e = cudaGetSymbolAddress(&p, g_grouped_static_scratch);
+    if (e != cudaSuccess) return int(e);
+    if (!p) return int(cudaErrorInvalidSymbol);
+    addr[dev] = p;
+  }
+  *out = addr[dev];
+  return SGLK_OK;
+}
+
+}  // namespace sglk
+
+extern "C" int64_t sglk_grouped_mm_static_max_tiles(void) {
+  return (int64_t(SGLK_GROUPED_STATIC_SCRATCH_BYTES) - 16) / 16;
+}
+
+extern "C" int sglk_fp8_blockwise_scaled_grouped_mm_static(const void* A, const void* B, const float* sa, const float* sb,
+                                                           void* C, const int32_t* expert_offsets,
+                                                           const int32_t* problem_sizes, int64_t num_experts,
+                                                           int64_t total_m, int64_t N, int64_t K, int64_t lda, int64_t ldb,
+                                                           int64_t ldc, int64_t sa_stride_m, int64_t sa_stride_k,
+                                                           int64_t sb_stride_e, int64_t sb_stride_k, int64_t sb_stride_n,
+                                                           int out_dtype, int num_sms, void* stream) {
+  // capacity first, so an oversized problem is refused whether or not a GPU is present
+  if (num_experts > 0 && total_m > 0 &&
+      sglk_grouped_mm_workspace_bytes(num_experts, total_m) > int64_t(SGLK_GROUPED_STATIC_SCRATCH_BYTES))
+    return SGLK_E_CAPACITY;
+  void* scratch = nullptr;
+  if (num_experts > 0 && total_m > 0 && N > 0) {   // empty problems launch nothing and need no scratch
+    const int rc = sglk::grouped_static_scratch(&scratch);
+    if (rc != SGLK_OK) return rc;
+  }
+  // Nothing in the array has to start at zero: the table-building kernel rewrites the tile count and every entry the
+  // GEMM will read, on `stream`, before the GEMM runs.  What the previous call left behind is simply overwritten.
+  return sglk::grouped_entry(A, B, sa, sb, C, expert_offsets, problem_sizes, num_experts, total_m, N, K, lda, ldb, ldc,
+                             sa_stride_m, sa_stride_k, sb_stride_e, sb_stride_k, sb_stride_n, out_dtype, num_sms,
+                             scratch, SGLK_GROUPED_STATIC_SCRATCH_BYTES, stream);
+}
+
 extern "C" int sglk_fp8_blockwise_scaled_mm_ex(const void* A, const void* B, const float* sa, const float* sb, void* C,
                                                int64_t M, int64_t N, int64_t K, int64_t lda, int64_t ldb, int64_t ldc,
                                                int64_t sa_stride_m, int64_t sa_stride_k, int64_t sb_stride_k,

@@ -42,6 +42,9 @@ SYMBOLS = {
     "sglk_fp8_blockwise_scaled_grouped_mm": (
         _i32, [_vp, _vp, _vp, _vp, _vp, _vp, _vp] + [_i64] * 12 + [_i32, _i32, _vp, _i64, _vp]),
     "sglk_grouped_mm_workspace_bytes": (_i64, [_i64, _i64]),
+    "sglk_fp8_blockwise_scaled_grouped_mm_static": (
+        _i32, [_vp, _vp, _vp, _vp, _vp, _vp, _vp] + [_i64] * 12 + [_i32, _i32, _vp]),
+    "sglk_grouped_mm_static_max_tiles": (_i64, []),
     "sglk_gemm_workspace_bytes": (_i64, [_i64, _i64, _i64, _i32, _i32, _i32]),
     "sglk_fp8_blockwise_scaled_mm_allgather": (
         _i32, [_vp, _vp, _vp, _vp, _vp, ctypes.POINTER(_vp), _i32, _vp] + [_i64] * 10 + [_i32, _i32, _i32, _vp, _i64, _vp]),
