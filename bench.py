@@ -504,6 +504,7 @@ def main():
         try:
             if sharded.sharded_quant_supported(M):
                 sharded.enable_sharded_quant(M)
+                sharded.gated_wait_polls = 16_000_000   # a rank that never delivers fails the bench after ~20-30 s instead of hanging the box
                 ref_panel = step()
                 ok_sq = True
                 for _ in range(3):

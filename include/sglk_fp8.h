@@ -30,7 +30,7 @@
 extern "C" {
 #endif
 
-#define SGLK_ABI_VERSION 2
+#define SGLK_ABI_VERSION 3
 
 #if defined(__GNUC__)
 #define SGLK_API __attribute__((visibility("default")))
@@ -271,14 +271,20 @@ SGLK_API int sglk_per_token_group_quant_fp8_bcast(const void* input, void* outpu
  * ring schedule, one sender per receiver at a time) the panels of ranks rank+1, rank+2, ... one after the other.
  * Same result bits as sglk_fp8_blockwise_scaled_mm on the completed buffers.
  * Requirements: M % (256 * panel_world) == 0, N >= 256, K-block-contiguous scales (sa_stride_k == sb_stride_k == 1,
- * 16-byte aligned rows), C 16-byte aligned rows.  A counter that never arrives traps the kernel after ~4 s.
+ * 16-byte aligned rows), C 16-byte aligned rows.
+ * wait_polls bounds how long a CTA waits for a counter: 0 = for ever (what a collective normally wants: a peer held up by
+ * a module load, a host pause or an allocator call is merely late, and the launch finishes when it delivers — a peer
+ * that is really gone has to be dealt with by the host's watchdog, as with NCCL); n > 0 = after n polling rounds (about
+ * 1-2 us each: 4 000 000 is a few seconds) the CTA executes a trap, which fails the launch with a STICKY error — the
+ * CUDA context of this process is unusable afterwards and has to be torn down.  Use a bound only where a dead context
+ * is preferable to a hang (tests, CI boxes with a wall-clock limit).
  */
 SGLK_API int sglk_fp8_blockwise_scaled_mm_gated(const void* A, const void* B, const float* sa, const float* sb, void* C,
                                        int64_t M, int64_t N, int64_t K, int64_t lda, int64_t ldb, int64_t ldc,
                                        int64_t sa_stride_m, int64_t sa_stride_k, int64_t sb_stride_k,
                                        int64_t sb_stride_n, int out_dtype, int num_sms,
                                        const uint32_t* row_ready_counters, uint32_t ready_target, int panel_rank,
-                                       int panel_world, int whole_panels, void* stream);
+                                       int panel_world, int whole_panels, int64_t wait_polls, void* stream);
 
 /* Host-side copy of the gated kernel's walk, for tests and schedulers: out[2t] / out[2t+1] = the 256-row m-block and the
  * 256-column n-block of the t-th tile in launch order (tile t goes to CTA pair t mod #pairs).  Returns the number of

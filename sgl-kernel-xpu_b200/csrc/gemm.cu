@@ -77,6 +77,7 @@ struct GemmParams {
   // order in which the panels, all sent at once, fill up.
   const uint32_t* a_ready;
   uint32_t a_ready_target;
+  uint32_t a_wait_polls;          // poll rounds before a waiting CTA gives up with __trap(); 0 = wait for ever
   int32_t panel_own;              // m-blocks per rank panel
   int32_t panel_rank, panel_world;
   int32_t panel_group;            // remote m-blocks per rasterisation group (a whole number of slices)
@@ -325,14 +326,14 @@ fp8_blockwise_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gr
                 seen = uint64_t(w0) | (uint64_t(w1) << 32);
                 asm volatile("fence.proxy.async;" ::: "memory");
                 if (ptx::elect_one()) asm volatile("st.release.cta.shared.u64 [%0], %1;" ::"r"(ready_word), "l"(seen) : "memory");
-                if (spins > 4000000u) __trap();            // a peer that never delivers: give up after a few seconds
+                if (p.a_wait_polls != 0u && spins > p.a_wait_polls) __trap();   // caller-set bound on waiting for a peer (0: none)
               }
             } else {                                       // more than 64 m-blocks: this tile's own counter, every tile
               const uint32_t* cp = p.a_ready + mb;
               uint32_t v, spins = 0;
               do {
                 asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(cp) : "memory");
-                if (++spins > 4000000u) __trap();
+                if (++spins > p.a_wait_polls && p.a_wait_polls != 0u) __trap();
               } while (__any_sync(0xFFFFFFFFu, int32_t(v - p.a_ready_target) < 0));
               asm volatile("fence.proxy.async;" ::: "memory");
             }
@@ -1318,7 +1319,7 @@ static int pick_variant(int64_t M, int64_t N, int64_t K, bool plain_output, int 
   //          (0: 192 tiles, stream-K) and 48.4 for pair tiles (29); N=7168: 0 19.4-20.7, 14 22.5-24.6 (28 tiles only)
   //   M=256: N=7168: 256x128 pair tiles (5) 19.8 — 56 tiles, one wave — against 27.5 (29) and 21.2 (0);
   //          N=24576: 29 52.5, 5 55.7, 0 71.2; N=2112: 0 16.4, 5 16.5, 29 22.2
-  const int64_t sms = num_sms > 0 ? num_sms : 148;
+  const int64_t sms = num_sms > 0 ? num_sms : device_sm_count();   // the current device's count (148 on B200; also the answer without a device)
   if (plain_output && M > kRowsMaxTokens && M <= 128) {
     const int64_t t256 = (N + 255) / 256;
     if (t256 <= sms && 5 * t256 >= 3 * sms) return 14;      // one wave of 256-wide tiles that fills >= 60 % of the SMs
@@ -1415,6 +1416,7 @@ struct GateIn {
   uint32_t target;
   int rank, world;
   int whole_panels;   // arrival order of the other ranks' panels: 0 = all at once, slice by slice; 1 = one panel after the other
+  uint32_t wait_polls; // see GemmParams::a_wait_polls
 };
 
 static int gemm_entry(const void* A, const void* B, const float* sa, const float* sb, void* Cout, int64_t M,
@@ -1453,7 +1455,8 @@ static int gemm_entry(const void* A, const void* B, const float* sa, const float
     variant = 29;
     flags = (flags & ~3) | SGLK_GEMM_STREAMK_NEVER;
   }
-  if (variant < 0) variant = pick_variant(M, N, K, plain_output, num_sms);
+  const bool picked = variant < 0;
+  if (picked) variant = pick_variant(M, N, K, plain_output, num_sms);
   if (!variant_available(variant)) return SGLK_E_VARIANT;
 #ifdef SGLK_DIAG
   if (variant == kTRowsVariant) {
@@ -1463,7 +1466,13 @@ static int gemm_entry(const void* A, const void* B, const float* sa, const float
 #endif
   if (variant == kRowsVariant) {
     if (!plain_output || !rows_supported(M, N, K)) return SGLK_E_VARIANT;
-    return rows_entry(A, B, sa, sb, Cout, M, N, K, lda, ldb, ldc, sa_sm, sa_sk, sb_sk, sb_sn, out_dtype, num_sms, flags, st);
+    const int rc = rows_entry(A, B, sa, sb, Cout, M, N, K, lda, ldb, ldc, sa_sm, sa_sk, sb_sk, sb_sn, out_dtype, num_sms, flags, st);
+    // A kernel the HEURISTIC chose must not surface its own planning limits to the user: if the row-balanced kernel
+    // cannot be planned for this problem (no ring that fits, no launch configuration, tensor map refused — all found
+    // before anything is launched), the general 128x128 tile kernel below takes it.  An explicitly requested variant
+    // still reports the error.
+    if (!picked || (rc != SGLK_E_SHAPE && rc != SGLK_E_VARIANT && rc != SGLK_E_DRIVER)) return rc;
+    variant = 0;
   }
   if (variant == kDecodeVariant1 || variant == kDecodeVariant2) {
     if (!plain_output || !decode_supported(M, N, K)) return SGLK_E_VARIANT;
@@ -1595,6 +1604,7 @@ static int gemm_entry(const void* A, const void* B, const float* sa, const float
     if (!p.scale_vec) return SGLK_E_STRIDE;
     p.a_ready = gate->counters;
     p.a_ready_target = gate->target;
+    p.a_wait_polls = gate->wait_polls;
     set_panel_walk(p, gate->rank, gate->world, gate->whole_panels);
     if (out_dtype == SGLK_BF16)
       return launch_variant<256, 5, 2, __nv_bfloat16, true, 0, true, false, 0, false, 3, true>(ta, tb, tc, p, pl.workers, st);
@@ -1804,8 +1814,11 @@ extern "C" int sglk_fp8_blockwise_scaled_mm_gated(const void* A, const void* B, 
                                                   int64_t sa_stride_m, int64_t sa_stride_k, int64_t sb_stride_k,
                                                   int64_t sb_stride_n, int out_dtype, int num_sms,
                                                   const uint32_t* row_ready_counters, uint32_t ready_target,
-                                                  int panel_rank, int panel_world, int whole_panels, void* stream) {
-  const sglk::GateIn gate{row_ready_counters, ready_target, panel_rank, panel_world, whole_panels};
+                                                  int panel_rank, int panel_world, int whole_panels, int64_t wait_polls,
+                                                  void* stream) {
+  if (wait_polls < 0) return SGLK_E_ARG;
+  const uint32_t polls = wait_polls > int64_t(0xFFFFFFFFu) ? 0xFFFFFFFFu : uint32_t(wait_polls);
+  const sglk::GateIn gate{row_ready_counters, ready_target, panel_rank, panel_world, whole_panels, polls};
   return sglk::gemm_entry(A, B, sa, sb, C, M, N, K, lda, ldb, ldc, sa_stride_m, sa_stride_k, sb_stride_k, sb_stride_n,
                           out_dtype, 29, num_sms, 0, nullptr, 0, stream, nullptr, 0, nullptr, nullptr, &gate);
 }

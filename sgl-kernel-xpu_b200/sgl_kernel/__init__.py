@@ -21,6 +21,7 @@ from .linear import (
     create_per_token_group_quant_fp8_output_scale,
     per_token_group_quant_fp8,
 )
+from ._ops import reserve_gemm_workspace
 from .moe import fp8_blockwise_scaled_grouped_mm
 from .sharded import ColumnShardedFp8Linear, HostStreamedShardedFp8Linear
 
@@ -41,4 +42,5 @@ __all__ = [
     "HostStreamedFp8Linear",
     "ColumnShardedFp8Linear",
     "HostStreamedShardedFp8Linear",
+    "reserve_gemm_workspace",
 ]

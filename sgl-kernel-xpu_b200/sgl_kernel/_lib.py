@@ -17,7 +17,7 @@ LIB_PATH = os.environ.get(
 # dtype / layout codes of include/sglk_fp8.h
 BF16, F16, F32, E4M3, INT8 = 0, 1, 2, 3, 4
 SCALE_F32_ROW_MAJOR, SCALE_F32_COL_MAJOR, SCALE_UE8M0_ROW_MAJOR, SCALE_UE8M0_COL_PACKED = 0, 1, 2, 3
-ABI_VERSION = 2
+ABI_VERSION = 3
 STREAMK_AUTO, STREAMK_FORCE, STREAMK_NEVER, GROUP_M_SHIFT, SPLIT_SHIFT, DECODE_2D_LOADS = 0, 1, 2, 8, 16, 1 << 24
 
 _i64, _i32, _f32, _vp = ctypes.c_int64, ctypes.c_int, ctypes.c_float, ctypes.c_void_p
@@ -50,7 +50,7 @@ SYMBOLS = {
         _i32, [_vp, _vp, _vp, _vp, _vp, ctypes.POINTER(_vp), _i32, _vp] + [_i64] * 10 + [_i32, _i32, _i32, _vp, _i64, _vp]),
     "sglk_per_token_group_quant_fp8_bcast": (_i32, [_vp, _vp, _vp, _vp, _i64, _i64, _i64, _i32, _f32, _i32, _vp]),
     "sglk_fp8_blockwise_scaled_mm_gated": (
-        _i32, [_vp, _vp, _vp, _vp, _vp] + [_i64] * 10 + [_i32, _i32, _vp, ctypes.c_uint32, _i32, _i32, _i32, _vp]),
+        _i32, [_vp, _vp, _vp, _vp, _vp] + [_i64] * 10 + [_i32, _i32, _vp, ctypes.c_uint32, _i32, _i32, _i32, _i64, _vp]),
     "sglk_gated_walk_order": (_i64, [_vp, _i64, _i64, _i64, _i32, _i32, _i32]),
     "sglk_gemm_num_variants": (_i32, []),
     "sglk_gemm_variant_name": (ctypes.c_char_p, [_i32]),

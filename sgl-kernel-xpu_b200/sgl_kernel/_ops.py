@@ -228,30 +228,65 @@ def _gemm_checks(mat_a, mat_b, scales_a, scales_b, out_dtype):
 # Stream-K workspaces: one zero-initialised buffer per (device, stream), grown on demand.  The kernel
 # leaves the counter region zeroed, so the buffer is reused by consecutive launches on its stream
 # (the same per-process cache idea as the reference's `_get_cache_buf`, python/sgl_kernel/gemm.py:80).
+# A buffer that has been handed to a launch is NEVER given back to the allocator: a CUDA graph captured earlier still
+# holds its address, and if the memory went to another tensor a replay would meet non-zero tile counters (tiles never
+# finished, silently wrong output) and would scribble partials over that tensor.  Replaced buffers are parked in
+# `_retired` for the life of the process; growth is geometric so that list stays short.
 _workspaces = {}
+_retired = []
 _workspaces_lock = threading.Lock()
 
 
 def _get_workspace(device: torch.device, stream_ptr: int, nbytes: int) -> Optional[torch.Tensor]:
     """The cached workspace of (device, stream), or None when one would have to be created inside a CUDA-graph
     capture: its zero-fill would only be recorded, not executed, and an eager launch before the first replay would
-    then meet garbage tile counters.  The op falls back to whole-tile scheduling for that call (same results);
-    warm the op up once outside the capture to get stream-K inside graphs."""
+    then meet garbage tile counters.  The op falls back to whole-tile scheduling for that call (same results).
+    The key is the stream the launch goes to: to get stream-K inside a graph, run the warm-up ON THE CAPTURE STREAM
+    (torch.cuda.graph captures on a side stream, not on the stream an earlier eager warm-up used) or call
+    `reserve_gemm_workspace(shapes, stream=capture_stream)` before capturing."""
     key = (device.index, stream_ptr)
     with _workspaces_lock:
         ws = _workspaces.get(key)
         if ws is None or ws.numel() < nbytes:
             if torch.cuda.is_current_stream_capturing():
                 return None
-            ws = torch.zeros(max(nbytes, 1 << 20), dtype=torch.uint8, device=device)
+            size = max(nbytes, 1 << 20)
+            if ws is not None:
+                size = max(size, 2 * ws.numel())
+                _retired.append(ws)          # graphs captured so far keep a valid, still-zeroed buffer
+            ws = torch.zeros(size, dtype=torch.uint8, device=device)
             _workspaces[key] = ws
         return ws
 
 
 def _invalidate_workspace(device: torch.device, stream_ptr: int) -> None:
-    """After a failed launch the tile counters may be non-zero: drop the buffer, the next call gets a fresh zeroed one."""
+    """After a failed launch the tile counters may be non-zero: stop using the buffer (the next call gets a fresh zeroed
+    one) but keep it alive, for the same reason as above."""
     with _workspaces_lock:
-        _workspaces.pop((device.index, stream_ptr), None)
+        ws = _workspaces.pop((device.index, stream_ptr), None)
+        if ws is not None:
+            _retired.append(ws)
+
+
+def reserve_gemm_workspace(shapes, device=None, stream=None) -> int:
+    """Create (or grow), outside any capture, the workspace that fp8_blockwise_scaled_mm launches on `stream` of
+    `device` will use, large enough for every (M, N, K) in `shapes`; returns its size in bytes.  Call it with the
+    stream a CUDA graph is going to be captured on, so the captured launches can use stream-K scheduling, and with
+    the largest shapes the process will see, so the buffer never has to be replaced afterwards."""
+    dev = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
+    if dev.index is None:
+        dev = torch.device("cuda", torch.cuda.current_device())
+    lib = _lib.load()
+    with torch.cuda.device(dev):
+        if torch.cuda.is_current_stream_capturing():
+            raise RuntimeError("reserve_gemm_workspace must be called outside CUDA-graph capture")
+        sp = (torch.cuda.current_stream(dev) if stream is None else stream).cuda_stream
+        need = 1 << 20
+        for M, N, K in shapes:
+            need = max(need, lib.sglk_gemm_workspace_bytes(int(M), int(N), int(K), -1, 0, 0),
+                       lib.sglk_gemm_workspace_bytes(int(M), int(N), int(K), -1, 0, _lib.STREAMK_FORCE))
+        ws = _get_workspace(dev, sp, need)
+    return ws.numel()
 
 
 # Scheduling override for tests and tuning tools (thread-local, Python-side only — the C library keeps no state):
@@ -382,9 +417,11 @@ def _quant_bcast(x, q_ptr: int, s_ptr: int, counters_ptr: int, multicast: bool, 
 
 
 def _gemm_gated(mat_a, mat_b, scales_a, scales_b, out_dtype, counters, target: int, panel_rank: int, panel_world: int,
-                num_sms: int = 0, whole_panels: bool = False):
+                num_sms: int = 0, whole_panels: bool = False, wait_polls: int = 0):
     """fp8_blockwise_scaled_mm whose activation rows arrive during the launch (include/sglk_fp8.h:
-    sglk_fp8_blockwise_scaled_mm_gated).  `counters`: uint32/int32 tensor, one entry per 256 rows of mat_a."""
+    sglk_fp8_blockwise_scaled_mm_gated).  `counters`: uint32/int32 tensor, one entry per 256 rows of mat_a.
+    wait_polls: 0 = wait for late rows as long as it takes; n > 0 = trap (sticky launch failure, the CUDA context is lost)
+    after n polling rounds of ~1-2 us."""
     _check(mat_a.is_cuda and mat_b.is_cuda and scales_a.is_cuda and scales_b.is_cuda and counters.is_cuda,
            "fp8_blockwise_scaled_mm: tensors must be CUDA tensors")
     M, N, K = _gemm_checks(mat_a, mat_b, scales_a, scales_b, out_dtype)
@@ -400,7 +437,7 @@ def _gemm_gated(mat_a, mat_b, scales_a, scales_b, out_dtype, counters, target: i
             mat_a.data_ptr(), mat_b.data_ptr(), scales_a.data_ptr(), scales_b.data_ptr(), out.data_ptr(), M, N, K, lda, ldb,
             out.stride(0), scales_a.stride(0), scales_a.stride(1), scales_b.stride(0), scales_b.stride(1),
             _GEMM_OUT[out_dtype], num_sms, counters.data_ptr(), int(target) & 0xFFFFFFFF, int(panel_rank), int(panel_world),
-            1 if whole_panels else 0, _stream_ptr(mat_a))
+            1 if whole_panels else 0, int(wait_polls), _stream_ptr(mat_a))
     _lib.check(rc, "fp8_blockwise_scaled_mm (gated)")
     return out
 

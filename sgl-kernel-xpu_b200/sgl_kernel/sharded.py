@@ -120,6 +120,11 @@ class ColumnShardedFp8Linear:
         self._sq_buf.zero_()
         self._sq_hdl = symm_mem.rendezvous(self._sq_buf, self.group if self.group is not None else dist.group.WORLD)
         self._sq_per_set, self._sq_tokens, self._sq_step = per_set, max_tokens, 0
+        # how long the gated GEMM waits for a late rank: 0 = as long as it takes (the default, like any collective);
+        # n > 0 = trap after n polling rounds of ~1-2 us — a STICKY failure that costs this process its CUDA context, so
+        # only for runs where a hang is worse (benchmarks and tests on boxes with a wall-clock limit)
+        if not hasattr(self, "gated_wait_polls"):
+            self.gated_wait_polls = 0
         self._sq_hdl.barrier(channel=0)                      # everybody's counters are zero before anybody adds to them
         mc = getattr(self._sq_hdl, "multicast_ptr", 0)
         self._sq_mc = int(mc) if mc else 0
@@ -180,7 +185,8 @@ class ColumnShardedFp8Linear:
         xs = self._sq_buf[off_s:off_s + m * g * 4].view(torch.float32).view(m, g)
         cnt = self._sq_buf[off_c:off_c + (m // 256) * 4].view(torch.int32)
         out = _ops._gemm_gated(xq, self.local.weight_q.t(), xs, self.local.weight_scale.t(), self.local.out_dtype, cnt,
-                               calls * _ops.counter_increments(k), self.rank, self.world, whole_panels=not multicast)
+                               calls * _ops.counter_increments(k), self.rank, self.world, whole_panels=not multicast,
+                               wait_polls=self.gated_wait_polls)
         self._sq_step += 1
         return out
 

@@ -10,6 +10,13 @@ import sgl_kernel
 from oracle import torch_oracle as O
 from sgl_kernel import _ops
 
+
+def _gated(*args, **kw):
+    """the gated GEMM with a bounded wait (a few seconds): here a trap is better than a box that hangs"""
+    kw.setdefault("wait_polls", 4_000_000)
+    return _ops._gemm_gated(*args, **kw)
+
+
 pytestmark = pytest.mark.gpu
 DEV = "cuda"
 
@@ -59,10 +66,10 @@ def test_gated_gemm_matches_plain(M, N, K, world):
     cnt = torch.full((M // 256,), 3 * inc, dtype=torch.int32, device=DEV)     # "third call on this buffer"
     for rank in range(world):
         for whole in (False, True):                      # both arrival orders of the other ranks' panels
-            out = _ops._gemm_gated(xq, wq.t(), xs, ws.t(), torch.bfloat16, cnt, 3 * inc, rank, world, whole_panels=whole)
+            out = _gated(xq, wq.t(), xs, ws.t(), torch.bfloat16, cnt, 3 * inc, rank, world, whole_panels=whole)
             torch.cuda.synchronize()
             assert torch.equal(out, ref), f"rank {rank} of {world}, whole_panels={whole}"
-    out = _ops._gemm_gated(xq, wq.t(), xs, ws.t(), torch.bfloat16, cnt, 2 * inc, 0, world)   # counters ahead of the target
+    out = _gated(xq, wq.t(), xs, ws.t(), torch.bfloat16, cnt, 2 * inc, 0, world)   # counters ahead of the target
     torch.cuda.synchronize()
     assert torch.equal(out, ref)
 
@@ -83,7 +90,7 @@ def test_quant_then_gated_gemm_stream_order():
             lo = r * rows
             _ops._quant_bcast(x[lo:lo + rows], q.data_ptr() + lo * K, s.data_ptr() + lo * (K // 128) * 4,
                               cnt.data_ptr() + (lo // 256) * 4, multicast=False)
-        out = _ops._gemm_gated(q.view(torch.float8_e4m3fn), wq.t(), s, ws.t(), torch.bfloat16, cnt,
+        out = _gated(q.view(torch.float8_e4m3fn), wq.t(), s, ws.t(), torch.bfloat16, cnt,
                                (step + 1) * _ops.counter_increments(K), step % world, world)
         torch.cuda.synchronize()
         assert torch.equal(out, ref)
@@ -95,8 +102,47 @@ def test_gated_errors():
     xq, xs = layer.quantize_input(x)
     cnt = torch.zeros(2, dtype=torch.int32, device=DEV)
     with pytest.raises(RuntimeError):        # 512 rows are not 4 whole 256-row panels
-        _ops._gemm_gated(xq, wq.t(), xs, ws.t(), torch.bfloat16, cnt, 0, 0, 4)
+        _gated(xq, wq.t(), xs, ws.t(), torch.bfloat16, cnt, 0, 0, 4)
     with pytest.raises(RuntimeError):        # M-major scales cannot be gated
-        _ops._gemm_gated(xq, wq.t(), xs.t().contiguous().t(), ws.t(), torch.bfloat16, cnt, 0, 0, 1)
+        _gated(xq, wq.t(), xs.t().contiguous().t(), ws.t(), torch.bfloat16, cnt, 0, 0, 1)
     with pytest.raises(RuntimeError):        # rows not a multiple of the counter block
         _ops._quant_bcast(x[:100], xq.data_ptr(), xs.data_ptr(), cnt.data_ptr(), multicast=False)
+
+
+@pytest.mark.parametrize("M,N,K,world,whole", [(2048, 768, 1024, 4, False), (2048, 512, 2048, 2, True),
+                                                 (256 * 66, 256, 512, 2, False)])
+def test_gated_gemm_waits_for_rows_that_arrive_during_the_launch(M, N, K, world, whole):
+    """The GEMM is launched on buffers that hold poison (NaN codes, NaN scales) and counters below the target; a side
+    stream delivers rows and counters block by block WHILE it runs — late, and not in the order the kernel walks them —
+    the way the copy-engine transport of forward_sharded_quant does (data first, then the counter, in stream order).
+    Exercises the polling loop, the publication of the arrival mask to the promotion warps, the proxy fence after a late
+    arrival and the late scale load; the last case has more than 64 m-blocks (one counter polled per tile).  A tile
+    started before its rows were there would put NaN into the output."""
+    x, wq, ws = make(M, N, K, seed=M + K + world)
+    layer = sgl_kernel.Fp8BlockLinear(wq, ws)
+    xq, xs = layer.quantize_input(x)
+    ref = layer.forward_quantized(xq, xs)
+    inc = _ops.counter_increments(K)
+    nblk = M // 256
+    done = torch.full((nblk,), 7 * inc, dtype=torch.int32, device=DEV)        # "seventh call on this buffer"
+    q = torch.full((M, K), 0x7F, dtype=torch.uint8, device=DEV)               # 0x7F = e4m3 NaN
+    s = torch.full((M, K // 128), float("nan"), dtype=torch.float32, device=DEV)
+    cnt = torch.full((nblk,), 6 * inc, dtype=torch.int32, device=DEV)
+    xq8 = xq.view(torch.uint8)
+    side = torch.cuda.Stream()
+    torch.cuda.synchronize()
+    step = max(1, nblk // 16)
+    with torch.cuda.stream(side):
+        torch.cuda._sleep(3_000_000)                                          # ~1.5 ms: the GEMM is running and waiting by then
+        for b0 in reversed(range(0, nblk, step)):                             # last blocks first: the walk's first tiles wait longest
+            r0, r1 = b0 * 256, min(nblk, b0 + step) * 256
+            q[r0:r1].copy_(xq8[r0:r1], non_blocking=True)
+            s[r0:r1].copy_(xs[r0:r1], non_blocking=True)
+            cnt[b0:b0 + step].copy_(done[b0:b0 + step], non_blocking=True)
+            torch.cuda._sleep(100_000)
+    # 128 of the 148 SMs: the delivery needs none for its copies, but the spinning helper kernels must stay schedulable
+    out = _gated(q.view(torch.float8_e4m3fn), wq.t(), s, ws.t(), torch.bfloat16, cnt, 7 * inc, world - 1, world,
+                 num_sms=128, whole_panels=whole)
+    torch.cuda.synchronize()
+    assert not torch.isnan(out.float()).any(), "a tile was started before its rows had arrived"
+    assert torch.equal(out, ref)

@@ -494,3 +494,55 @@ def test_capture_without_warmup_is_safe():
     torch.cuda.synchronize()
     check(eager.cpu(), ref)
     check(out.cpu(), ref)
+
+
+def test_graph_keeps_its_workspace_when_the_cache_grows():
+    """A graph captured with a stream-K launch points at the workspace of its stream.  When a later eager call needs a
+    bigger one, the old buffer must stay alive and zeroed: were it handed back to the allocator, the tensor that gets
+    the memory next would put non-zero bytes under the graph's tile counters and the replay would be wrong."""
+    a, b, sa, sb = O.make_gemm_inputs(128, 2112, 2048, seed=21)
+    ad, bd = a.to(DEV), b.t().contiguous().to(DEV).t()
+    sad, sbd = sa.to(DEV), sb.to(DEV)
+    ref = O.baseline_scaled_mm(a, b, sa, sb, torch.bfloat16)
+    st = torch.cuda.Stream()
+    g = torch.cuda.CUDAGraph()
+    with torch.cuda.stream(st):
+        with _ops.stream_k_mode("force"):
+            _ops._gemm(ad, bd, sad, sbd, torch.bfloat16)               # warm-up on the capture stream: creates its workspace
+            old = _ops._workspaces[(ad.device.index, st.cuda_stream)]
+            with torch.cuda.graph(g, stream=st):
+                out = _ops._gemm(ad, bd, sad, sbd, torch.bfloat16)
+        grown = _ops._get_workspace(ad.device, st.cuda_stream, old.numel() * 3)
+        assert grown.data_ptr() != old.data_ptr() and any(w is old for w in _ops._retired)
+        old_ptr = old.data_ptr()
+        del old
+        torch.cuda.synchronize()
+        junk = [torch.full((1 << 20,), 0x5A, dtype=torch.uint8, device=DEV) for _ in range(8)]   # would land on a freed buffer
+        assert all(j.data_ptr() != old_ptr for j in junk)
+        g.replay()
+    torch.cuda.synchronize()
+    check(out.cpu(), ref)
+
+
+def test_reserve_gemm_workspace_gives_side_stream_captures_stream_k():
+    """torch.cuda.graph captures on a side stream; a warm-up on the default stream does not create that stream's
+    workspace.  reserve_gemm_workspace(stream=...) does, so the captured launch gets one (and stream-K with it)."""
+    st = torch.cuda.Stream()
+    key = (torch.cuda.current_device(), st.cuda_stream)
+    assert key not in _ops._workspaces
+    n = sgl_kernel.reserve_gemm_workspace([(128, 2112, 2048), (16384, 4096, 7168)], stream=st)
+    assert _ops._workspaces[key].numel() == n >= _lib.load().sglk_gemm_workspace_bytes(16384, 4096, 7168, -1, 0, 0)
+    a, b, sa, sb = O.make_gemm_inputs(128, 2112, 2048, seed=22)
+    ad, bd, sad, sbd = a.to(DEV), b.t().contiguous().to(DEV).t(), sa.to(DEV), sb.to(DEV)
+    g = torch.cuda.CUDAGraph()
+    with torch.cuda.stream(st):
+        with torch.cuda.graph(g, stream=st):
+            with _ops.stream_k_mode("force"):
+                out = _ops._gemm(ad, bd, sad, sbd, torch.bfloat16)
+            assert _ops._get_workspace(ad.device, st.cuda_stream, 1 << 20) is _ops._workspaces[key]
+        with pytest.raises(RuntimeError, match="outside"):
+            with torch.cuda.graph(torch.cuda.CUDAGraph(), stream=st):
+                sgl_kernel.reserve_gemm_workspace([(1, 1, 16)], stream=st)
+    g.replay()
+    torch.cuda.synchronize()
+    check(out.cpu(), O.baseline_scaled_mm(a, b, sa, sb, torch.bfloat16))

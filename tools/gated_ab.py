@@ -8,6 +8,13 @@ sys.path[:0] = [ROOT, os.path.join(ROOT, "sgl-kernel-xpu_b200")]
 import torch
 import sgl_kernel
 from sgl_kernel import _ops
+
+
+def _gated(*args, **kw):
+    """the gated GEMM with a bounded wait (a few seconds): here a trap is better than a box that hangs"""
+    kw.setdefault("wait_polls", 4_000_000)
+    return _ops._gemm_gated(*args, **kw)
+
 dev = "cuda"
 worlds = [int(v) for v in (sys.argv[1] if len(sys.argv) > 1 else "2,4,8").split(",")]
 M, NT, K = (int(sys.argv[i]) if len(sys.argv) > i else d for i, d in ((2, 16384), (3, 18432), (4, 7168)))
@@ -37,10 +44,10 @@ for world in worlds:
     fns = {"plain": lambda: layer.forward_quantized(xq, xs)}
     for whole in (False, True):
         for rank in sorted({0, world - 1}):
-            out = _ops._gemm_gated(xq, wq.t(), xs, ws.t(), torch.bfloat16, zero, 0, rank, world, whole_panels=whole)
+            out = _gated(xq, wq.t(), xs, ws.t(), torch.bfloat16, zero, 0, rank, world, whole_panels=whole)
             assert torch.equal(out, ref)
             fns[f"gated_{'panels' if whole else 'slices'}_rank{rank}"] = (
-                lambda rank=rank, whole=whole: _ops._gemm_gated(xq, wq.t(), xs, ws.t(), torch.bfloat16, zero, 0, rank, world,
+                lambda rank=rank, whole=whole: _gated(xq, wq.t(), xs, ws.t(), torch.bfloat16, zero, 0, rank, world,
                                                                 whole_panels=whole))
     # interleaved rounds: the chip's clock drifts under its power cap, so configurations are compared round by round
     ts = {k: [] for k in fns}

@@ -10,6 +10,13 @@ import torch.distributed as dist
 import sgl_kernel
 from sgl_kernel.sharded import ColumnShardedFp8Linear, shard_bounds
 
+
+def _gated(*args, **kw):
+    """the gated GEMM with a bounded wait (a few seconds): here a trap is better than a box that hangs"""
+    kw.setdefault("wait_polls", 4_000_000)
+    return _ops._gemm_gated(*args, **kw)
+
+
 rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
 torch.cuda.set_device(int(os.environ["LOCAL_RANK"]))
 dev = torch.device("cuda", int(os.environ["LOCAL_RANK"]))
@@ -21,6 +28,7 @@ wq = ((torch.rand(hi - lo, K, generator=gw, device=dev) - 0.5) * 896).to(torch.f
 ws = (torch.rand(-((hi - lo) // -128), K // 128, generator=gw, device=dev) + 0.5) * 1e-3
 layer = ColumnShardedFp8Linear(sgl_kernel.Fp8BlockLinear(wq, ws), N)
 ok = layer.sharded_quant_supported(M) and layer.enable_sharded_quant(M)
+layer.gated_wait_polls = 16_000_000
 TRANSPORTS = ["copy", "multicast"] if (ok and layer._sq_mc) else ["copy"]
 res = {"world": world, "M": M, "N": N, "K": K, "multicast_available": bool(ok)}
 same = True
@@ -50,7 +58,7 @@ if ok:
     fns = {"replicated_quant_step": lambda: layer.forward_local(x),
            "sharded_quant_step": lambda: layer.forward_sharded_quant(x),
            "gemm_alone": lambda: layer.local.forward_quantized(xq, xs),
-           "gated_gemm_alone": lambda: _ops._gemm_gated(xq, wq.t(), xs, ws.t(), torch.bfloat16, zero, 0, rank, world, whole_panels=True)}
+           "gated_gemm_alone": lambda: _gated(xq, wq.t(), xs, ws.t(), torch.bfloat16, zero, 0, rank, world, whole_panels=True)}
     if "multicast" in TRANSPORTS:
         fns["sharded_quant_step_multicast"] = lambda: layer.forward_sharded_quant(x, transport="multicast")
     # interleaved rounds (the clocks drift under the power cap); every configuration is a collective or rank-local, and
