@@ -176,3 +176,41 @@ def test_product_never_imports_oracle():
                 txt = open(os.path.join(dirpath, f)).read()
                 assert not re.search(r"^\s*(from|import)\s+oracle\b", txt, re.M), f"{f} imports the oracle"
                 assert "torch_oracle" not in txt and "c_oracle" not in txt, f
+
+
+def test_grouped_bench_imports_under_a_foreign_command_line(monkeypatch):
+    """bench.py imports tools/grouped_bench.py for its f4 sub-record; the module must not read the importer's argv
+    (BENCH_r02.json carried "invalid literal for int() with base 10: '--gpus'" instead of the record) nor touch a GPU
+    at import time."""
+    import importlib
+    import sys
+
+    monkeypatch.setattr(sys, "argv", ["bench.py", "--gpus", "1", "--steps", "20"])
+    monkeypatch.syspath_prepend(os.path.join(ROOT, "tools"))
+    sys.modules.pop("grouped_bench", None)
+    gb = importlib.import_module("grouped_bench")
+    assert gb.Es == [8, 32, 64] and gb.avg == 512 and callable(gb.records)
+    sys.modules.pop("grouped_bench", None)
+
+
+def test_jit_entry_points_have_the_reference_signatures():
+    """sgl_kernel.jit.per_token_group_quant_8bit{,_v2}: names, order and defaults of
+    /root/reference/python/sgl_kernel/jit/per_token_group_quant_8bit.py:153-162 and
+    jit/per_token_group_quant_8bit_v2.py:118-129; both refuse a CPU tensor the way the reference refuses a non-XPU one."""
+    from sgl_kernel import jit
+
+    assert set(jit.__all__) == {"per_token_group_quant_8bit", "per_token_group_quant_8bit_v2"}
+    common = ["input", "output_q", "output_s", "group_size", "eps", "min_8bit", "max_8bit", "scale_ue8m0"]
+    s1 = inspect.signature(jit.per_token_group_quant_8bit)
+    assert list(s1.parameters) == common and s1.parameters["scale_ue8m0"].default is False
+    s2 = inspect.signature(jit.per_token_group_quant_8bit_v2)
+    assert list(s2.parameters) == common + ["fuse_silu_and_mul", "masked_m"]
+    assert s2.parameters["fuse_silu_and_mul"].default is False and s2.parameters["masked_m"].default is None
+    x = torch.zeros(2, 128, dtype=torch.bfloat16)
+    q, s = torch.empty(2, 128, dtype=torch.float8_e4m3fn), torch.empty(2, 1)
+    with pytest.raises(RuntimeError, match="CUDA"):
+        jit.per_token_group_quant_8bit(x, q, s, 128, 1e-10, -448.0, 448.0)
+    with pytest.raises(RuntimeError, match="CUDA"):
+        jit.per_token_group_quant_8bit_v2(x, q, s, 128, 1e-10, -448.0, 448.0)
+    with pytest.raises(AssertionError, match="eps"):
+        jit.per_token_group_quant_8bit_v2(x, q, s, 128, 1e-6, -448.0, 448.0)

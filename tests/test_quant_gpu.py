@@ -473,3 +473,25 @@ def test_cuda_graph_capture():
     torch.cuda.synchronize()
     q_ref, s_ref = O.per_token_group_quant_fp8_ref(x.cpu(), 128, EPS)
     assert_bits_equal(q.cpu(), s.cpu(), q_ref, s_ref)
+
+
+@pytest.mark.parametrize("fuse", [False, True])
+def test_jit_entry_points_match_the_ops(fuse):
+    """sgl_kernel.jit.* (the reference's JIT twins, jit/__init__.py:34-35) give the AOT ops' bits and the reference's
+    return values: (output_q, output_s) from v1, None from v2."""
+    from sgl_kernel import jit
+
+    T, H = 48, 512
+    x = torch.randn(T, H * (2 if fuse else 1), device="cuda").to(torch.bfloat16)
+    mk = lambda: (torch.empty(T, H, dtype=torch.float8_e4m3fn, device="cuda"), torch.empty(T, H // 128, device="cuda"))
+    q0, s0 = mk()
+    torch.ops.sgl_kernel.sgl_per_token_group_quant_8bit_v2(x, q0, s0, 128, 1e-10, -448.0, 448.0, False, fuse, None)
+    q1, s1 = mk()
+    assert jit.per_token_group_quant_8bit_v2(x, q1, s1, 128, 1e-10, -448.0, 448.0, False, fuse) is None
+    assert torch.equal(q0.view(torch.uint8), q1.view(torch.uint8)) and torch.equal(s0, s1)
+    assert jit.per_token_group_quant_8bit_v2(x[:0], q1[:0], s1[:0], 128, 1e-10, -448.0, 448.0) is None
+    if not fuse:
+        q2, s2 = mk()
+        rq, rs = jit.per_token_group_quant_8bit(x, q2, s2, 128, 1e-10, -448.0, 448.0)
+        assert rq is q2 and rs is s2
+        assert torch.equal(q0.view(torch.uint8), q2.view(torch.uint8)) and torch.equal(s0, s2)

@@ -10,12 +10,18 @@ sys.path[:0] = [ROOT, os.path.join(ROOT, "sgl-kernel-xpu_b200")]
 import torch
 import sgl_kernel
 dev = "cuda"
-Es = [int(v) for v in (sys.argv[1] if len(sys.argv) > 1 else "8,32,64").split(",")]
-avg = int(sys.argv[2]) if len(sys.argv) > 2 else 512
-flush = torch.zeros(256 << 20, dtype=torch.uint8, device=dev).view(torch.int64)
+# defaults; bench.py imports this module and sets them, the command line is read only under __main__ (an importer's argv
+# is not ours: parsing it at import time turned bench.py's f4 sub-record into an error string in BENCH_r02.json)
+Es = [8, 32, 64]
+avg = 512
+_flush = None
 
 
 def med(fn, reps=9):
+    global _flush
+    if _flush is None:
+        _flush = torch.zeros(256 << 20, dtype=torch.uint8, device=dev).view(torch.int64)
+    flush = _flush
     for _ in range(3):
         fn()
     ts = []
@@ -65,5 +71,9 @@ def records():
 
 
 if __name__ == "__main__":
+    if len(sys.argv) > 1:
+        Es = [int(v) for v in sys.argv[1].split(",")]
+    if len(sys.argv) > 2:
+        avg = int(sys.argv[2])
     for r in records():
         print(json.dumps(r), flush=True)
