@@ -16,7 +16,9 @@ ls -la gpurun_out | grep $R
 # decode shapes (weight streaming): one full capture each of the row-balanced swap-AB kernel the default dispatch picks —
 # N=24576 at 16 and 64 tokens (one 168-row range per CTA), N=2112 at 16 tokens (clusters of 4 over K) — and of the 128-row
 # tile kernel at M=128
-for T in "decode 16 24576" "decoden 16 2112" "decode64 64 24576" "decode128 128 24576"; do
+# (r03: decode128 = what is timed at M=128 now, the one-wave 128x256 split-N tiles of variant 14; decode256 = variant 29
+# pair tiles at M=256; decoden128 = the 128-wide stream-K tiles at N=2112 M=128)
+for T in "decode 16 24576" "decoden 16 2112" "decode64 64 24576" "decode128 128 24576" "decode256 256 24576" "decoden128 128 2112"; do
   set -- $T
   DCMD="python tools/ncu_target.py gemm $2 $3 7168"
   $DCMD > gpurun_out/plain_$1.log 2>&1 && \

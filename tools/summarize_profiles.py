@@ -85,6 +85,8 @@ dump_kernel("decode")
 dump_kernel("decoden")
 dump_kernel("decode64")
 dump_kernel("decode128")
+dump_kernel("decode256")
+dump_kernel("decoden128")
 dump_kernel("grouped")
 dump_kernel("gated")
 dump_kernel("tokenquant")
