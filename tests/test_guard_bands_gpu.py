@@ -200,3 +200,42 @@ def test_grouped_gemm_stays_inside_output_and_is_repeatable():
         if first is None:
             first = out.clone()
         assert torch.equal(out, first)
+
+
+@pytest.mark.parametrize("M,N,K,world", [(1024, 768, 1024, 2), (2048, 1280, 2048, 4)])
+def test_row_sharded_quant_and_gated_gemm_stay_inside_their_buffers_and_repeat(M, N, K, world):
+    """sglk_per_token_group_quant_fp8_bcast writes codes, scales and arrival counters at raw addresses;
+    sglk_fp8_blockwise_scaled_mm_gated polls the counters and hands an arrival mask between warps through shared memory.
+    All four buffers are guarded views; 10 runs (counters accumulating, each rank's panel walk in turn) must leave the
+    canaries alone and give the same bits every time."""
+    lib = _lib.load()
+    g = K // 128
+    x = torch.randn(M, K, device=DEV).to(torch.bfloat16)
+    wq = ((torch.rand(N, K, device=DEV) - 0.5) * 896).to(torch.float8_e4m3fn)
+    ws = (torch.rand(-(N // -128), g, device=DEV) + 0.5) * 1e-3
+    gq, gs, gc = Guarded(M * K), Guarded(M * g * 4), Guarded((M // 256) * 4)
+    gc.data().zero_()
+    q, s, cnt = gq.view((M, K), torch.uint8), gs.view((M, g), torch.float32), gc.view((M // 256,), torch.int32)
+    rows = M // world
+    first = None
+    for run in range(10):
+        for r in range(world):
+            lo = r * rows
+            _ops._quant_bcast(x[lo:lo + rows], q.data_ptr() + lo * K, s.data_ptr() + lo * g * 4,
+                              cnt.data_ptr() + (lo // 256) * 4, multicast=False)
+        go = Guarded(M * N * 2)
+        out = go.view((M, N), torch.bfloat16)
+        rc = lib.sglk_fp8_blockwise_scaled_mm_gated(
+            q.data_ptr(), wq.data_ptr(), s.data_ptr(), ws.data_ptr(), out.data_ptr(), M, N, K, K, K, N, g, 1, 1, g,
+            _lib.BF16, 0, cnt.data_ptr(), (run + 1) * _ops.counter_increments(K), run % world, world, run & 1, 4_000_000,
+            torch.cuda.current_stream().cuda_stream)
+        assert rc == 0, lib.sglk_error_string(rc)
+        torch.cuda.synchronize()
+        for name, gb in (("codes", gq), ("scales", gs), ("counters", gc), ("gated GEMM output", go)):
+            gb.assert_intact(name)
+        assert cnt.tolist() == [(run + 1) * _ops.counter_increments(K)] * (M // 256)
+        if first is None:
+            first = out.clone()
+            ref = sgl_kernel.Fp8BlockLinear(wq, ws)(x)
+            assert torch.equal(first, ref)
+        assert torch.equal(out, first), f"run {run} differs from run 0"
